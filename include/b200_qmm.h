@@ -1,0 +1,181 @@
+/*
+ * b200_qmm.h -- C ABI of the B200-native (sm_100a) quantized MUL_MAT / MUL_MAT_ID hot path.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and a CUDA stream handle; no C++ or torch types.  Every pointer
+ * named "device" is a CUDA device pointer valid on the current device; every call is asynchronous on `stream` and
+ * returns a b200_status (0 = success).  There is NO CPU fallback: when no sm_100 device is present the calls fail with
+ * B200_ERR_NO_DEVICE / B200_ERR_CUDA.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the reference tree,
+ * DreamChaser-luzeyu/llama.cpp.dsp @ 9561c161).  The ggml backend plug-in that binds these into
+ * ggml_backend_i / supports_op / graph_compute lives in llama.cpp.dsp_b200/ggml_backend/ (see INTEGRATION.md).
+ */
+#ifndef B200_QMM_H
+#define B200_QMM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define B200_API
+#else
+#define B200_API __attribute__((visibility("default")))
+#endif
+
+/* cudaStream_t, kept opaque so that C callers need no CUDA headers */
+typedef void * b200_stream_t;
+
+typedef enum {
+    B200_OK              = 0,
+    B200_ERR_TYPE        = 1, /* ggml type not on the path */
+    B200_ERR_SHAPE       = 2, /* k not a multiple of the block size, negative sizes, ... */
+    B200_ERR_ALIGNMENT   = 3, /* pointer / stride alignment the kernels require is violated */
+    B200_ERR_WORKSPACE   = 4, /* workspace missing or too small */
+    B200_ERR_NO_DEVICE   = 5, /* no CUDA device of compute capability 10.x */
+    B200_ERR_CUDA        = 6, /* a CUDA runtime call failed: see b200_last_cuda_error() */
+    B200_ERR_UNSUPPORTED = 7
+} b200_status;
+
+/* weight types, numerically equal to enum ggml_type (ggml/include/ggml.h:350-392) */
+typedef enum {
+    B200_TYPE_Q4_0   = 2,
+    B200_TYPE_Q8_0   = 8,
+    B200_TYPE_Q8_1   = 9,
+    B200_TYPE_Q4_K   = 12,
+    B200_TYPE_Q6_K   = 14,
+    B200_TYPE_IQ4_XS = 23
+} b200_type;
+
+/* ---- introspection ------------------------------------------------------------------------------------------- */
+
+B200_API int          b200_qmm_abi_version(void);          /* bumped on any signature change; currently 1 */
+B200_API const char * b200_status_string(int status);
+B200_API const char * b200_last_cuda_error(void);          /* text of the last failing CUDA call on this thread */
+B200_API int          b200_device_ok(int device);          /* 1 if `device` is an sm_100 part this library runs on */
+B200_API int          b200_sm_count(int device);
+/* number of kernels this library has launched since load (all threads); bench.py reports the delta as gpu_launches */
+B200_API int64_t      b200_launch_count(void);
+
+/* is (type) one of Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS?      -- replaces the type switch in ggml_cuda_mul_mat,
+ * ggml/src/ggml-cuda/ggml-cuda.cu:1877-1938 and ggml_cuda_should_use_mmq, ggml/src/ggml-cuda/mmq.cu:99-153 */
+B200_API int    b200_type_supported(int type);
+B200_API int    b200_block_size(int type);                  /* elements per block   (ggml_blck_size)  */
+B200_API size_t b200_type_size(int type);                   /* bytes per block      (ggml_type_size)  */
+B200_API size_t b200_row_size(int type, int64_t k);         /* bytes per row of k   (ggml_row_size)   */
+/*
+ * Bytes a device allocation holding `nrows` rows must have so that the kernels' 16-byte-granular bulk loads stay
+ * inside it -- replaces ggml_backend_cuda_buffer_type_get_alloc_size, ggml/src/ggml-cuda/ggml-cuda.cu:675-688.
+ * (Any cudaMalloc'ed block already satisfies this: the driver's granularity is >= 256 B.)
+ */
+B200_API size_t b200_weight_alloc_size(int type, int64_t k, int64_t nrows);
+
+/* ---- activation quantizer ------------------------------------------------------------------------------------ */
+
+/*
+ * f32 rows -> ggml block_q8_1 {half d; half s; int8 qs[32]} (ggml/src/ggml-common.h:216-227), BIT-EXACT with
+ * quantize_row_q8_1_ref (ggml/src/ggml-quants.c:220-253).
+ * Replaces quantize_row_q8_1_cuda, ggml/src/ggml-cuda/quantize.cu:129-141 (whose own arithmetic is NOT bit-exact with
+ * the CPU reference; this one is).
+ *   x : device, nrows rows of k f32, row stride x_row_stride elements (>= k)
+ *   y : device, nrows * (k/32) blocks of 36 bytes, rows packed back to back
+ */
+B200_API int b200_quantize_q8_1(const float * x, int64_t x_row_stride, void * y, int64_t k, int64_t nrows,
+                                b200_stream_t stream);
+
+/* ---- dequantizer ---------------------------------------------------------------------------------------------- */
+
+/*
+ * quantized rows -> f32, BIT-EXACT with dequantize_row_{q4_0,q8_0,q4_K,q6_K,iq4_xs}
+ * (ggml/src/ggml-quants.c:255-273, 349-363, 1280-1302, 1690-1722, 2454-2476).
+ * Replaces the to_fp32 table ggml_get_to_fp32_cuda, ggml/src/ggml-cuda/convert.cu:654 (kernels :6-25,70-96,189-218,
+ * 254-278,440-455).
+ *   w : device, nrows rows, row stride w_row_stride bytes (0 => b200_row_size(type,k))
+ *   y : device, nrows rows of k f32, packed
+ */
+B200_API int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * y, int64_t k, int64_t nrows,
+                                 b200_stream_t stream);
+
+/* ---- MUL_MAT --------------------------------------------------------------------------------------------------- */
+
+/*
+ * dst[j*dst_row_stride + i] = sum_c W[i][c] * x[j*x_row_stride + c],   i < m, j < n
+ * (ggml_mul_mat semantics, ggml/src/ggml.c:2722-2747; weights "src0" = m rows of k, activations "src1" = n rows of k,
+ * dst = n rows of m).  Activations are quantized on the fly to q8_1 exactly as b200_quantize_q8_1 does.
+ * Replaces ggml_cuda_mul_mat for quantized src0 (ggml/src/ggml-cuda/ggml-cuda.cu:1877-1938) and what it dispatches
+ * to: quantize_row_q8_1_cuda + mul_mat_vec_q (mmvq.cu:130-206,423-511) for small n, quantize_mmq_q8_1_cuda +
+ * mul_mat_q (+ stream-k fixup) (mmq.cuh:2516-2762, mmq.cu:3-97) for large n.
+ *
+ *   W            device, quantized, m rows; row stride w_row_stride bytes (0 => packed). Must be 16-byte aligned for
+ *                Q4_K, 8 for IQ4_XS, 2 otherwise.
+ *   x            device f32, n rows of k, row stride x_row_stride elements
+ *   dst          device f32, n rows of m, row stride dst_row_stride elements
+ *   workspace    device scratch of at least b200_mul_mat_workspace_size(type, m, n, k) bytes (may be NULL if that is 0)
+ */
+B200_API size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k);
+B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x, int64_t x_row_stride,
+                             float * dst, int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
+                             size_t workspace_bytes, b200_stream_t stream);
+
+/* ---- MUL_MAT_ID ------------------------------------------------------------------------------------------------ */
+
+/*
+ * dst[t][s][:] = as[ids[t][s]] * b[t][s % ne11][:]        (ggml_mul_mat_id, ggml/src/ggml.c:2771-2799)
+ * Entirely on the device: the expert ids are read by the kernel, there is NO device->host copy or stream sync.
+ * Replaces ggml_cuda_mul_mat_id + k_copy_src1_to_contiguous + k_copy_dst_from_contiguous,
+ * ggml/src/ggml-cuda/ggml-cuda.cu:1940-2130 (which copies ids to the host and synchronizes, :2008-2011).
+ *
+ *   as   device, n_expert matrices of m rows x k, expert stride expert_stride bytes (0 => m * row_size)
+ *   b    device f32 [n_tokens][ne11][k]; token stride b_token_stride, slot stride b_slot_stride (elements)
+ *   ids  device int32 [n_tokens][>= n_used]; row stride ids_row_stride elements
+ *   dst  device f32 [n_tokens][n_used][m]; token stride dst_token_stride, slot stride dst_slot_stride (elements)
+ */
+B200_API size_t b200_mul_mat_id_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
+                                               int64_t n_tokens);
+B200_API int    b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const float * b,
+                                int64_t b_token_stride, int64_t b_slot_stride, int64_t ne11, const int32_t * ids,
+                                int64_t ids_row_stride, float * dst, int64_t dst_token_stride,
+                                int64_t dst_slot_stride, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
+                                int64_t n_tokens, void * workspace, size_t workspace_bytes, b200_stream_t stream);
+
+/* ---- multi-GPU row split ---------------------------------------------------------------------------------------- */
+
+/*
+ * Row range [*row_low, *row_high) of an m-row weight owned by `rank` of `world` under the reference's tensor_split
+ * rule: cumulative fractions, boundaries rounded down to a multiple of 128 rows, last rank takes the remainder
+ * (get_row_split / get_row_rounding, ggml/src/ggml-cuda/ggml-cuda.cu:727-753).  tensor_split == NULL => equal split.
+ */
+B200_API int b200_row_split(int64_t m, int world, int rank, const float * tensor_split, int64_t * row_low,
+                            int64_t * row_high);
+
+/*
+ * Row-split MUL_MAT with the all-gather FUSED into the GEMV epilogue: every rank computes rows [row_low,row_high) of
+ * dst and stores them straight into every peer's dst buffer over NVLink (peer_dst[r] = rank r's dst, mapped through
+ * CUDA IPC / peer access), then signals a per-call flag.  Replaces the broadcast + strided peer-copy + event
+ * choreography of ggml_cuda_op_mul_mat in split mode, ggml/src/ggml-cuda/ggml-cuda.cu:1560-1700.
+ * A plain NCCL all-gather of the slices produced by b200_mul_mat (dst = local slice) is the non-fused alternative.
+ *
+ *   W         this rank's row slice (rows row_low..row_high of the full matrix), packed
+ *   x         device f32 [n][k], identical on every rank
+ *   peer_dst  host array of `world` device pointers; entry r is rank r's full [n][m] dst (entry `rank` is local)
+ *   flags     host array of `world` device pointers to int32 arrival counters (one per rank, zero-initialised)
+ *   epoch     strictly increasing per call on a given (dst, flags) pair
+ */
+B200_API int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64_t x_row_stride,
+                                         float * const * peer_dst, int32_t * const * flags, int32_t epoch,
+                                         int64_t dst_row_stride, int64_t m, int64_t row_low, int64_t row_high,
+                                         int64_t n, int64_t k, int world, int rank, void * workspace,
+                                         size_t workspace_bytes, b200_stream_t stream);
+
+/* CUDA IPC helpers so that one-process-per-GPU hosts (torchrun) can exchange peer buffers without torch types */
+B200_API int b200_ipc_get_handle(void * device_ptr, void * handle_out_64_bytes);
+B200_API int b200_ipc_open_handle(const void * handle_64_bytes, void ** device_ptr_out);
+B200_API int b200_ipc_close_handle(void * device_ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_QMM_H */

@@ -1,0 +1,298 @@
+// api.cu -- the extern "C" boundary declared in include/b200_qmm.h: argument validation, kernel selection, workspace
+// carving.  Host-only logic; every device kernel lives in quantize.cu / mmvq.cu / mmq.cu.
+#include "actquant.cuh"
+#include "kernels.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+namespace b200 {
+
+thread_local char g_last_cuda_error[256] = "";
+static std::atomic<int64_t> g_launches{0};
+
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+int check_cuda(cudaError_t e, const char * what) {
+    if (e == cudaSuccess) return B200_OK;
+    snprintf(g_last_cuda_error, sizeof(g_last_cuda_error), "%s: %s (%s)", what, cudaGetErrorName(e),
+             cudaGetErrorString(e));
+    return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? B200_ERR_NO_DEVICE : B200_ERR_CUDA;
+}
+
+static int blck_of(int type) {
+    switch (type) {
+        case B200_TYPE_Q4_0: case B200_TYPE_Q8_0: case B200_TYPE_Q8_1: return 32;
+        case B200_TYPE_Q4_K: case B200_TYPE_Q6_K: case B200_TYPE_IQ4_XS: return 256;
+    }
+    return 0;
+}
+static size_t tsize_of(int type) {
+    switch (type) {
+        case B200_TYPE_Q4_0: return 18;
+        case B200_TYPE_Q8_0: return 34;
+        case B200_TYPE_Q8_1: return 36;
+        case B200_TYPE_Q4_K: return 144;
+        case B200_TYPE_Q6_K: return 210;
+        case B200_TYPE_IQ4_XS: return 136;
+    }
+    return 0;
+}
+static int align_of(int type) { return type == B200_TYPE_Q4_K ? 16 : type == B200_TYPE_IQ4_XS ? 8 : 2; }
+static bool weight_type(int type) { return type != B200_TYPE_Q8_1 && blck_of(type) != 0; }
+
+static int check_weights(int type, const void * W, int64_t & stride, int64_t k) {
+    if (!weight_type(type)) return B200_ERR_TYPE;
+    if (k < 0 || k % blck_of(type) != 0) return B200_ERR_SHAPE;
+    const int64_t rs = (int64_t) (k / blck_of(type)) * (int64_t) tsize_of(type);
+    if (stride == 0) stride = rs;
+    if (stride < rs) return B200_ERR_SHAPE;
+    const int al = align_of(type);
+    if ((uintptr_t) W % al != 0 || stride % al != 0) return B200_ERR_ALIGNMENT;
+    return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_qmm_abi_version(void) { return 1; }
+
+const char * b200_status_string(int s) {
+    switch (s) {
+        case B200_OK: return "ok";
+        case B200_ERR_TYPE: return "type not on the path (Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS)";
+        case B200_ERR_SHAPE: return "bad shape or stride";
+        case B200_ERR_ALIGNMENT: return "pointer or stride alignment";
+        case B200_ERR_WORKSPACE: return "workspace missing or too small";
+        case B200_ERR_NO_DEVICE: return "no sm_100 CUDA device";
+        case B200_ERR_CUDA: return "CUDA runtime error";
+        case B200_ERR_UNSUPPORTED: return "unsupported configuration";
+    }
+    return "unknown status";
+}
+
+const char * b200_last_cuda_error(void) { return g_last_cuda_error; }
+
+int b200_device_ok(int device) {
+    int major = 0, n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device) != cudaSuccess) return 0;
+    return major == 10;
+}
+
+int b200_sm_count(int device) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
+    return n;
+}
+
+int64_t b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int    b200_type_supported(int type) { return weight_type(type) ? 1 : 0; }
+int    b200_block_size(int type) { return blck_of(type); }
+size_t b200_type_size(int type) { return tsize_of(type); }
+size_t b200_row_size(int type, int64_t k) {
+    const int b = blck_of(type);
+    return b && k >= 0 && k % b == 0 ? (size_t) (k / b) * tsize_of(type) : 0;
+}
+size_t b200_weight_alloc_size(int type, int64_t k, int64_t nrows) {
+    const size_t n = b200_row_size(type, k) * (size_t) nrows;
+    return ((n + 15) & ~(size_t) 15) + 16;
+}
+
+int b200_quantize_q8_1(const float * x, int64_t x_row_stride, void * y, int64_t k, int64_t nrows,
+                       b200_stream_t stream) {
+    if (k < 0 || nrows < 0 || k % 32 != 0 || x_row_stride < k) return B200_ERR_SHAPE;
+    if ((uintptr_t) x % 4 != 0 || (uintptr_t) y % 4 != 0) return B200_ERR_ALIGNMENT;
+    return launch_quantize_q8_1_ggml(x, x_row_stride, y, k, nrows, (cudaStream_t) stream);
+}
+
+int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * y, int64_t k, int64_t nrows,
+                        b200_stream_t stream) {
+    if (!weight_type(type)) return B200_ERR_TYPE;
+    if (k < 0 || nrows < 0 || k % blck_of(type) != 0) return B200_ERR_SHAPE;
+    if (w_row_stride == 0) w_row_stride = (int64_t) b200_row_size(type, k);
+    return launch_dequantize_f32(type, w, w_row_stride, y, k, nrows, (cudaStream_t) stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------- MUL_MAT
+// n <= 2 : one fused launch (quantize in the GEMV prologue).
+// n  > 2 : quantize all columns once into the workspace (SoA q8_1), then GEMV launches of up to 8 columns.
+static const int FUSED_QUANT_MAX_COLS = 2;
+
+size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
+    (void) m;
+    if (!weight_type(type) || k <= 0 || n <= FUSED_QUANT_MAX_COLS) return 0;
+    return (size_t) n * q8_soa_layout(k).bytes;
+}
+
+int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x, int64_t x_row_stride, float * dst,
+                 int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace, size_t workspace_bytes,
+                 b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    int st = check_weights(type, W, w_row_stride, k);
+    if (st != B200_OK) return st;
+    if (m < 0 || n < 0 || x_row_stride < k || dst_row_stride < m) return B200_ERR_SHAPE;
+    if (m > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
+    if ((uintptr_t) x % 4 != 0 || (uintptr_t) dst % 4 != 0) return B200_ERR_ALIGNMENT;
+    if (m == 0 || n == 0) return B200_OK;
+    if (k == 0) {
+        B200_CUDA_TRY(cudaMemset2DAsync(dst, dst_row_stride * 4, 0, m * 4, n, stream));
+        return B200_OK;
+    }
+    const int maxc = gemv_max_cols(type, k);
+    if (maxc < 1) return B200_ERR_UNSUPPORTED;
+
+    gemv_args g = {};
+    g.type = type, g.W = (const uint8_t *) W, g.w_row_stride = w_row_stride;
+    g.m = m, g.k = k, g.dst_col_stride = dst_row_stride, g.x_col_stride = x_row_stride;
+    g.world = 1;
+
+    if (n <= FUSED_QUANT_MAX_COLS && n <= maxc) {
+        g.x = x, g.dst = dst, g.ncols = (int) n;
+        return launch_gemv(g, stream);
+    }
+    const q8_layout L = q8_soa_layout(k);
+    if (!workspace || workspace_bytes < (size_t) n * L.bytes) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 16 != 0) return B200_ERR_ALIGNMENT;
+    st = launch_quantize_q8_soa(x, x_row_stride, workspace, k, n, type == B200_TYPE_IQ4_XS, stream);
+    if (st != B200_OK) return st;
+    for (int64_t c0 = 0; c0 < n; c0 += maxc) {
+        g.ncols = (int) (n - c0 < maxc ? n - c0 : maxc);
+        g.xq    = (const uint8_t *) workspace + (size_t) c0 * L.bytes;
+        g.dst   = dst + c0 * dst_row_stride;
+        st = launch_gemv(g, stream);
+        if (st != B200_OK) return st;
+    }
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------- MUL_MAT_ID
+size_t b200_mul_mat_id_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
+                                      int64_t n_tokens) {
+    (void) type, (void) m, (void) k, (void) n_expert, (void) n_used, (void) n_tokens;
+    return 0;
+}
+
+int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const float * b, int64_t b_token_stride,
+                    int64_t b_slot_stride, int64_t ne11, const int32_t * ids, int64_t ids_row_stride, float * dst,
+                    int64_t dst_token_stride, int64_t dst_slot_stride, int64_t m, int64_t k, int64_t n_expert,
+                    int64_t n_used, int64_t n_tokens, void * workspace, size_t workspace_bytes,
+                    b200_stream_t stream_) {
+    (void) workspace, (void) workspace_bytes;
+    cudaStream_t stream = (cudaStream_t) stream_;
+    int64_t row_stride = 0;
+    int st = check_weights(type, as, row_stride, k);
+    if (st != B200_OK) return st;
+    if (m < 0 || n_expert <= 0 || n_used < 0 || n_tokens < 0 || ne11 <= 0 || ids_row_stride < n_used)
+        return B200_ERR_SHAPE;
+    if (m > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
+    if (expert_stride == 0) expert_stride = row_stride * m;
+    if (expert_stride % (type == B200_TYPE_Q4_K ? 16 : type == B200_TYPE_IQ4_XS ? 8 : 2) != 0)
+        return B200_ERR_ALIGNMENT;
+    if (m == 0 || n_used == 0 || n_tokens == 0) return B200_OK;
+    if (k == 0) {
+        for (int64_t t = 0; t < n_tokens; t++)
+            B200_CUDA_TRY(cudaMemset2DAsync(dst + t * dst_token_stride, dst_slot_stride * 4, 0, m * 4, n_used, stream));
+        return B200_OK;
+    }
+    if (gemv_max_cols(type, k) < 1) return B200_ERR_UNSUPPORTED;
+
+    gemv_args g = {};
+    g.type = type, g.W = (const uint8_t *) as, g.w_row_stride = row_stride, g.w_expert_stride = expert_stride;
+    g.x = b, g.dst = dst, g.m = m, g.k = k, g.ncols = 1, g.world = 1;
+    g.x_col_stride = k, g.dst_col_stride = m;
+    g.ids = ids, g.ids_row_stride = ids_row_stride, g.n_used = (int) n_used, g.ne11 = (int) ne11;
+    g.x_token_stride = b_token_stride, g.x_slot_stride = b_slot_stride;
+    g.dst_token_stride = dst_token_stride, g.dst_slot_stride = dst_slot_stride;
+    // grid.y is limited to 65535 pairs per launch
+    const int64_t pairs = n_tokens * n_used;
+    const int64_t tok_per_launch = 65535 / n_used > 0 ? 65535 / n_used : 1;
+    for (int64_t t0 = 0; t0 < n_tokens; t0 += tok_per_launch) {
+        const int64_t nt = n_tokens - t0 < tok_per_launch ? n_tokens - t0 : tok_per_launch;
+        g.npairs = nt * n_used;
+        g.x      = b + t0 * b_token_stride;
+        g.dst    = dst + t0 * dst_token_stride;
+        g.ids    = ids + t0 * ids_row_stride;
+        st = launch_gemv(g, stream);
+        if (st != B200_OK) return st;
+    }
+    (void) pairs;
+    return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- row split
+int b200_row_split(int64_t m, int world, int rank, const float * tensor_split, int64_t * row_low, int64_t * row_high) {
+    if (world <= 0 || rank < 0 || rank >= world || m < 0 || !row_low || !row_high) return B200_ERR_SHAPE;
+    // cumulative split points in [0,1), as ggml_backend_cuda_split_buffer_type builds them (ggml-cuda.cu:1012-1052)
+    auto frac = [&](int r) -> double {
+        if (r <= 0) return 0.0;
+        if (r >= world) return 1.0;
+        if (!tensor_split) return (double) r / world;
+        double tot = 0, acc = 0;
+        for (int i = 0; i < world; i++) tot += tensor_split[i];
+        for (int i = 0; i < r; i++) acc += tensor_split[i];
+        return tot > 0 ? acc / tot : (double) r / world;
+    };
+    const int64_t rounding = 128;  // get_row_rounding: mmq_y for every int8-MMA capable device (ggml-cuda.cu:727-738)
+    int64_t lo = rank == 0 ? 0 : (int64_t) (m * (float) frac(rank));
+    lo -= lo % rounding;
+    int64_t hi;
+    if (rank == world - 1) hi = m;
+    else { hi = (int64_t) (m * (float) frac(rank + 1)); hi -= hi % rounding; }
+    *row_low = lo, *row_high = hi;
+    return B200_OK;
+}
+
+int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64_t x_row_stride,
+                                float * const * peer_dst, int32_t * const * flags, int32_t epoch,
+                                int64_t dst_row_stride, int64_t m, int64_t row_low, int64_t row_high, int64_t n,
+                                int64_t k, int world, int rank, void * workspace, size_t workspace_bytes,
+                                b200_stream_t stream_) {
+    (void) workspace, (void) workspace_bytes;
+    cudaStream_t stream = (cudaStream_t) stream_;
+    int64_t row_stride = 0;
+    int st = check_weights(type, W, row_stride, k);
+    if (st != B200_OK) return st;
+    if (world < 1 || world > 16 || rank < 0 || rank >= world || row_low < 0 || row_high < row_low || row_high > m)
+        return B200_ERR_SHAPE;
+    if (n < 1 || n > FUSED_QUANT_MAX_COLS || k <= 0) return B200_ERR_UNSUPPORTED;
+    if (gemv_max_cols(type, k) < n) return B200_ERR_UNSUPPORTED;
+    gemv_args g = {};
+    g.type = type, g.W = (const uint8_t *) W, g.w_row_stride = row_stride;
+    g.x = x, g.x_col_stride = x_row_stride, g.dst = peer_dst[rank], g.dst_col_stride = dst_row_stride;
+    g.m = row_high - row_low, g.k = k, g.ncols = (int) n;
+    g.world = world > 1 ? world : 2, g.rank = rank, g.row_offset = row_low, g.epoch = epoch;
+    if (world == 1) {  // degenerate: plain local matmul at the row offset
+        g.world = 1;
+        g.dst   = peer_dst[0] + row_low;
+        return launch_gemv(g, stream);
+    }
+    g.world = world;
+    for (int r = 0; r < world; r++) g.peer_dst[r] = peer_dst[r], g.peer_flag[r] = flags[r];
+    return launch_gemv(g, stream);
+}
+
+int b200_ipc_get_handle(void * device_ptr, void * handle_out) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    B200_CUDA_TRY(cudaIpcGetMemHandle(&h, device_ptr));
+    memcpy(handle_out, &h, sizeof(h));
+    return B200_OK;
+}
+int b200_ipc_open_handle(const void * handle, void ** device_ptr_out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    B200_CUDA_TRY(cudaIpcOpenMemHandle(device_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return B200_OK;
+}
+int b200_ipc_close_handle(void * device_ptr) {
+    B200_CUDA_TRY(cudaIpcCloseMemHandle(device_ptr));
+    return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,47 @@
+// kernels.h -- internal launcher interface between api.cu (the C ABI) and the kernel translation units.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows,
+                              cudaStream_t stream);
+int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
+                           cudaStream_t stream);
+int launch_dequantize_f32(int type, const void * w, int64_t w_stride, float * y, int64_t k, int64_t nrows,
+                          cudaStream_t stream);
+
+// Batched-GEMV ("mmvq") problem: up to 8 activation columns against a streamed weight matrix, optionally with
+// per-(token,slot) expert indirection (MUL_MAT_ID) and with the row-split all-gather fused into the epilogue.
+struct gemv_args {
+    int            type;
+    const uint8_t * W;
+    int64_t        w_row_stride;     // bytes
+    int64_t        w_expert_stride;  // bytes (MUL_MAT_ID)
+    const float *  x;                // f32 activations (quantized in the kernel prologue) ...
+    int64_t        x_col_stride;     // elements
+    const uint8_t * xq;              // ... or activations already in the SoA q8 layout (column pitch = layout.bytes)
+    float *        dst;
+    int64_t        dst_col_stride;   // elements
+    int64_t        m, k;
+    int            ncols;            // 1..8
+    // MUL_MAT_ID (ids != nullptr): grid.y = n_tokens * n_used pairs, ncols must be 1
+    const int32_t * ids;
+    int64_t        ids_row_stride;
+    int            n_used, ne11;
+    int64_t        npairs;
+    int64_t        x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
+    // fused row-split all-gather (world > 1): dst rows are offset by row_offset and mirrored into every peer
+    int            world, rank;
+    int64_t        row_offset;
+    float *        peer_dst[16];
+    int32_t *      peer_flag[16];
+    int32_t        epoch;
+};
+size_t gemv_q8_smem_bytes(int64_t k, int ncols);
+int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring
+int    launch_gemv(const gemv_args & a, cudaStream_t stream);
+
+}  // namespace b200

@@ -1,0 +1,197 @@
+"""ctypes binding of libb200qmm.so + thin torch-pointer wrappers named after the reference interface they replace.
+
+Reference interface (paths relative to the reference tree):
+  quantize_row_q8_1_cuda      ggml/src/ggml-cuda/quantize.cu:129-141      -> quantize_row_q8_1
+  ggml_get_to_fp32_cuda(type) ggml/src/ggml-cuda/convert.cu:654           -> dequantize_row
+  ggml_cuda_mul_mat           ggml/src/ggml-cuda/ggml-cuda.cu:1877-1938   -> mul_mat
+  ggml_cuda_mul_mat_id        ggml/src/ggml-cuda/ggml-cuda.cu:1994-2130   -> mul_mat_id
+Tensor conventions are ggml's: weights [m rows][k], activations [n][k] f32, dst [n][m] f32.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libb200qmm.so")
+
+GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_Q8_1, GGML_TYPE_Q4_K, GGML_TYPE_Q6_K, GGML_TYPE_IQ4_XS = 2, 8, 9, 12, 14, 23
+TYPE_BY_NAME = {"q4_0": 2, "q8_0": 8, "q4_K": 12, "q6_K": 14, "iq4_xs": 23}
+BLOCK = {2: 32, 8: 32, 9: 32, 12: 256, 14: 256, 23: 256}
+TYPE_SIZE = {2: 18, 8: 34, 9: 36, 12: 144, 14: 210, 23: 136}
+
+EXPORTS = [
+    "b200_qmm_abi_version", "b200_status_string", "b200_last_cuda_error", "b200_device_ok", "b200_sm_count",
+    "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
+    "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
+    "b200_mul_mat", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
+    "b200_mul_mat_rowsplit_fused", "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
+]
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """Load the C-ABI library.  Fails loudly when it has not been built: there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200Error("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(make -f llama.cpp.dsp_b200/Makefile). There is no CPU fallback." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, i64, sz, i32 = C.c_void_p, C.c_int64, C.c_size_t, C.c_int
+    L.b200_qmm_abi_version.restype = i32
+    L.b200_status_string.restype = C.c_char_p
+    L.b200_status_string.argtypes = [i32]
+    L.b200_last_cuda_error.restype = C.c_char_p
+    L.b200_device_ok.argtypes = [i32]
+    L.b200_sm_count.argtypes = [i32]
+    L.b200_launch_count.restype = i64
+    L.b200_type_supported.argtypes = [i32]
+    L.b200_block_size.argtypes = [i32]
+    L.b200_type_size.restype = sz
+    L.b200_type_size.argtypes = [i32]
+    L.b200_row_size.restype = sz
+    L.b200_row_size.argtypes = [i32, i64]
+    L.b200_weight_alloc_size.restype = sz
+    L.b200_weight_alloc_size.argtypes = [i32, i64, i64]
+    L.b200_quantize_q8_1.argtypes = [vp, i64, vp, i64, i64, vp]
+    L.b200_dequantize_f32.argtypes = [i32, vp, i64, vp, i64, i64, vp]
+    L.b200_mul_mat_workspace_size.restype = sz
+    L.b200_mul_mat_workspace_size.argtypes = [i32, i64, i64, i64]
+    L.b200_mul_mat.argtypes = [i32, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
+    L.b200_mul_mat_id_workspace_size.restype = sz
+    L.b200_mul_mat_id_workspace_size.argtypes = [i32, i64, i64, i64, i64, i64]
+    L.b200_mul_mat_id.argtypes = [i32, vp, i64, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp,
+                                  sz, vp]
+    L.b200_row_split.argtypes = [i64, i32, i32, vp, C.POINTER(i64), C.POINTER(i64)]
+    L.b200_mul_mat_rowsplit_fused.argtypes = [i32, vp, vp, i64, vp, vp, i32, i64, i64, i64, i64, i64, i64, i32, i32,
+                                              vp, sz, vp]
+    L.b200_ipc_get_handle.argtypes = [vp, vp]
+    L.b200_ipc_open_handle.argtypes = [vp, C.POINTER(vp)]
+    L.b200_ipc_close_handle.argtypes = [vp]
+    _lib = L
+    return L
+
+
+def check(status):
+    if status != 0:
+        L = lib()
+        msg = L.b200_status_string(status).decode()
+        if status in (5, 6):
+            msg += ": " + L.b200_last_cuda_error().decode()
+        raise B200Error("b200_qmm: %s (status %d)" % (msg, status))
+
+
+def row_size(t, k):
+    return k // BLOCK[t] * TYPE_SIZE[t]
+
+
+def launch_count():
+    return int(lib().b200_launch_count())
+
+
+def row_split(m, world, rank, tensor_split=None):
+    lo, hi = C.c_int64(), C.c_int64()
+    ts = None
+    if tensor_split is not None:
+        ts = (C.c_float * world)(*tensor_split)
+    check(lib().b200_row_split(m, world, rank, ts, C.byref(lo), C.byref(hi)))
+    return lo.value, hi.value
+
+
+# ---- torch-pointer wrappers (torch is device-memory plumbing only) -------------------------------------------------
+
+def _stream_ptr(stream=None):
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B200Error("b200_qmm operates on CUDA tensors only (no CPU fallback)")
+
+
+def quantize_row_q8_1(x, stream=None):
+    """x: [nrows, k] f32 cuda (last dim contiguous) -> uint8 [nrows, k/32*36] ggml block_q8_1 bytes"""
+    import torch
+    _require_cuda(x)
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    nrows, k = x.shape
+    y = torch.empty((nrows, k // 32 * 36), dtype=torch.uint8, device=x.device)
+    check(lib().b200_quantize_q8_1(x.data_ptr(), x.stride(0) if nrows > 1 else k, y.data_ptr(), k, nrows,
+                                   _stream_ptr(stream)))
+    return y
+
+
+def dequantize_row(t, w, k, stream=None):
+    """w: uint8 [nrows, row_size] cuda -> f32 [nrows, k]"""
+    import torch
+    _require_cuda(w)
+    assert w.dtype == torch.uint8 and w.dim() == 2 and w.stride(1) == 1
+    nrows = w.shape[0]
+    y = torch.empty((nrows, k), dtype=torch.float32, device=w.device)
+    check(lib().b200_dequantize_f32(t, w.data_ptr(), w.stride(0) if nrows > 1 else 0, y.data_ptr(), k, nrows,
+                                    _stream_ptr(stream)))
+    return y
+
+
+class Workspace:
+    """grow-only device scratch owned by the caller (the ggml plug-in keeps one per backend stream)"""
+
+    def __init__(self, device):
+        self.device = device
+        self.buf = None
+
+    def get(self, nbytes):
+        import torch
+        if nbytes == 0:
+            return None, 0
+        if self.buf is None or self.buf.numel() < nbytes:
+            self.buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
+        return self.buf.data_ptr(), self.buf.numel()
+
+
+_ws = {}
+
+
+def _workspace(device, nbytes):
+    key = str(device)
+    if key not in _ws:
+        _ws[key] = Workspace(device)
+    return _ws[key].get(nbytes)
+
+
+def mul_mat(t, w, x, m, k, out=None, stream=None):
+    """w: uint8 cuda holding m rows (packed); x: [n, k] f32 cuda; returns dst [n, m] f32"""
+    import torch
+    _require_cuda(w, x)
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] == k
+    n = x.shape[0]
+    dst = out if out is not None else torch.empty((n, m), dtype=torch.float32, device=x.device)
+    ws, wsz = _workspace(x.device, lib().b200_mul_mat_workspace_size(t, m, n, k))
+    check(lib().b200_mul_mat(t, w.data_ptr(), 0, x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
+                             dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
+    return dst
+
+
+def mul_mat_id(t, w, b, ids, m, k, n_expert, out=None, stream=None):
+    """w: uint8 cuda, n_expert*m rows; b: [n_tokens, ne11, k] f32; ids: [n_tokens, n_used] int32 (row stride free)
+    returns dst [n_tokens, n_used, m]"""
+    import torch
+    _require_cuda(w, b, ids)
+    assert b.dtype == torch.float32 and b.dim() == 3 and b.stride(2) == 1
+    assert ids.dtype == torch.int32 and ids.dim() == 2 and ids.stride(1) == 1
+    n_tokens, ne11, _ = b.shape
+    n_used = ids.shape[1]
+    dst = out if out is not None else torch.empty((n_tokens, n_used, m), dtype=torch.float32, device=b.device)
+    check(lib().b200_mul_mat_id(t, w.data_ptr(), 0, b.data_ptr(), b.stride(0), b.stride(1), ne11, ids.data_ptr(),
+                                ids.stride(0), dst.data_ptr(), dst.stride(0), dst.stride(1), m, k, n_expert, n_used,
+                                n_tokens, None, 0, _stream_ptr(stream)))
+    return dst

@@ -467,7 +467,10 @@ static double dot_q8_1(int type, int64_t k, const void * w, const blk_q8_1 * y) 
                 int sumi = 0;
                 for (int j = 0; j < QK / 2; j++)
                     sumi += (x[ib].qs[j] & 0xF) * y[ib].qs[j] + (x[ib].qs[j] >> 4) * y[ib].qs[j + QK / 2];
-                acc += (double) F16(x[ib].d) * ((double) sumi * F16(y[ib].d) - 8.0 * F16(y[ib].s));
+                int ysum = 0;
+                for (int j = 0; j < QK; j++) ysum += y[ib].qs[j];
+                /* s = d*sum(qs) taken before its fp16 rounding (the device keeps it in f32) */
+                acc += (double) F16(x[ib].d) * F16(y[ib].d) * ((double) sumi - 8.0 * ysum);
             }
         } break;
         case QREF_TYPE_Q8_0: { /* vecdotq.cuh:151-163 */
@@ -489,8 +492,10 @@ static double dot_q8_1(int type, int64_t k, const void * w, const blk_q8_1 * y) 
                     const uint8_t *  q  = x[i].qs + 32 * (sb / 2);
                     int dot = 0;
                     for (int l = 0; l < 32; l++) dot += ((sb & 1) ? (q[l] >> 4) : (q[l] & 0xF)) * yb->qs[l];
+                    int ysum = 0;
+                    for (int l = 0; l < 32; l++) ysum += yb->qs[l];
                     sd += (double) F16(yb->d) * sc * dot;
-                    sm += (double) F16(yb->s) * mn;
+                    sm += (double) F16(yb->d) * ysum * mn;   /* s before its fp16 rounding */
                 }
                 acc += (double) F16(x[i].d) * sd - (double) F16(x[i].dmin) * sm;
             }

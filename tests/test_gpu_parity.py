@@ -1,0 +1,207 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (ctypes), against the oracle on the same seeded
+inputs, against the committed golden vectors, and -- at BASELINE sizes -- through size-independent properties.
+Bars: bit-exact for quantize / dequantize; NMSE <= 5e-4 vs the ggml-cpu semantics (tests/test-backend-ops.cpp:1990)
+plus a tight bound vs the q8_1-semantics oracle (catches bit-decoding bugs the loose bound would hide)."""
+import numpy as np
+import pytest
+
+import qref
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+NMSE_HARNESS = 5e-4   # max_nmse_err for MUL_MAT / MUL_MAT_ID in the reference harness
+NMSE_TIGHT = 1e-9     # fp32-vs-double accumulation noise only
+
+
+@pytest.fixture(scope="module")
+def qmm():
+    import b200pkg
+    q = b200pkg.load()
+    assert torch.cuda.is_available(), "these tests need the B200"
+    assert q.lib().b200_device_ok(torch.cuda.current_device()) == 1
+    return q
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+TYPES = list(qref.WEIGHT_TYPES.items())
+
+
+# ------------------------------------------------------------------------------------------------ quantize_q8_1
+def test_quantize_q8_1_golden_bit_exact(qmm, golden):
+    x = golden["act_x"]
+    got = qmm.quantize_row_q8_1(dev(x)).cpu().numpy()
+    assert np.array_equal(got, golden["act_q8_1"])
+
+
+@pytest.mark.parametrize("k", [32, 64, 96, 4096, 4096 + 32, 14336])
+def test_quantize_q8_1_vs_oracle(qmm, k):
+    rng = np.random.default_rng(k)
+    nrows = 5
+    x = (rng.normal(0, 1, (nrows, k)) * rng.choice([1e-4, 1.0, 300.0], (nrows, 1))).astype(np.float32)
+    x[1, :32] = 0
+    got = qmm.quantize_row_q8_1(dev(x)).cpu().numpy()
+    assert np.array_equal(got, qref.quantize(qref.Q8_1, x))
+
+
+def test_quantize_q8_1_strided_unaligned_rows(qmm):
+    rng = np.random.default_rng(1)
+    big = rng.normal(0, 1, (7, 200)).astype(np.float32)
+    xb = dev(big)
+    view = xb[:, 3:3 + 160]                       # row stride 200, base offset 12 bytes: scalar-load path
+    got = qmm.quantize_row_q8_1(view).cpu().numpy()
+    assert np.array_equal(got, qref.quantize(qref.Q8_1, big[:, 3:163]))
+
+
+def test_quantize_empty(qmm):
+    x = torch.empty((0, 64), dtype=torch.float32, device="cuda")
+    assert qmm.quantize_row_q8_1(x).shape == (0, 72)
+
+
+# ------------------------------------------------------------------------------------------------ dequantize
+@pytest.mark.parametrize("name,t", TYPES)
+def test_dequantize_golden_bit_exact(qmm, golden, name, t):
+    w = golden["w_" + name]
+    want = golden["deq_" + name]
+    got = qmm.dequantize_row(t, dev(w), want.shape[1]).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("name,t", TYPES)
+def test_dequantize_random_bit_patterns(qmm, name, t):
+    rng = np.random.default_rng(17)
+    k = 1024
+    w = qref.random_blocks(t, 40, k, rng)
+    got = qmm.dequantize_row(t, dev(w), k).cpu().numpy()
+    want = qref.dequantize(t, w, k)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+# ------------------------------------------------------------------------------------------------ MUL_MAT
+def check_mul_mat(qmm, t, w, x, m, k):
+    got = qmm.mul_mat(t, dev(w), dev(x), m, k)
+    torch.cuda.synchronize()
+    got = got.cpu().numpy()
+    assert np.isfinite(got).all()
+    tight = qref.mul_mat(t, w, x, m, k, "q8_1")
+    cpu = qref.mul_mat(t, w, x, m, k, "cpu")
+    assert qref.nmse(tight, got) < NMSE_TIGHT, ("tight", qref.nmse(tight, got))
+    assert qref.nmse(cpu, got) < NMSE_HARNESS, ("harness", qref.nmse(cpu, got))
+    return got
+
+
+@pytest.mark.parametrize("name,t", TYPES)
+def test_mul_mat_golden(qmm, golden, name, t):
+    w, x = golden["w_" + name], golden["mm_x"]
+    got = check_mul_mat(qmm, t, w, x, w.shape[0], x.shape[1])
+    assert qref.nmse(golden["mm_cpu_" + name], got) < NMSE_HARNESS
+
+
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 8, 9, 17])
+def test_mul_mat_small_harness_shapes(qmm, name, t, n):
+    # the reference harness' eval shapes: m=16, k=256, n=1..9 (tests/test-backend-ops.cpp:4143-4147)
+    rng = np.random.default_rng(100 + n)
+    m, k = 16, 256
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    check_mul_mat(qmm, t, w, x, m, k)
+
+
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("m,k", [(1, 256), (33, 512), (257, 1024 + 256), (1000, 4096), (300, 14336)])
+def test_mul_mat_ragged_rows(qmm, name, t, m, k):
+    rng = np.random.default_rng(m * 7 + k)
+    w = qref.random_blocks(t, m, k, rng)
+    for n in (1, 3):
+        x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+        check_mul_mat(qmm, t, w, x, m, k)
+
+
+@pytest.mark.parametrize("name,t", [("q4_0", qref.Q4_0), ("q8_0", qref.Q8_0)])
+def test_mul_mat_k_of_one_block(qmm, name, t):
+    rng = np.random.default_rng(5)
+    for k in (32, 96):
+        w = qref.random_blocks(t, 16, k, rng)
+        x = rng.uniform(-1, 1, (1, k)).astype(np.float32)
+        check_mul_mat(qmm, t, w, x, 16, k)
+
+
+def test_mul_mat_empty_and_bad_args(qmm):
+    w = torch.zeros(144 * 4, dtype=torch.uint8, device="cuda")
+    x = torch.zeros((0, 256), dtype=torch.float32, device="cuda")
+    assert qmm.mul_mat(qref.Q4_K, w, x, 4, 256).shape == (0, 4)
+    with pytest.raises(qmm.B200Error):
+        qmm.mul_mat(7, w, torch.zeros((1, 256), device="cuda"), 4, 256)            # Q5_1: not on the path
+    with pytest.raises(qmm.B200Error):
+        qmm.mul_mat(qref.Q4_K, w, torch.zeros((1, 128), device="cuda"), 4, 128)    # k % 256 != 0
+    with pytest.raises(qmm.B200Error):
+        qmm.mul_mat(qref.Q4_K, w, torch.zeros((1, 256)), 4, 256)                   # host tensor: no CPU fallback
+
+
+@pytest.mark.parametrize("name,t", TYPES)
+def test_mul_mat_realistic_quantized_weights_vs_exact(qmm, name, t):
+    # weights that went through a real quantizer (golden) replicated to a larger matrix; vs the exact f64 product
+    rng = np.random.default_rng(9)
+    m, k, n = 512, 4096, 2
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.normal(0, 1, (n, k)).astype(np.float32)
+    got = qmm.mul_mat(t, dev(w), dev(x), m, k).cpu().numpy()
+    exact = qref.mul_mat(t, w, x, m, k, "f64")
+    assert qref.nmse(exact, got) < NMSE_HARNESS
+
+
+# ------------------------------------------------------------------------------------------------ full-size properties
+@pytest.mark.parametrize("name,t", TYPES)
+def test_full_size_properties(qmm, name, t):
+    """BASELINE size (m=4096, k=14336; tests/test-backend-ops.cpp:4514-4520): too slow for the scalar oracle on every
+    row, so check (a) a sampled set of rows against the oracle, (b) exact power-of-two homogeneity, (c) zero input,
+    (d) an independent device path: bit-exact dequantize + fp64 matmul."""
+    rng = np.random.default_rng(42)
+    m, k = 4096, 14336
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (1, k)).astype(np.float32)
+    wd, xd = dev(w), dev(x)
+    got = qmm.mul_mat(t, wd, xd, m, k)
+    rows = rng.choice(m, 64, replace=False)
+    want = qref.mul_mat(t, w[rows], x, len(rows), k, "q8_1")
+    assert qref.nmse(want, got.cpu().numpy()[:, rows]) < NMSE_TIGHT
+    twice = qmm.mul_mat(t, wd, xd * 2.0, m, k)
+    assert torch.equal(twice, got * 2.0)
+    zero = qmm.mul_mat(t, wd, torch.zeros_like(xd), m, k)
+    assert torch.count_nonzero(zero) == 0
+    deq = qmm.dequantize_row(t, wd, k).double()
+    ref = (deq @ xd.double().T).T.float()
+    assert qref.nmse(ref.cpu().numpy(), got.cpu().numpy()) < NMSE_HARNESS
+
+
+# ------------------------------------------------------------------------------------------------ MUL_MAT_ID
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("n_expert,n_used,n_tokens,bcast", [(4, 1, 1, False), (4, 2, 5, True), (8, 4, 3, False),
+                                                            (8, 2, 32, True), (4, 4, 129, False)])
+def test_mul_mat_id(qmm, name, t, n_expert, n_used, n_tokens, bcast):
+    # shapes of the harness' MUL_MAT_ID cases (tests/test-backend-ops.cpp:4240-4270), smaller m
+    rng = np.random.default_rng(n_expert * 100 + n_used * 10 + n_tokens)
+    m, k = 64, 256
+    ne11 = 1 if bcast else n_used
+    w = qref.random_blocks(t, n_expert * m, k, rng)
+    b = rng.uniform(-1, 1, (n_tokens, ne11, k)).astype(np.float32)
+    # ids is a VIEW of a wider tensor when n_used < n_expert (test-backend-ops.cpp:2105-2110): row stride n_expert
+    ids_full = np.stack([rng.permutation(n_expert) for _ in range(n_tokens)]).astype(np.int32)
+    ids_dev = dev(ids_full)[:, :n_used]
+    got = qmm.mul_mat_id(t, dev(w), dev(b), ids_dev, m, k, n_expert).cpu().numpy()
+    ids = ids_full[:, :n_used]
+    tight = qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "q8_1")
+    cpu = qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "cpu")
+    assert qref.nmse(tight, got) < NMSE_TIGHT
+    assert qref.nmse(cpu, got) < NMSE_HARNESS
+
+
+def test_launch_counter_counts_kernels(qmm):
+    before = qmm.launch_count()
+    w = torch.zeros(144 * 16, dtype=torch.uint8, device="cuda")
+    qmm.mul_mat(qref.Q4_K, w, torch.ones((1, 256), device="cuda"), 16, 256)
+    assert qmm.launch_count() == before + 1      # n=1: quantize is fused into the GEMV, one launch per matmul
