@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -120,13 +121,21 @@ int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * 
 }
 
 // ---------------------------------------------------------------------------------------------------------- MUL_MAT
-// n <= 2 : one fused launch (quantize in the GEMV prologue).
-// n  > 2 : quantize all columns once into the workspace (SoA q8_1), then GEMV launches of up to 8 columns.
-static const int FUSED_QUANT_MAX_COLS = 2;
+// Activation quantization policy (measured trade-off):
+//  * fused   : every lane of the GEMV quantizes its own 64-element unit from f32 in registers -- one launch per
+//              matmul, but each CTA re-reads the f32 row from L2 (2 * #SM * k * 4 bytes of L2 traffic).
+//  * separate: one small kernel writes the SoA q8_1 row(s) to the workspace, the GEMV loads 1/4 of the bytes.
+// Fused is used for a single column with k <= FUSED_QUANT_MAX_K; everything else is pre-quantized once and then
+// consumed by GEMV launches of up to 4 columns each.
+static int fused_quant_max_k() {
+    const char * e = getenv("B200_FUSED_QUANT_MAX_K");
+    return e && *e ? atoi(e) : 8192;
+}
+static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
 
 size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     (void) m;
-    if (!weight_type(type) || k <= 0 || n <= FUSED_QUANT_MAX_COLS) return 0;
+    if (!weight_type(type) || k <= 0 || n <= 0 || use_fused_quant(n, k)) return 0;
     return (size_t) n * q8_soa_layout(k).bytes;
 }
 
@@ -152,8 +161,8 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
     g.m = m, g.k = k, g.dst_col_stride = dst_row_stride, g.x_col_stride = x_row_stride;
     g.world = 1;
 
-    if (n <= FUSED_QUANT_MAX_COLS && n <= maxc) {
-        g.x = x, g.dst = dst, g.ncols = (int) n;
+    if (use_fused_quant(n, k)) {
+        g.x = x, g.dst = dst, g.ncols = 1;
         return launch_gemv(g, stream);
     }
     const q8_layout L = q8_soa_layout(k);
@@ -260,7 +269,7 @@ int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64
     if (st != B200_OK) return st;
     if (world < 1 || world > 16 || rank < 0 || rank >= world || row_low < 0 || row_high < row_low || row_high > m)
         return B200_ERR_SHAPE;
-    if (n < 1 || n > FUSED_QUANT_MAX_COLS || k <= 0) return B200_ERR_UNSUPPORTED;
+    if (n != 1 || k <= 0) return B200_ERR_UNSUPPORTED;
     if (gemv_max_cols(type, k) < n) return B200_ERR_UNSUPPORTED;
     gemv_args g = {};
     g.type = type, g.W = (const uint8_t *) W, g.w_row_stride = row_stride;

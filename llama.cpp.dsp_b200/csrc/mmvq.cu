@@ -1,4 +1,4 @@
-// mmvq.cu -- batch 1..8 quantized GEMV for sm_100a: the decode hot path.
+// mmvq.cu -- batch 1..4 quantized GEMV for sm_100a: the decode hot path.
 //
 // Replaces (reference): mul_mat_vec_q<type,ncols_y> + vec_dot_*_q8_1 + quantize_q8_1 as used by
 // ggml_cuda_op_mul_mat_vec_q (ggml/src/ggml-cuda/mmvq.cu:130-206,423-511; vecdotq.cuh:23-42,151-163,357-380,476-497,
@@ -6,15 +6,20 @@
 // ggml_cuda_mul_mat_id (ggml-cuda.cu:1994-2130).
 //
 // Design (B200-first, not a port):
-//  * HBM-bound streaming.  Every warp owns a contiguous range of weight rows, i.e. one contiguous byte stream, and
-//    pulls it through its PRIVATE ring of shared-memory slots with 1-D bulk TMA copies (cp.async.bulk, SASS UBLKCP)
-//    completing on per-slot mbarriers.  No block-wide synchronisation in the main loop, NW*NST slots (~100 KB/SM) in
-//    flight, raw ggml block bytes (18/34/144/210/136-byte blocks) re-sliced from shared memory.
-//  * One launch per matmul: the f32 activation row is quantized to q8_1 in the prologue by the same routine the
-//    standalone quantizer uses (actquant.cuh), into shared memory, while the first weight slots are already in flight.
-//  * Programmatic dependent launch: weight prefetch is issued BEFORE griddepcontrol.wait (weights never depend on
-//    the previous kernel), so back-to-back matmuls of a decode step overlap their ramp-up with the predecessor's tail.
-//  * int8 dot products with dp4a, fp32 scale math, warp-shuffle reduction, one deterministic writer per output.
+//  * HBM-bound streaming.  A CTA owns a contiguous slab of weight rows and pulls it through a ring of shared-memory
+//    stages (R whole rows, ~32 KB each) with 1-D bulk TMA copies (cp.async.bulk, SASS UBLKCP) that complete on
+//    per-stage "full" mbarriers; compute warps release a stage through an "empty" mbarrier.  Raw ggml block bytes
+//    (18/34/144/210/136-byte blocks) are re-sliced out of shared memory; nothing is repacked.
+//  * k is split ACROSS WARPS, rows across lane groups: every lane owns one fixed 64-element unit of k for the whole
+//    kernel, so its q8_1 activations live in REGISTERS (16 words + scales) and shared-memory traffic is weights only.
+//    Activations are quantized in-lane (each lane holds whole 32-blocks: no shuffles, no shared memory, no barrier)
+//    with exactly the arithmetic of the standalone quantizer (actquant.cuh), or loaded pre-quantized for large k.
+//  * Warp roles: NWC compute warps + 1 producer/epilogue warp (issues TMA, then sums the per-warp partials of a
+//    finished stage in a fixed order -> deterministic results, one writer per output).
+//  * <= 112 KB of shared memory and <= 112 registers per thread: two CTAs per SM, so that under programmatic
+//    dependent launch the next matmul's CTAs become resident and prefetch their weights (issued BEFORE
+//    griddepcontrol.wait; weights never depend on the previous kernel) while this one drains.
+//  * int8 dot products with dp4a, fp32 scale math.
 #include "actquant.cuh"
 #include "kernels.h"
 
@@ -22,169 +27,165 @@
 
 namespace b200 {
 
-// blocks per ring slot ("segment"): ~4.5 KB of weights, never crossing a row
-template <int TYPE> struct seg_cfg;
-template <> struct seg_cfg<B200_TYPE_Q4_0>   { static constexpr int blocks = 256; };  // 4608 B, 8192 weights
-template <> struct seg_cfg<B200_TYPE_Q8_0>   { static constexpr int blocks = 128; };  // 4352 B, 4096 weights
-template <> struct seg_cfg<B200_TYPE_Q4_K>   { static constexpr int blocks = 32;  };  // 4608 B, 8192 weights
-template <> struct seg_cfg<B200_TYPE_Q6_K>   { static constexpr int blocks = 16;  };  // 3360 B, 4096 weights
-template <> struct seg_cfg<B200_TYPE_IQ4_XS> { static constexpr int blocks = 32;  };  // 4352 B, 8192 weights
-
-template <int TYPE> __host__ __device__ constexpr int slot_bytes() {
-    // payload + up to 15 bytes of leading misalignment, rounded to 16, + 16 bytes so that word-granular reads of a
-    // 2-byte-aligned tail stay inside the slot
-    return ((seg_cfg<TYPE>::blocks * qtraits<TYPE>::bytes + 15 + 15) & ~15) + 16;
-}
-
 __device__ __forceinline__ int dp4a(uint32_t a, uint32_t b, int c) { return __dp4a((int) a, (int) b, c); }
 
-// q8 activations in shared memory
-struct q8_smem {
-    uint32_t qs, ds, s16;  // shared-space addresses of the three sections of column 0
-    uint32_t pitch;        // bytes between columns
+// ------------------------------------------------------------------------------------------------ q8_1 unit in registers
+// One unit = 64 consecutive weights of a row as the weight format groups them:
+//   Q4_K / IQ4_XS / Q4_0 / Q8_0 : two whole 32-blocks (elements 64u .. 64u+63)
+//   Q6_K                        : four 16-element groups, elements 256b + 128h + 32j + l0 + [0,16), j = 0..3
+struct q8_unit {
+    uint32_t q[16];  // int8 x 64
+    float    d[4];   // block scales (fp16-rounded): [0..1] for two-block types, [0..3] for Q6_K
+    float    s[4];   // two-block types: d * sum(q) per block; Q6_K: 32 * sum(q) of the 16-group, as float
 };
 
-// ------------------------------------------------------------------------------------------------ per-type segment dots
-// Each accumulates, into acc[c], this lane's share of  sum_k W[row][k] * X[c][k]  over the `nb` blocks of the segment
-// that starts at shared address `seg`; `kb0` is the index of the segment's first block inside the row.
+__device__ __forceinline__ int q8_round(float v) { return (int) roundf(v); }
 
-template <int NCOLS>
-__device__ __forceinline__ void seg_dot_q4_K(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane, float * acc) {
-    for (int u = lane; u < nb * 4; u += 32) {
-        const int      b = u >> 2, j = u & 3;
-        const uint32_t blk = seg + b * 144;
-        const uint4    hdr = lds128(blk);                       // d | dmin<<16, scales[12]
-        const float    d = half_bits_to_float(hdr.x & 0xffff), dmin = half_bits_to_float(hdr.x >> 16);
-        const uint32_t sh = (j & 1) * 16;
-        const uint32_t sa = (hdr.y >> sh) & 0xffff, sb = (hdr.z >> sh) & 0xffff, sc = (hdr.w >> sh) & 0xffff;
-        // 6-bit scales / mins of sub-blocks 2j, 2j+1 (reference get_scale_min_k4, ggml-quants.c:631-639)
-        const uint32_t sc2 = j < 2 ? (sa & 0x3f3f) : ((sc & 0x0f0f) | ((sa >> 2) & 0x3030));
-        const uint32_t mn2 = j < 2 ? (sb & 0x3f3f) : (((sc >> 4) & 0x0f0f) | ((sb >> 2) & 0x3030));
-        const float sc0 = (float) (sc2 & 0xff), sc1 = (float) (sc2 >> 8);
-        const float mn0 = (float) (mn2 & 0xff), mn1 = (float) (mn2 >> 8);
-        const uint4 v0 = lds128(blk + 16 + 32 * j), v1 = lds128(blk + 32 + 32 * j);
-        const uint32_t v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-        const int sbg = (kb0 + b) * 8 + 2 * j;                  // q8 block of sub-block 2j
+// quantize 32 floats held by this lane; returns the fp16-rounded scale, packs to q[0..7]; *isum = sum of the int8s
+template <bool INTERLEAVE>
+__device__ __forceinline__ float quant32_inlane(const float * v, uint32_t * q, int * isum) {
+    float amax = 0.f;
 #pragma unroll
-        for (int c = 0; c < NCOLS; c++) {
-            const uint32_t qa = q.qs + c * q.pitch + sbg * 32;
-            const uint4 a0 = lds128(qa), a1 = lds128(qa + 16), b0 = lds128(qa + 32), b1 = lds128(qa + 48);
-            const uint4 dd = lds128(q.ds + c * q.pitch + sbg * 8);   // d(2j), d*sum(2j), d(2j+1), d*sum(2j+1)
-            const uint32_t ua[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t ub[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            int dot0 = 0, dot1 = 0;
+    for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(v[i]));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    int qi[32];
+    int sum = 0;
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                dot0 = dp4a(v[i] & 0x0F0F0F0Fu, ua[i], dot0);
-                dot1 = dp4a((v[i] >> 4) & 0x0F0F0F0Fu, ub[i], dot1);
+    for (int i = 0; i < 32; i++) {
+        qi[i] = q8_round(__fmul_rn(v[i], id));
+        sum += qi[i];
+    }
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        int a, b, c, e;
+        if (INTERLEAVE) { a = qi[2 * w], b = qi[16 + 2 * w], c = qi[2 * w + 1], e = qi[16 + 2 * w + 1]; }
+        else            { a = qi[4 * w], b = qi[4 * w + 1], c = qi[4 * w + 2], e = qi[4 * w + 3]; }
+        q[w] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (c & 0xff) << 16) |
+               ((uint32_t) (e & 0xff) << 24);
+    }
+    *isum = sum;
+    return __half2float(__float2half_rn(d));
+}
+
+__device__ __forceinline__ void load32(const float * p, float * v, bool vec) {
+    if (vec) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const float4 t = __ldg(reinterpret_cast<const float4 *>(p) + i);
+            v[4 * i] = t.x, v[4 * i + 1] = t.y, v[4 * i + 2] = t.z, v[4 * i + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = __ldg(p + i);
+    }
+}
+
+// Build this lane's unit from f32 activations.  `ug` = unit index in the row, k = row length.
+template <int TYPE>
+__device__ __forceinline__ void make_unit_f32(q8_unit & u, const float * __restrict__ x, int k, int ug, bool vec) {
+    if (TYPE == B200_TYPE_Q6_K) {
+        // groups j = 0..3 are the 16 elements at 256b + 128h + 32j + l0; the other half of each 32-block is held by
+        // the neighbouring lane (ug ^ 1), which is always valid because k % 256 == 0
+        const int base = (ug >> 2) * 256 + ((ug >> 1) & 1) * 128 + (ug & 1) * 16;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float v[16];
+            const float * p = x + base + 32 * j;
+            if (vec) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const float4 t = __ldg(reinterpret_cast<const float4 *>(p) + i);
+                    v[4 * i] = t.x, v[4 * i + 1] = t.y, v[4 * i + 2] = t.z, v[4 * i + 3] = t.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; i++) v[i] = __ldg(p + i);
             }
-            const float s = __uint_as_float(dd.x) * sc0 * (float) dot0 + __uint_as_float(dd.z) * sc1 * (float) dot1;
-            const float t = __uint_as_float(dd.y) * mn0 + __uint_as_float(dd.w) * mn1;
-            acc[c] += d * s - dmin * t;
+            float amax = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(v[i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            const float d  = __fdiv_rn(amax, 127.0f);
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            int sum = 0;
+#pragma unroll
+            for (int w = 0; w < 4; w++) {
+                const int a = q8_round(__fmul_rn(v[4 * w], id)), b = q8_round(__fmul_rn(v[4 * w + 1], id));
+                const int c = q8_round(__fmul_rn(v[4 * w + 2], id)), e = q8_round(__fmul_rn(v[4 * w + 3], id));
+                sum += a + b + c + e;
+                u.q[4 * j + w] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (c & 0xff) << 16) |
+                                 ((uint32_t) (e & 0xff) << 24);
+            }
+            u.d[j] = __half2float(__float2half_rn(d));
+            u.s[j] = (float) (32 * sum);
+        }
+    } else {
+        const int nblk = k / 32;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int b = 2 * ug + h;
+            if (b < nblk) {
+                float v[32];
+                load32(x + (int64_t) b * 32, v, vec);
+                int isum;
+                u.d[h] = quant32_inlane<TYPE == B200_TYPE_IQ4_XS>(v, u.q + 8 * h, &isum);
+                u.s[h] = u.d[h] * (float) isum;
+            } else {  // k % 64 == 32 (Q4_0 / Q8_0 only): the unit's second block does not exist
+#pragma unroll
+                for (int i = 0; i < 8; i++) u.q[8 * h + i] = 0;
+                u.d[h] = 0.f, u.s[h] = 0.f;
+            }
         }
     }
 }
 
-// codebook lookup of four 4-bit indices (the low 16 bits of h): two 8-entry prmt lookups + a prmt select on bit 3
+// Build the unit from activations already quantized into the SoA layout (actquant.cuh) in global memory.
+template <int TYPE>
+__device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __restrict__ xq, q8_layout L, int k, int ug) {
+    const float2 * ds  = reinterpret_cast<const float2 *>(xq + L.off_ds);
+    const short2 * s16 = reinterpret_cast<const short2 *>(xq + L.off_s16);
+    if (TYPE == B200_TYPE_Q6_K) {
+        const int b32 = (ug >> 2) * 8 + ((ug >> 1) & 1) * 4, l0 = (ug & 1) * 16;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint4 t = __ldg(reinterpret_cast<const uint4 *>(xq + (b32 + j) * 32 + l0));
+            u.q[4 * j] = t.x, u.q[4 * j + 1] = t.y, u.q[4 * j + 2] = t.z, u.q[4 * j + 3] = t.w;
+            u.d[j] = __ldg(&ds[b32 + j]).x;
+            const short2 ss = __ldg(&s16[b32 + j]);
+            u.s[j] = (float) (32 * (int) (l0 ? ss.y : ss.x));
+        }
+    } else {
+        const int nblk = k / 32;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int b = 2 * ug + h;
+            if (b < nblk) {
+                const uint4 t0 = __ldg(reinterpret_cast<const uint4 *>(xq + b * 32));
+                const uint4 t1 = __ldg(reinterpret_cast<const uint4 *>(xq + b * 32 + 16));
+                u.q[8 * h] = t0.x, u.q[8 * h + 1] = t0.y, u.q[8 * h + 2] = t0.z, u.q[8 * h + 3] = t0.w;
+                u.q[8 * h + 4] = t1.x, u.q[8 * h + 5] = t1.y, u.q[8 * h + 6] = t1.z, u.q[8 * h + 7] = t1.w;
+                const float2 dd = __ldg(&ds[b]);
+                u.d[h] = dd.x, u.s[h] = dd.y;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) u.q[8 * h + i] = 0;
+                u.d[h] = 0.f, u.s[h] = 0.f;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ per-type unit dots
+// `row` = shared address of the row's first block, `ug` = this lane's unit, `k32` = number of 32-blocks in the row.
+// Weight bytes are decoded ONCE per unit and dotted with every activation column.
+
 __device__ __forceinline__ uint32_t iq4nl_lookup4(uint32_t h) {
+    // four 4-bit codebook indices (low 16 bits of h): two 8-entry prmt lookups + a prmt select on index bit 3
     const uint32_t sel = h & 0x7777u;
     const uint32_t lo  = __byte_perm(IQ4NL_T0, IQ4NL_T1, sel);
     const uint32_t hi  = __byte_perm(IQ4NL_T2, IQ4NL_T3, sel);
     return __byte_perm(lo, hi, ((h >> 1) & 0x4444u) | 0x3210u);
-}
-
-template <int NCOLS>
-__device__ __forceinline__ void seg_dot_iq4_xs(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane,
-                                               float * acc) {
-    for (int u = lane; u < nb * 4; u += 32) {
-        const int      b = u >> 2, j = u & 3;
-        const uint32_t blk = seg + b * 136;
-        const uint2    hdr = lds64(blk);                        // d | scales_h<<16, scales_l[4]
-        const float    d  = half_bits_to_float(hdr.x & 0xffff);
-        const uint32_t sh = hdr.x >> 16, sl = (hdr.y >> (8 * j)) & 0xff;
-        const int ls0 = (int) ((sl & 0xf) | (((sh >> (4 * j)) & 3) << 4)) - 32;
-        const int ls1 = (int) ((sl >> 4) | (((sh >> (4 * j + 2)) & 3) << 4)) - 32;
-        const uint32_t qa = blk + 8 + 32 * j;                   // 32 bytes: sub-blocks 2j and 2j+1
-        const uint2 w0 = lds64(qa), w1 = lds64(qa + 8), w2 = lds64(qa + 16), w3 = lds64(qa + 24);
-        const uint32_t w[8] = {w0.x, w0.y, w1.x, w1.y, w2.x, w2.y, w3.x, w3.y};
-        uint32_t t[16];  // decoded int8 weights in nibble order: (j, j+16) pairs, matching the interleaved q8 layout
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            t[2 * i]     = iq4nl_lookup4(w[i]);
-            t[2 * i + 1] = iq4nl_lookup4(w[i] >> 16);
-        }
-        const int sbg = (kb0 + b) * 8 + 2 * j;
-#pragma unroll
-        for (int c = 0; c < NCOLS; c++) {
-            const uint32_t ya = q.qs + c * q.pitch + sbg * 32;
-            const uint4 a0 = lds128(ya), a1 = lds128(ya + 16), b0 = lds128(ya + 32), b1 = lds128(ya + 48);
-            const uint4 dd = lds128(q.ds + c * q.pitch + sbg * 8);
-            const uint32_t ua[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t ub[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            int dot0 = 0, dot1 = 0;
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                dot0 = dp4a(t[i], ua[i], dot0);
-                dot1 = dp4a(t[8 + i], ub[i], dot1);
-            }
-            acc[c] += d * (__uint_as_float(dd.x) * (float) (ls0 * dot0) + __uint_as_float(dd.z) * (float) (ls1 * dot1));
-        }
-    }
-}
-
-template <int NCOLS>
-__device__ __forceinline__ void seg_dot_q4_0(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane, float * acc) {
-    for (int b = lane; b < nb; b += 32) {
-        const uint32_t blk = seg + b * 18;                      // 2-byte aligned
-        const uint32_t a4 = blk & ~3u, sh = (blk & 2u) * 8u;
-        const uint32_t w0 = lds32(a4), w1 = lds32(a4 + 4), w2 = lds32(a4 + 8), w3 = lds32(a4 + 12), w4 = lds32(a4 + 16);
-        const float    d  = half_bits_to_float((w0 >> sh) & 0xffff);
-        const uint32_t v[4] = {__funnelshift_rc(w0, w1, sh + 16), __funnelshift_rc(w1, w2, sh + 16),
-                               __funnelshift_rc(w2, w3, sh + 16), __funnelshift_rc(w3, w4, sh + 16)};
-        const int g = kb0 + b;
-#pragma unroll
-        for (int c = 0; c < NCOLS; c++) {
-            const uint32_t ya = q.qs + c * q.pitch + g * 32;
-            const uint4 a0 = lds128(ya), a1 = lds128(ya + 16);
-            const uint2 dd = lds64(q.ds + c * q.pitch + g * 8);
-            const uint32_t ul[4] = {a0.x, a0.y, a0.z, a0.w}, uh[4] = {a1.x, a1.y, a1.z, a1.w};
-            int dot = 0;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                dot = dp4a(v[i] & 0x0F0F0F0Fu, ul[i], dot);
-                dot = dp4a((v[i] >> 4) & 0x0F0F0F0Fu, uh[i], dot);
-            }
-            // sum (q - 8) * y = sum q*y - 8 * sum y
-            acc[c] += d * (__uint_as_float(dd.x) * (float) dot - 8.0f * __uint_as_float(dd.y));
-        }
-    }
-}
-
-template <int NCOLS>
-__device__ __forceinline__ void seg_dot_q8_0(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane, float * acc) {
-    for (int b = lane; b < nb; b += 32) {
-        const uint32_t blk = seg + b * 34;                      // 2-byte aligned
-        const float    d   = half_bits_to_float(lds16(blk));
-        const uint32_t qa = blk + 2, a4 = qa & ~3u, sh = (qa & 2u) * 8u;
-        uint32_t w[9];
-#pragma unroll
-        for (int i = 0; i < 9; i++) w[i] = lds32(a4 + 4 * i);
-        uint32_t v[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = __funnelshift_rc(w[i], w[i + 1], sh);
-        const int g = kb0 + b;
-#pragma unroll
-        for (int c = 0; c < NCOLS; c++) {
-            const uint32_t ya = q.qs + c * q.pitch + g * 32;
-            const uint4 a0 = lds128(ya), a1 = lds128(ya + 16);
-            const float d8 = __uint_as_float(lds32(q.ds + c * q.pitch + g * 8));
-            const uint32_t u[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            int dot = 0;
-#pragma unroll
-            for (int i = 0; i < 8; i++) dot = dp4a(v[i], u[i], dot);
-            acc[c] += d * d8 * (float) dot;
-        }
-    }
 }
 
 __device__ __forceinline__ int lds_s8(uint32_t a) {
@@ -193,12 +194,132 @@ __device__ __forceinline__ int lds_s8(uint32_t a) {
     return v;
 }
 
-template <int NCOLS>
-__device__ __forceinline__ void seg_dot_q6_K(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane, float * acc) {
-    // unit = (block, 128-half, 16-lane column group l0): 64 weights = four 16-element groups, one per 32-sub-block
-    for (int u = lane; u < nb * 4; u += 32) {
-        const int      b = u >> 2, half = (u >> 1) & 1, l0 = (u & 1) * 16;
-        const uint32_t blk = seg + b * 210;                     // 2-byte aligned
+template <int TYPE, int NCOLS>
+__device__ __forceinline__ void unit_dot(uint32_t row, int ug, int k32, const q8_unit * u, float * out) {
+    if (TYPE == B200_TYPE_Q4_K) {
+        const int      j   = ug & 3;
+        const uint32_t blk = row + (ug >> 2) * 144;
+        const uint4    hdr = lds128(blk);                       // d | dmin<<16, scales[12]
+        const uint4    v0 = lds128(blk + 16 + 32 * j), v1 = lds128(blk + 32 + 32 * j);
+        const float    d = half_bits_to_float(hdr.x & 0xffff), dmin = half_bits_to_float(hdr.x >> 16);
+        const uint32_t sh = (j & 1) * 16;
+        const uint32_t sa = (hdr.y >> sh) & 0xffff, sb = (hdr.z >> sh) & 0xffff, sc = (hdr.w >> sh) & 0xffff;
+        // 6-bit scales / mins of sub-blocks 2j, 2j+1 (reference get_scale_min_k4, ggml-quants.c:631-639)
+        const uint32_t sc2 = j < 2 ? (sa & 0x3f3f) : ((sc & 0x0f0f) | ((sa >> 2) & 0x3030));
+        const uint32_t mn2 = j < 2 ? (sb & 0x3f3f) : (((sc >> 4) & 0x0f0f) | ((sb >> 2) & 0x3030));
+        const int   sc0 = sc2 & 0xff, sc1 = sc2 >> 8;
+        const float mn0 = (float) (mn2 & 0xff), mn1 = (float) (mn2 >> 8);
+        const uint32_t v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        uint32_t lo[8], hi[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) lo[i] = v[i] & 0x0F0F0F0Fu, hi[i] = (v[i] >> 4) & 0x0F0F0F0Fu;
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                a0 = dp4a(lo[i], u[c].q[i], a0);
+                a1 = dp4a(lo[4 + i], u[c].q[4 + i], a1);
+                b0 = dp4a(hi[i], u[c].q[8 + i], b0);
+                b1 = dp4a(hi[4 + i], u[c].q[12 + i], b1);
+            }
+            const float s = u[c].d[0] * (float) (sc0 * (a0 + a1)) + u[c].d[1] * (float) (sc1 * (b0 + b1));
+            const float t = u[c].s[0] * mn0 + u[c].s[1] * mn1;
+            out[c] = d * s - dmin * t;
+        }
+    } else if (TYPE == B200_TYPE_IQ4_XS) {
+        const int      j   = ug & 3;
+        const uint32_t blk = row + (ug >> 2) * 136;
+        const uint2    hdr = lds64(blk);                        // d | scales_h<<16, scales_l[4]
+        const uint32_t qa  = blk + 8 + 32 * j;                  // 32 bytes: sub-blocks 2j and 2j+1
+        const uint2 w0 = lds64(qa), w1 = lds64(qa + 8), w2 = lds64(qa + 16), w3 = lds64(qa + 24);
+        const float    d  = half_bits_to_float(hdr.x & 0xffff);
+        const uint32_t sh = hdr.x >> 16, sl = (hdr.y >> (8 * j)) & 0xff;
+        const int ls0 = (int) ((sl & 0xf) | (((sh >> (4 * j)) & 3) << 4)) - 32;
+        const int ls1 = (int) ((sl >> 4) | (((sh >> (4 * j + 2)) & 3) << 4)) - 32;
+        const uint32_t w[8] = {w0.x, w0.y, w1.x, w1.y, w2.x, w2.y, w3.x, w3.y};
+        uint32_t t[16];  // decoded int8 weights in nibble order: (j, j+16) pairs = the interleaved q8 order
+#pragma unroll
+        for (int i = 0; i < 8; i++) t[2 * i] = iq4nl_lookup4(w[i]), t[2 * i + 1] = iq4nl_lookup4(w[i] >> 16);
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                a0 = dp4a(t[i], u[c].q[i], a0);
+                a1 = dp4a(t[4 + i], u[c].q[4 + i], a1);
+                b0 = dp4a(t[8 + i], u[c].q[8 + i], b0);
+                b1 = dp4a(t[12 + i], u[c].q[12 + i], b1);
+            }
+            out[c] = d * (u[c].d[0] * (float) (ls0 * (a0 + a1)) + u[c].d[1] * (float) (ls1 * (b0 + b1)));
+        }
+    } else if (TYPE == B200_TYPE_Q4_0) {
+        // two 18-byte blocks = 36 bytes, 2-byte aligned: ten aligned words + clamped funnel shifts
+        const uint32_t a  = row + ug * 36;
+        const uint32_t a4 = a & ~3u, sh = (a & 2u) * 8u;
+        uint32_t w[10];
+#pragma unroll
+        for (int i = 0; i < 10; i++) w[i] = lds32(a4 + 4 * i);
+        uint32_t s[9];  // the 36 bytes as aligned words
+#pragma unroll
+        for (int i = 0; i < 9; i++) s[i] = __funnelshift_rc(w[i], w[i + 1], sh);
+        const bool  two = 2 * ug + 1 < k32;
+        const float d0 = half_bits_to_float(s[0] & 0xffff);
+        const float d1 = two ? half_bits_to_float(s[4] >> 16) : 0.f;
+        uint32_t v0[4], v1[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            v0[i] = __funnelshift_r(s[i], s[i + 1], 16);        // bytes 2..17
+            v1[i] = s[5 + i];                                    // bytes 20..35
+        }
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                a0 = dp4a(v0[i] & 0x0F0F0F0Fu, u[c].q[i], a0);
+                a1 = dp4a((v0[i] >> 4) & 0x0F0F0F0Fu, u[c].q[4 + i], a1);
+                b0 = dp4a(v1[i] & 0x0F0F0F0Fu, u[c].q[8 + i], b0);
+                b1 = dp4a((v1[i] >> 4) & 0x0F0F0F0Fu, u[c].q[12 + i], b1);
+            }
+            // sum (q - 8) * y = sum q*y - 8 * sum y
+            out[c] = d0 * (u[c].d[0] * (float) (a0 + a1) - 8.0f * u[c].s[0]) +
+                     d1 * (u[c].d[1] * (float) (b0 + b1) - 8.0f * u[c].s[1]);
+        }
+    } else if (TYPE == B200_TYPE_Q8_0) {
+        // two 34-byte blocks = 68 bytes, 2-byte aligned
+        const uint32_t a  = row + ug * 68;
+        const uint32_t a4 = a & ~3u, sh = (a & 2u) * 8u;
+        uint32_t w[18];
+#pragma unroll
+        for (int i = 0; i < 18; i++) w[i] = lds32(a4 + 4 * i);
+        uint32_t s[17];
+#pragma unroll
+        for (int i = 0; i < 17; i++) s[i] = __funnelshift_rc(w[i], w[i + 1], sh);
+        const bool  two = 2 * ug + 1 < k32;
+        const float d0 = half_bits_to_float(s[0] & 0xffff);
+        const float d1 = two ? half_bits_to_float(s[8] >> 16) : 0.f;
+        uint32_t v0[8], v1[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            v0[i] = __funnelshift_r(s[i], s[i + 1], 16);        // bytes 2..33
+            v1[i] = s[9 + i];                                    // bytes 36..67
+        }
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                a0 = dp4a(v0[i], u[c].q[i], a0);
+                a1 = dp4a(v0[4 + i], u[c].q[4 + i], a1);
+                b0 = dp4a(v1[i], u[c].q[8 + i], b0);
+                b1 = dp4a(v1[4 + i], u[c].q[12 + i], b1);
+            }
+            out[c] = d0 * u[c].d[0] * (float) (a0 + a1) + d1 * u[c].d[1] * (float) (b0 + b1);
+        }
+    } else {  // Q6_K
+        const int      half = (ug >> 1) & 1, l0 = (ug & 1) * 16;
+        const uint32_t blk  = row + (ug >> 2) * 210;            // 2-byte aligned
         const uint4 qa = lds128_align2(blk + 64 * half + l0);
         const uint4 qb = lds128_align2(blk + 64 * half + 32 + l0);
         const uint4 qh = lds128_align2(blk + Q6K_OFF_QH + 32 * half + l0);
@@ -214,34 +335,21 @@ __device__ __forceinline__ void seg_dot_q6_K(uint32_t seg, int nb, int kb0, cons
             v[2][i] = ((A[i] >> 4) & 0x0F0F0F0Fu) | (H[i] & 0x30303030u);
             v[3][i] = ((B[i] >> 4) & 0x0F0F0F0Fu) | ((H[i] >> 2) & 0x30303030u);
         }
-        const int sbg = (kb0 + b) * 8 + 4 * half;               // q8 block of sub-block j = 0
 #pragma unroll
         for (int c = 0; c < NCOLS; c++) {
             float s = 0.f;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const uint4 y  = lds128(q.qs + c * q.pitch + (sbg + j) * 32 + l0);
-                const float d8 = __uint_as_float(lds32(q.ds + c * q.pitch + (sbg + j) * 8));
-                const int   s16 = (int) (short) lds16(q.s16 + c * q.pitch + (sbg + j) * 4 + (l0 >> 3));
-                int dot = dp4a(v[j][0], y.x, 0);
-                dot = dp4a(v[j][1], y.y, dot);
-                dot = dp4a(v[j][2], y.z, dot);
-                dot = dp4a(v[j][3], y.w, dot);
-                // weights are stored with a +32 offset: sum (v - 32) * y = sum v*y - 32 * sum y
-                s += d8 * (float) (sc[j] * (dot - 32 * s16));
+                int dot = dp4a(v[j][0], u[c].q[4 * j], 0);
+                dot = dp4a(v[j][1], u[c].q[4 * j + 1], dot);
+                dot = dp4a(v[j][2], u[c].q[4 * j + 2], dot);
+                dot = dp4a(v[j][3], u[c].q[4 * j + 3], dot);
+                // weights carry a +32 offset: sum (v - 32) * y = sum v*y - 32 * sum y
+                s += u[c].d[j] * (float) sc[j] * ((float) dot - u[c].s[j]);
             }
-            acc[c] += d * s;
+            out[c] = d * s;
         }
     }
-}
-
-template <int TYPE, int NCOLS>
-__device__ __forceinline__ void seg_dot(uint32_t seg, int nb, int kb0, const q8_smem & q, int lane, float * acc) {
-    if (TYPE == B200_TYPE_Q4_K)        seg_dot_q4_K<NCOLS>(seg, nb, kb0, q, lane, acc);
-    else if (TYPE == B200_TYPE_IQ4_XS) seg_dot_iq4_xs<NCOLS>(seg, nb, kb0, q, lane, acc);
-    else if (TYPE == B200_TYPE_Q4_0)   seg_dot_q4_0<NCOLS>(seg, nb, kb0, q, lane, acc);
-    else if (TYPE == B200_TYPE_Q8_0)   seg_dot_q8_0<NCOLS>(seg, nb, kb0, q, lane, acc);
-    else                               seg_dot_q6_K<NCOLS>(seg, nb, kb0, q, lane, acc);
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
@@ -253,13 +361,20 @@ struct gemv_kargs {
     const uint8_t * xq;
     float *         dst;
     int64_t         dst_col_stride;
-    int             m, k, nst;
+    int             m, k;
+    int             nst;          // ring depth
+    int             R;            // rows per stage (multiple of rows-per-iteration, <= 32)
+    int             lpr_log2;     // log2(lanes per row): each warp covers 2^lpr_log2 units of k
+    int             nwc;          // compute warps = ceil(units_per_row / lanes_per_row)
+    int             row_pitch;    // bytes between rows inside a stage
+    int             stage_bytes;  // R * row_pitch + slack, multiple of 128
     const int32_t * ids;
     int64_t         ids_row_stride;
     int             n_used, ne11;
     int64_t         x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
     int             world, rank;
     int64_t         row_offset;
+    int             dbg;          // profiling aid: 1 = skip the dot products, 2 = skip the TMA loads
 };
 struct gemv_peers {
     float *   dst[16];
@@ -267,23 +382,25 @@ struct gemv_peers {
     int32_t   epoch;
 };
 
-template <int TYPE, int NCOLS, bool PEERS>
-__global__ void __launch_bounds__(512, 1) k_gemv(const gemv_kargs a, const gemv_peers peers) {
+constexpr int GEMV_MAX_R = 32;
+
+template <int TYPE, int NCOLS, int MINB, bool PEERS>
+__global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv_kargs a, const gemv_peers peers) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int BYTES = qtraits<TYPE>::bytes;
-    constexpr int SEGB  = seg_cfg<TYPE>::blocks;
-    constexpr int SLOT  = slot_bytes<TYPE>();
+    constexpr int BLCK  = qtraits<TYPE>::blck;
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int nst  = a.nst;
-    const q8_layout L = q8_soa_layout(a.k);
+    const int  lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int  nwc = a.nwc, nst = a.nst, R = a.R;
+    const bool producer = warp == nwc;                          // the last warp issues TMA and writes results
 
-    // shared memory: [q8 columns][rings: nw * nst slots][mbarriers: nw * nst]
-    uint8_t *      q8base = smem;
-    const uint32_t ring   = smem_u32(smem) + ((NCOLS * L.bytes + 127) & ~127u) + warp * nst * SLOT;
-    const uint32_t bars   = smem_u32(smem) + ((NCOLS * L.bytes + 127) & ~127u) + nw * nst * SLOT + warp * nst * 8;
+    // shared memory: [stages: nst * stage_bytes][partials: nst * 2 * NCOLS * R * nwc floats][full bars][empty bars]
+    const uint32_t sm_stage = smem_u32(smem);
+    float *        partial  = reinterpret_cast<float *>(smem + (size_t) nst * a.stage_bytes);
+    const int      part_sz  = NCOLS * R * nwc;                  // floats per (slot, parity)
+    const uint32_t bar_full = smem_u32(partial) + (uint32_t) nst * 2 * part_sz * 4;
+    const uint32_t bar_empty = bar_full + 8 * nst;
 
-    // which matrix / activation / output this CTA row (blockIdx.y) works on
     const uint8_t * W   = a.W;
     const float *   x   = a.x;
     float *         dst = a.dst;
@@ -296,101 +413,155 @@ __global__ void __launch_bounds__(512, 1) k_gemv(const gemv_kargs a, const gemv_
         dst += tok * a.dst_token_stride + slot * a.dst_slot_stride;
     }
 
-    // this warp's rows and work items (row segments)
-    const int64_t tw = (int64_t) gridDim.x * nw, gw = (int64_t) blockIdx.x * nw + warp;
-    const int     r_begin = (int) (gw * a.m / tw), r_end = (int) ((gw + 1) * a.m / tw);
-    const int     nblk = a.k / qtraits<TYPE>::blck;             // blocks per row
-    const int     nseg = (nblk + SEGB - 1) / SEGB;
-    const int     nitems = (r_end - r_begin) * nseg;
+    // this CTA's rows and stages
+    const int r_begin = (int) ((int64_t) blockIdx.x * a.m / gridDim.x);
+    const int r_end   = (int) ((int64_t) (blockIdx.x + 1) * a.m / gridDim.x);
+    const int nrows   = r_end - r_begin;
+    const int nstages = (nrows + R - 1) / R;
+    const int row_bytes = a.k / BLCK * BYTES;
+    const bool contiguous = a.w_row_stride == row_bytes;
 
-    if (lane == 0) {
-        for (int s = 0; s < nst; s++) mbar_init(bars + 8 * s, 1);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nst; s++) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, nwc);
+        }
         mbar_fence_init();
     }
-    __syncwarp();
-
-    // producer state (lane 0 only): next item to issue
-    int      p_row = r_begin, p_seg = 0, p_it = 0;
-    auto issue = [&]() {
-        const int       blk0  = p_seg * SEGB;
-        const int       nb    = min(SEGB, nblk - blk0);
-        const uint8_t * src   = W + (int64_t) p_row * a.w_row_stride + (int64_t) blk0 * BYTES;
-        const uint64_t  g     = (uint64_t) src;
-        const uint64_t  g0    = g & ~(uint64_t) 15;
-        const uint32_t  span  = (uint32_t) (((g + (uint64_t) nb * BYTES + 15) & ~(uint64_t) 15) - g0);
-        const int       slot  = p_it % nst;
-        mbar_expect_tx(bars + 8 * slot, span);
-        tma_load_1d(ring + slot * SLOT, (const void *) g0, span, bars + 8 * slot);
-        if (++p_seg == nseg) { p_seg = 0; p_row++; }
-        p_it++;
-    };
-    if (lane == 0) {
-        const int pre = min(nst, nitems);
-        for (int i = 0; i < pre; i++) issue();
-    }
-
-    // everything above touched only weights; from here on we read what the previous kernel produced
-    pdl_wait();
+    __syncthreads();
     pdl_launch_dependents();
 
-    // activations -> shared memory, in the SoA q8_1 layout
-    if (a.xq) {
-        const uint4 * src = reinterpret_cast<const uint4 *>(a.xq);
-        uint4 *       dq  = reinterpret_cast<uint4 *>(q8base);
-        const int     n16 = NCOLS * L.bytes / 16;
-        for (int i = threadIdx.x; i < n16; i += blockDim.x) dq[i] = src[i];
-    } else {
-        const bool vec = ((uintptr_t) x % 16 == 0) && (a.x_col_stride % 4 == 0);
-#pragma unroll 1
-        for (int c = 0; c < NCOLS; c++)
-            quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS>(x + c * a.x_col_stride, a.k, q8base + c * L.bytes, L, warp, nw,
-                                                          lane, vec);
-    }
-    __syncthreads();
-
-    q8_smem q;
-    q.qs = smem_u32(q8base), q.ds = q.qs + L.off_ds, q.s16 = q.qs + L.off_s16, q.pitch = L.bytes;
-
-    float acc[NCOLS];
-#pragma unroll
-    for (int c = 0; c < NCOLS; c++) acc[c] = 0.f;
-
-    int row = r_begin, sgi = 0;
-    for (int it = 0; it < nitems; it++) {
-        const int slot = it % nst;
-        mbar_wait(bars + 8 * slot, (it / nst) & 1);
-        const int      blk0 = sgi * SEGB;
-        const int      nb   = min(SEGB, nblk - blk0);
-        const uint32_t off  = (uint32_t) ((uint64_t) (W + (int64_t) row * a.w_row_stride + (int64_t) blk0 * BYTES) & 15);
-        seg_dot<TYPE, NCOLS>(ring + slot * SLOT + off, nb, blk0, q, lane, acc);
-        __syncwarp();                                           // all lanes are done reading the slot
-        if (lane == 0 && p_it < nitems) issue();
-        if (++sgi == nseg) {
-#pragma unroll
-            for (int c = 0; c < NCOLS; c++) {
-                const float v = warp_sum(acc[c]);
+    if (producer) {
+        // ---------------------------------------------------------------------------------------- TMA + epilogue warp
+        auto issue = [&](int st) {  // all lanes call; stage st -> slot st % nst
+            const int      slot = st % nst;
+            const int      r0 = r_begin + st * R, nr = min(R, r_end - r0);
+            const uint32_t dstb = sm_stage + slot * a.stage_bytes;
+            const uint32_t bar  = bar_full + 8 * slot;
+            if (a.dbg == 2) {
+                if (lane == 0) mbar_arrive(bar);
+            } else if (contiguous) {
                 if (lane == 0) {
+                    const uint64_t g    = (uint64_t) (W + (int64_t) r0 * row_bytes);
+                    const uint64_t g0   = g & ~(uint64_t) 15;
+                    const uint32_t span = (uint32_t) (((g + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
+                    mbar_expect_tx(bar, span);
+                    tma_load_1d(dstb, (const void *) g0, span, bar);
+                }
+            } else {  // strided rows: one bulk copy per row, lane i copies row i
+                uint32_t span = 0;
+                uint64_t g0   = 0;
+                if (lane < nr) {
+                    const uint64_t g = (uint64_t) (W + (int64_t) (r0 + lane) * a.w_row_stride);
+                    g0   = g & ~(uint64_t) 15;
+                    span = (uint32_t) (((g + (uint64_t) row_bytes + 15) & ~(uint64_t) 15) - g0);
+                }
+                uint32_t total = span;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+                if (lane == 0) mbar_expect_tx(bar, total);
+                __syncwarp();
+                if (lane < nr) tma_load_1d(dstb + lane * a.row_pitch, (const void *) g0, span, bar);
+            }
+        };
+        auto finish = [&](int st) {  // sum the per-warp partials of stage st in a fixed order and write the outputs
+            const int slot = st % nst, par = (st / nst) & 1;
+            const int r0 = r_begin + st * R, nr = min(R, r_end - r0);
+            const float * p = partial + (size_t) (slot * 2 + par) * part_sz;
+            if (lane < nr) {
+#pragma unroll
+                for (int c = 0; c < NCOLS; c++) {
+                    float v = 0.f;
+                    for (int w = 0; w < nwc; w++) v += p[(c * R + lane) * nwc + w];
                     if (PEERS) {
                         for (int r = 0; r < a.world; r++)
-                            peers.dst[r][c * a.dst_col_stride + a.row_offset + row] = v;
+                            peers.dst[r][c * a.dst_col_stride + a.row_offset + r0 + lane] = v;
                     } else {
-                        dst[c * a.dst_col_stride + row] = v;
+                        dst[c * a.dst_col_stride + r0 + lane] = v;
                     }
                 }
-                acc[c] = 0.f;
             }
-            sgi = 0;
-            row++;
+        };
+        const int pre = min(nst, nstages);
+        for (int st = 0; st < pre; st++) issue(st);             // weights only: legal before the dependency wait
+        pdl_wait();                                             // dst may still be read by the previous kernel
+        for (int st = 0; st < nstages; st++) {
+            const int slot = st % nst;
+            mbar_wait(bar_empty + 8 * slot, (st / nst) & 1);    // all compute warps are done with stage st
+            if (st + nst < nstages) issue(st + nst);            // refill first, then reduce
+            finish(st);
+        }
+        if (PEERS) {
+            __syncwarp();
+            if (lane == 0) {
+                __threadfence_system();
+                for (int r = 0; r < a.world; r++) atomicAdd_system(peers.flag[r], 1);
+            }
+        }
+        return;
+    }
+
+    // -------------------------------------------------------------------------------------------- compute warps
+    const int lpr   = 1 << a.lpr_log2;                          // lanes per row
+    const int rpi   = 32 >> a.lpr_log2;                         // rows per warp iteration
+    const int ug    = warp * lpr + (lane & (lpr - 1));          // this lane's unit of k, fixed for the whole kernel
+    const int rsub  = lane >> a.lpr_log2;
+    const int k32   = a.k / 32;
+    const int upr   = (a.k + 63) / 64;                          // units per row
+    const bool have = ug < upr;
+
+    pdl_wait();
+    q8_unit u[NCOLS];
+    if (have) {
+        if (a.xq) {
+            const q8_layout L = q8_soa_layout(a.k);
+#pragma unroll
+            for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], a.xq + (size_t) c * L.bytes, L, a.k, ug);
+        } else {
+            const bool vec = ((uintptr_t) x % 16 == 0) && (a.x_col_stride % 4 == 0);
+#pragma unroll
+            for (int c = 0; c < NCOLS; c++) make_unit_f32<TYPE>(u[c], x + c * a.x_col_stride, a.k, ug, vec);
+        }
+    } else {
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+#pragma unroll
+            for (int i = 0; i < 16; i++) u[c].q[i] = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) u[c].d[i] = 0.f, u[c].s[i] = 0.f;
         }
     }
 
-    if (PEERS) {
-        // publish: all of this CTA's peer stores are visible system-wide before its arrival is counted
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence_system();
-            for (int r = 0; r < a.world; r++) atomicAdd_system(peers.flag[r], 1);
+    for (int st = 0; st < nstages; st++) {
+        const int slot = st % nst, par = (st / nst) & 1;
+        const int r0 = st * R, nr = min(R, nrows - r0);
+        mbar_wait(bar_full + 8 * slot, par);
+        const uint32_t stage = sm_stage + slot * a.stage_bytes;
+        float * p = partial + (size_t) (slot * 2 + par) * part_sz;
+        for (int rr = rsub; rr < R; rr += rpi) {
+            float out[NCOLS];
+#pragma unroll
+            for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
+            if (have && rr < nr && a.dbg != 1) {
+                uint32_t rowa;
+                if (contiguous) {
+                    const uint32_t off = (uint32_t) ((uint64_t) (W + (int64_t) (r_begin + r0) * row_bytes) & 15);
+                    rowa = stage + off + rr * row_bytes;
+                } else {
+                    const uint32_t off = (uint32_t) ((uint64_t) (W + (int64_t) (r_begin + r0 + rr) * a.w_row_stride) & 15);
+                    rowa = stage + rr * a.row_pitch + off;
+                }
+                unit_dot<TYPE, NCOLS>(rowa, ug, k32, u, out);
+            }
+#pragma unroll
+            for (int c = 0; c < NCOLS; c++) {
+                float v = out[c];
+                for (int o = lpr >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if ((lane & (lpr - 1)) == 0 && rr < nr) p[(c * R + rr) * nwc + warp] = v;
+            }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8 * slot);       // release: partials visible to the epilogue warp
     }
 }
 
@@ -400,80 +571,122 @@ static int env_int(const char * name, int dflt) {
     return s && *s ? atoi(s) : dflt;
 }
 
+struct gemv_plan {
+    int lpr_log2, nwc, R, nst, row_pitch, stage_bytes, minb;
+    size_t smem;
+};
 
-static int slot_bytes_of(int type) {
+static int type_block_bytes(int type) {
     switch (type) {
-        case B200_TYPE_Q4_0:   return slot_bytes<B200_TYPE_Q4_0>();
-        case B200_TYPE_Q8_0:   return slot_bytes<B200_TYPE_Q8_0>();
-        case B200_TYPE_Q4_K:   return slot_bytes<B200_TYPE_Q4_K>();
-        case B200_TYPE_Q6_K:   return slot_bytes<B200_TYPE_Q6_K>();
-        case B200_TYPE_IQ4_XS: return slot_bytes<B200_TYPE_IQ4_XS>();
+        case B200_TYPE_Q4_0: return 18;
+        case B200_TYPE_Q8_0: return 34;
+        case B200_TYPE_Q4_K: return 144;
+        case B200_TYPE_Q6_K: return 210;
+        case B200_TYPE_IQ4_XS: return 136;
     }
     return 0;
 }
+static int type_block_elems(int type) { return type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 ? 32 : 256; }
 
-static constexpr int SMEM_LIMIT = 227 * 1024;
+static constexpr size_t SMEM_2CTA = 112 * 1024;   // two CTAs (+1 KB reserved each) fit in 228 KB
+static constexpr size_t SMEM_1CTA = 226 * 1024;
+static constexpr int    WARPS_2CTA = 8, WARPS_1CTA = 16;   // compute warps (one more warp is the producer)
 
-size_t gemv_q8_smem_bytes(int64_t k, int ncols) { return ((size_t) ncols * q8_soa_layout(k).bytes + 127) & ~(size_t) 127; }
-
-int gemv_max_cols(int type, int64_t k) {
-    const int slot = slot_bytes_of(type);
-    int best = 0;
-    for (int n = 1; n <= 8; n++)
-        if (gemv_q8_smem_bytes(k, n) + (size_t) 4 * 2 * (slot + 8) <= (size_t) SMEM_LIMIT) best = n;
-    return best;
+// Choose the k split, stage geometry and ring depth.  Returns false if the shape cannot be planned
+// (k > 32768: more than one unit per lane would be needed).
+static bool make_plan(int type, int64_t k, int ncols, bool contiguous, gemv_plan & P) {
+    const int upr = (int) ((k + 63) / 64);
+    int lg = 2;
+    while (lg < 5 && (upr + (1 << lg) - 1) / (1 << lg) > WARPS_2CTA) lg++;
+    lg = env_int("B200_GEMV_LPR_LOG2", lg);
+    if (lg < 0 || lg > 5) return false;
+    const int nwc = (upr + (1 << lg) - 1) / (1 << lg);
+    if (nwc > WARPS_1CTA) return false;
+    P.minb = (nwc > WARPS_2CTA || ncols > 2) ? 1 : 2;           // 24 registers of activations per column
+    P.minb = env_int("B200_GEMV_MINB", P.minb);
+    if (nwc > WARPS_2CTA) P.minb = 1;
+    P.lpr_log2 = lg, P.nwc = nwc;
+    const int rpi = 32 >> lg;
+    const int row_bytes = (int) (k / type_block_elems(type)) * type_block_bytes(type);
+    P.row_pitch = contiguous ? row_bytes : ((row_bytes + 15 + 15) & ~15);
+    const int target = env_int("B200_GEMV_STAGE_KB", 32) * 1024;
+    const int want   = env_int("B200_GEMV_STAGES", 4);
+    for (;;) {
+        const size_t budget = P.minb == 2 ? SMEM_2CTA : SMEM_1CTA;
+        int R = target / P.row_pitch / rpi * rpi;
+        if (R < rpi) R = rpi;
+        if (R > GEMV_MAX_R) R = GEMV_MAX_R / rpi * rpi;
+        for (; R >= rpi; R -= rpi) {
+            // payload + 15 bytes of leading misalignment + 16 so word reads of a 2-byte-aligned tail stay inside
+            P.stage_bytes = (R * P.row_pitch + 15 + 16 + 127) & ~127;
+            const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * R * nwc * 4 + 16;
+            int nst = (int) (budget / per_stage);
+            if (nst > want) nst = want;
+            if (nst >= 2 || (R == rpi && nst >= 1)) {
+                P.nst = nst, P.R = R, P.smem = (size_t) nst * per_stage;
+                return true;
+            }
+        }
+        if (P.minb == 1) return false;
+        P.minb = 1;                                             // one row does not fit in half an SM: take all of it
+    }
 }
 
-template <int TYPE, int NCOLS>
-static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
-    static int sm_count = 0;
+size_t gemv_q8_smem_bytes(int64_t k, int ncols) { (void) k, (void) ncols; return 0; }
+
+int gemv_max_cols(int type, int64_t k) {
+    gemv_plan P;
+    for (int n = 4; n >= 1; n--)
+        if (make_plan(type, k, n, true, P)) return n;
+    return 0;
+}
+
+template <int TYPE, int NCOLS, int MINB, bool PEERS>
+static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, cudaStream_t stream) {
+    static int  sm_count = 0;
+    static bool attr_set = false;
     if (!sm_count) {
         int dev = 0;
         B200_CUDA_TRY(cudaGetDevice(&dev));
         B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
     }
-    const int    slot = slot_bytes<TYPE>();
-    const size_t q8   = gemv_q8_smem_bytes(g.k, NCOLS);
-    // warps per CTA and ring depth: as much in flight as shared memory allows, preferring 8 warps x 3 slots
-    int nw  = env_int("B200_GEMV_WARPS", 8);
-    int nst = env_int("B200_GEMV_STAGES", 3);
-    while (q8 + (size_t) nw * nst * (slot + 8) > (size_t) SMEM_LIMIT) {
-        if (nst > 2) nst--;
-        else if (nw > 4) nw -= 4;
-        else return B200_ERR_UNSUPPORTED;
+    auto kern = k_gemv<TYPE, NCOLS, MINB, PEERS>;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int) (MINB == 2 ? SMEM_2CTA : SMEM_1CTA)));
+        attr_set = true;
     }
-    const size_t smem = q8 + (size_t) nw * nst * (slot + 8);
-
     gemv_kargs a;
     a.W = g.W, a.w_row_stride = g.w_row_stride, a.w_expert_stride = g.w_expert_stride;
     a.x = g.x, a.x_col_stride = g.x_col_stride, a.xq = g.xq;
     a.dst = g.dst, a.dst_col_stride = g.dst_col_stride;
-    a.m = (int) g.m, a.k = (int) g.k, a.nst = nst;
-    a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used, a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
+    a.m = (int) g.m, a.k = (int) g.k;
+    a.nst = P.nst, a.R = P.R, a.lpr_log2 = P.lpr_log2, a.nwc = P.nwc, a.row_pitch = P.row_pitch;
+    a.stage_bytes = P.stage_bytes;
+    a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used > 0 ? g.n_used : 1;
+    a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
     a.x_token_stride = g.x_token_stride, a.x_slot_stride = g.x_slot_stride;
     a.dst_token_stride = g.dst_token_stride, a.dst_slot_stride = g.dst_slot_stride;
     a.world = g.world, a.rank = g.rank, a.row_offset = g.row_offset;
+    a.dbg = env_int("B200_GEMV_DEBUG", 0);
     gemv_peers peers = {};
-    const bool use_peers = g.world > 1;
-    if (use_peers) {
+    if (PEERS) {
         for (int r = 0; r < g.world && r < 16; r++) peers.dst[r] = g.peer_dst[r], peers.flag[r] = g.peer_flag[r];
         peers.epoch = g.epoch;
     }
-
-    // grid.x: one CTA per SM, but never more warps than rows
+    // grid.x: MINB CTAs per SM, but at least rows-per-iteration rows each
     const int64_t pairs = g.ids ? g.npairs : 1;
-    int gx = sm_count * env_int("B200_GEMV_CTAS_PER_SM", 1);
+    int gx = sm_count * MINB * env_int("B200_GEMV_WAVES", 1);
     if (g.ids && pairs > 1) gx = (int) ((gx + pairs - 1) / pairs);  // MUL_MAT_ID: the pairs share the machine
-    const int64_t max_ctas = (g.m + nw - 1) / nw;
+    const int     rpi = 32 >> P.lpr_log2;
+    const int64_t max_ctas = (g.m + rpi - 1) / rpi;
     if (gx > max_ctas) gx = (int) max_ctas;
     if (gx < 1) gx = 1;
 
-    auto kern = use_peers ? k_gemv<TYPE, NCOLS, true> : k_gemv<TYPE, NCOLS, false>;
-    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) gx, (unsigned) pairs, 1);
-    cfg.blockDim         = dim3((unsigned) nw * 32, 1, 1);
-    cfg.dynamicSmemBytes = smem;
+    cfg.blockDim         = dim3((unsigned) (P.nwc + 1) * 32, 1, 1);
+    cfg.dynamicSmemBytes = P.smem;
     cfg.stream           = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -484,6 +697,19 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     return B200_OK;
 }
 
+template <int TYPE, int NCOLS>
+static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
+    gemv_plan P;
+    const int row_bytes = (int) (g.k / type_block_elems(TYPE)) * type_block_bytes(TYPE);
+    if (!make_plan(TYPE, g.k, NCOLS, g.w_row_stride == row_bytes, P)) return B200_ERR_UNSUPPORTED;
+    const bool peers = g.world > 1;
+    if (P.minb == 2) {
+        return peers ? launch_gemv_k<TYPE, NCOLS, 2, true>(g, P, stream)
+                     : launch_gemv_k<TYPE, NCOLS, 2, false>(g, P, stream);
+    }
+    return peers ? launch_gemv_k<TYPE, NCOLS, 1, true>(g, P, stream) : launch_gemv_k<TYPE, NCOLS, 1, false>(g, P, stream);
+}
+
 template <int TYPE>
 static int launch_gemv_n(const gemv_args & g, cudaStream_t stream) {
     switch (g.ncols) {
@@ -491,10 +717,6 @@ static int launch_gemv_n(const gemv_args & g, cudaStream_t stream) {
         case 2: return launch_gemv_t<TYPE, 2>(g, stream);
         case 3: return launch_gemv_t<TYPE, 3>(g, stream);
         case 4: return launch_gemv_t<TYPE, 4>(g, stream);
-        case 5: return launch_gemv_t<TYPE, 5>(g, stream);
-        case 6: return launch_gemv_t<TYPE, 6>(g, stream);
-        case 7: return launch_gemv_t<TYPE, 7>(g, stream);
-        case 8: return launch_gemv_t<TYPE, 8>(g, stream);
     }
     return B200_ERR_SHAPE;
 }

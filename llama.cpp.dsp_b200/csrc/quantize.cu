@@ -50,23 +50,41 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
 }
 
 // ---------------------------------------------------------------------------------------------- q8_1, SoA layout
-// one CTA of 8 warps per activation row; output rows are L.bytes apart in the workspace
+// grid (ceil(k/32 / 32), nrows), 8 warps: every 8-lane group quantizes one block; output rows are L.bytes apart.
+// Launched with programmatic stream serialization so the GEMV that consumes it can prefetch weights meanwhile.
 template <bool INTERLEAVE>
 __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restrict__ x, int64_t x_stride,
                                                          uint8_t * __restrict__ y, int64_t k, bool vec) {
+    pdl_wait();
+    pdl_launch_dependents();
     const q8_layout L = q8_soa_layout(k);
-    quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.x * x_stride, k, y + (int64_t) blockIdx.x * L.bytes, L,
-                                    threadIdx.x >> 5, 8, threadIdx.x & 31, vec);
+    quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.y * x_stride, k, y + (int64_t) blockIdx.y * L.bytes, L,
+                                    blockIdx.x * 8 + (threadIdx.x >> 5), gridDim.x * 8, threadIdx.x & 31, vec);
 }
 
 int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
                            cudaStream_t stream) {
     if (k == 0 || nrows == 0) return B200_OK;
     const bool vec = ((uintptr_t) x % 16 == 0) && (x_stride % 4 == 0);
-    if (interleave) k_quantize_q8_soa<true><<<(unsigned) nrows, 256, 0, stream>>>(x, x_stride, (uint8_t *) y, k, vec);
-    else            k_quantize_q8_soa<false><<<(unsigned) nrows, 256, 0, stream>>>(x, x_stride, (uint8_t *) y, k, vec);
-    note_launch();
-    return check_cuda(cudaGetLastError(), "k_quantize_q8_soa");
+    int64_t done = 0;
+    while (done < nrows) {
+        const int64_t rows = nrows - done < 65535 ? nrows - done : 65535;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim  = dim3((unsigned) ((k / 32 + 31) / 32), (unsigned) rows, 1);
+        cfg.blockDim = dim3(256, 1, 1);
+        cfg.stream   = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr, cfg.numAttrs = 1;
+        const float * xp = x + done * x_stride;
+        uint8_t *     yp = (uint8_t *) y + done * (int64_t) q8_soa_layout(k).bytes;
+        if (interleave) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<true>, xp, x_stride, yp, k, vec));
+        else            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<false>, xp, x_stride, yp, k, vec));
+        note_launch();
+        done += rows;
+    }
+    return B200_OK;
 }
 
 // ---------------------------------------------------------------------------------------------- dequantizers

@@ -1,5 +1,6 @@
-"""Micro-benchmark of the GEMV kernel on distinct (> L2) weight matrices; sweeps env knobs in-process.
-usage: python tools/gemv_sweep.py [type ...]"""
+"""Micro-benchmark of the GEMV kernel on distinct (> L2) weight matrices, replayed from a CUDA graph so that host
+launch overhead is out of the picture; sweeps env knobs in-process.
+usage: python tools/gemv_sweep.py [--quick] [type ...]"""
 import os
 import sys
 
@@ -13,60 +14,80 @@ import b200pkg  # noqa: E402
 import qref  # noqa: E402
 
 qmm = b200pkg.load()
+KNOBS = ["B200_GEMV_STAGES", "B200_GEMV_STAGE_KB", "B200_GEMV_LPR_LOG2", "B200_GEMV_MINB", "B200_PDL",
+         "B200_FUSED_QUANT_MAX_K", "B200_GEMV_WAVES"]
 
 
 def make_weights(t, m, k, copies, rng):
-    rs = qmm.row_size(t, k)
     one = torch.from_numpy(qref.random_blocks(t, m, k, rng)).cuda()
-    ws = [one]
-    for _ in range(copies - 1):
-        ws.append(one.clone())
-    return ws, rs * m
+    return [one] + [one.clone() for _ in range(copies - 1)]
 
 
-def time_gemv(t, m, k, n, ws, iters=20):
+def time_gemv(t, m, k, n, ws, iters=10, graph=True):
     x = torch.rand((n, k), device="cuda") * 2 - 1
     outs = [torch.empty((n, m), device="cuda") for _ in ws]
-    for w, o in zip(ws, outs):
-        qmm.mul_mat(t, w, x, m, k, out=o)
+
+    def run():
+        for w, o in zip(ws, outs):
+            qmm.mul_mat(t, w, x, m, k, out=o)
+
+    run()
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    if graph:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(s):
+            run()
+            s.synchronize()
+            with torch.cuda.graph(g, stream=s):
+                run()
+        fn = g.replay
+    else:
+        fn = run
+    fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        for w, o in zip(ws, outs):
-            qmm.mul_mat(t, w, x, m, k, out=o)
+        fn()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) * 1e3 / (iters * len(ws))  # us per matmul
 
 
 def main():
-    names = sys.argv[1:] or ["q4_K"]
+    args = sys.argv[1:]
+    quick = "--quick" in args
+    names = [a for a in args if not a.startswith("--")] or ["q4_K"]
     rng = np.random.default_rng(0)
     shapes = [(4096, 14336), (14336, 4096), (4096, 4096), (1024, 4096)]
+    configs = [{}] if quick else [
+        {}, {"B200_PDL": 0}, {"B200_GEMV_STAGES": 3}, {"B200_GEMV_STAGES": 6, "B200_GEMV_STAGE_KB": 16},
+        {"B200_GEMV_STAGE_KB": 16}, {"B200_GEMV_STAGE_KB": 24, "B200_GEMV_STAGES": 4},
+        {"B200_GEMV_MINB": 1, "B200_GEMV_STAGES": 6}, {"B200_GEMV_LPR_LOG2": 4}, {"B200_GEMV_LPR_LOG2": 3},
+        {"B200_FUSED_QUANT_MAX_K": 0}, {"B200_FUSED_QUANT_MAX_K": 100000}, {"B200_GEMV_WAVES": 2},
+    ]
     for name in names:
         t = qref.WEIGHT_TYPES[name]
         for (m, k) in shapes:
             nbytes = qmm.row_size(t, k) * m
             copies = max(2, int(600e6 // nbytes))          # > 4x L2
-            ws, _ = make_weights(t, m, k, copies, rng)
+            ws = make_weights(t, m, k, copies, rng)
             for n in (1, 2, 4, 8):
-                for warps, stages, ctas, pdl in [(8, 3, 1, 1), (8, 3, 1, 0), (8, 4, 1, 1), (16, 2, 1, 1), (16, 3, 1, 1),
-                                                 (4, 4, 2, 1), (8, 2, 2, 1), (4, 6, 1, 1)]:
-                    if n > 1 and (warps, stages, ctas, pdl) != (8, 3, 1, 1):
+                for cfg in configs:
+                    if n > 1 and cfg:
                         continue
-                    os.environ["B200_GEMV_WARPS"] = str(warps)
-                    os.environ["B200_GEMV_STAGES"] = str(stages)
-                    os.environ["B200_GEMV_CTAS_PER_SM"] = str(ctas)
-                    os.environ["B200_PDL"] = str(pdl)
+                    for kn in KNOBS:
+                        os.environ.pop(kn, None)
+                    for kn, v in cfg.items():
+                        os.environ[kn] = str(v)
                     try:
                         us = time_gemv(t, m, k, n, ws)
                     except Exception as e:  # noqa: BLE001
-                        print(name, m, k, n, warps, stages, ctas, "ERR", e)
+                        print(name, m, k, n, cfg, "ERR", str(e)[:100])
                         continue
                     gbs = (nbytes + n * k * 4 + n * m * 4) / us / 1e3
-                    print("%-6s m=%5d k=%5d n=%d warps=%2d stages=%d ctas/sm=%d pdl=%d : %8.2f us  %7.1f GB/s" %
-                          (name, m, k, n, warps, stages, ctas, pdl, us, gbs), flush=True)
+                    print("%-6s m=%5d k=%5d n=%d %-55s: %8.2f us  %7.1f GB/s" % (name, m, k, n, cfg, us, gbs), flush=True)
             del ws
             torch.cuda.empty_cache()
 
