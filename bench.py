@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""bench.py -- the measurement contract for the quantized MUL_MAT hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one decode token's pass over the hot path: every quantized MUL_MAT of a Llama-shaped transformer
+(7 per layer + the output head) at batch 1, weights random-init in the GGUF block formats and resident in HBM.
+  * N = 1  : BASELINE.json configs[1], Llama-3-8B-shaped Q4_K_M (225 matmuls, 4.6 GB of weights per token).
+  * N > 1  : BASELINE.json configs[4], Llama-3-70B-shaped Q4_K_M, split-mode row: every weight's output rows are
+             sharded over the ranks (get_row_split rule) and the per-rank dst slices are all-gathered (NCCL) after each
+             matmul.  Strong scaling: the model is fixed, per-GPU work shrinks with N.
+value   = tokens/s with inputs resident in HBM (device-timed with CUDA events, max over ranks).
+e2e     = the same step through the host-buffer C-ABI call b200_mul_mat_host: activations start in pinned host
+          memory and results end there, per matmul (what the ggml scheduler does around a MUL_MAT-only backend).
+roofline= algorithmic bytes of the step's GEMV launches / their device time, against MEASURED_PEAKS.json hbm_gbs.
+cpu_baseline / --impl reference = the UNMODIFIED reference ggml-cpu backend (oracle/_ref, built by
+          oracle/Makefile.ref from /root/reference) on this host's cores, timed by oracle/_ref/ref-mulmat-bench.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+import zlib
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS = 2, 8, 12, 14, 23
+TNAME = {Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K", IQ4_XS: "iq4_xs"}
+BLOCK = {Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, IQ4_XS: 256}
+TSIZE = {Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, IQ4_XS: 136}
+
+MODELS = {
+    # name: n_layer, n_embd, n_ff, n_kv (= n_head_kv * head_dim), vocab, recipe
+    "llama3-8b-q4_k_m": dict(n_layer=32, n_embd=4096, n_ff=14336, n_kv=1024, vocab=128256, recipe="q4_k_m"),
+    "llama3-70b-q4_k_m": dict(n_layer=80, n_embd=8192, n_ff=28672, n_kv=1024, vocab=128256, recipe="q4_k_m"),
+    "llama2-7b-q4_0": dict(n_layer=32, n_embd=4096, n_ff=11008, n_kv=4096, vocab=32000, recipe="q4_0"),
+}
+
+
+def use_more_bits(i, n):
+    # src/llama-quant.cpp:129-131 of the reference
+    return i < n // 8 or i >= 7 * n // 8 or (i - n // 8) % 3 == 2
+
+
+def matmul_list(model):
+    """[(name, ggml_type, m, k)] in graph order for one token (llm_build_llama, src/llama-model.cpp:4408).
+    Q4_K_M recipe (src/llama-quant.cpp:166-168,235-236,291-297): attn_v and ffn_down are Q6_K in use_more_bits layers,
+    output.weight is Q6_K, everything else Q4_K (the 70B recipe's Q5_K attn_v is replaced by Q4_K: out of scope)."""
+    c = MODELS[model]
+    L, e, ff, kv, V = c["n_layer"], c["n_embd"], c["n_ff"], c["n_kv"], c["vocab"]
+    out = []
+    for i in range(L):
+        if c["recipe"] == "q4_k_m":
+            hi = Q6_K if use_more_bits(i, L) else Q4_K
+            base = Q4_K
+        else:
+            hi = base = Q4_0
+        out += [("attn_q.%d" % i, base, e, e), ("attn_k.%d" % i, base, kv, e), ("attn_v.%d" % i, hi, kv, e),
+                ("attn_output.%d" % i, base, e, e), ("ffn_gate.%d" % i, base, ff, e), ("ffn_up.%d" % i, base, ff, e),
+                ("ffn_down.%d" % i, hi, e, ff)]
+    out.append(("output", Q6_K, V, e))   # output.weight is Q6_K under both recipes (src/llama-quant.cpp:166-168)
+    return out
+
+
+def row_bytes(t, k):
+    return k // BLOCK[t] * TSIZE[t]
+
+
+def gemv_bytes(t, m, k, n):
+    """algorithmic bytes of one matmul: weights + f32 activations + f32 result"""
+    return m * row_bytes(t, k) + n * k * 4 + n * m * 4
+
+
+# ------------------------------------------------------------------------------------------------ reference (CPU) arm
+def host_threads():
+    try:
+        import psutil
+        phys = psutil.cpu_count(logical=False) or 0
+    except Exception:  # noqa: BLE001
+        phys = 0
+    avail = len(os.sched_getaffinity(0))
+    n = min(phys, avail) if phys else avail
+    return max(1, min(n, 512))
+
+
+def ref_specs(model):
+    agg = {}
+    for _, t, m, k in matmul_list(model):
+        agg[(t, m, k)] = agg.get((t, m, k), 0) + 1
+    return ["%s:%d:%d:%d" % (TNAME[t], m, k, c) for (t, m, k), c in agg.items()]
+
+
+def run_reference(model, steps, warmup, threads, copies=3):
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref-mulmat-bench")
+    if not os.path.exists(exe):
+        raise RuntimeError("oracle/_ref/ref-mulmat-bench missing: run __graft_entry__.build() where /root/reference exists")
+    cmd = [exe, "--threads", str(threads), "--steps", str(steps), "--warmup", str(warmup), "--n", "1", "--copies",
+           str(copies)] + ref_specs(model)
+    out = subprocess.run(cmd, check=True, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+    line = [ln for ln in out.splitlines() if ln.startswith("{")][-1]
+    return json.loads(line)
+
+
+def metric_name(model):
+    return "tg128 tok/s (%s-shaped, every quantized MUL_MAT of one decode token, batch 1)" % model
+
+
+def reference_arm(args, model):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = host_threads()
+    try:
+        r = run_reference(model, args.steps, args.warmup, threads)
+    except Exception as e:  # noqa: BLE001
+        print(json.dumps({"impl": "reference", "unavailable": str(e)[:200]}))
+        return
+    toks = 1e3 / r["ms_per_step"]
+    sample = "%d warm-up + %d timed tokens, each all %d MUL_MATs of %s, 3 weight copies per shape cycled" % (
+        args.warmup, args.steps, r["nodes"], model)
+    print(json.dumps({
+        "impl": "reference", "metric": metric_name(model), "value": toks, "unit": "tok/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "config": {"workload": model + " decode (ggml-cpu, %d threads)" % threads},
+        "cpu_baseline": {"value": toks, "unit": "tok/s", "cores": threads, "kind": "reference", "sample": sample,
+                         "weight_gbs": r["weight_gbs"]},
+        "e2e": {"value": toks, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop = [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # noqa: BLE001
+            self.nv = None
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop and self.nv is not None:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                bits = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for b, name in self.REASONS.items():
+                    if bits & b:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=1)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------ device weights
+def gen_weights(torch, t, rows, k, gen, device):
+    """random VALID blocks written directly in the quantized format on the device (same rule as
+    tests/qref.py:random_blocks): random payload bytes, sane finite fp16 scales"""
+    nb = rows * (k // BLOCK[t])
+    raw = torch.randint(0, 256, (nb, TSIZE[t]), dtype=torch.uint8, device=device, generator=gen)
+
+    def put(col, scale, signed):
+        v = (torch.rand(nb, device=device, generator=gen) * 0.9 + 0.1) * scale
+        if signed:
+            v = v * (torch.randint(0, 2, (nb,), device=device, generator=gen) * 2 - 1)
+        raw[:, col:col + 2] = v.to(torch.float16).view(torch.uint8).view(nb, 2)
+
+    if t == Q4_0:
+        put(0, 0.02 / 4, True)
+    elif t == Q8_0:
+        put(0, 0.02 / 64, True)
+    elif t == Q4_K:
+        put(0, 0.02 / 200, False)
+        put(2, 0.02 / 60, False)
+    elif t == Q6_K:
+        put(208, 0.02 / 2000, True)
+    elif t == IQ4_XS:
+        put(0, 0.02 / 2000, True)
+    return raw.view(rows, -1)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(MODELS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-pp", action="store_true", help="skip the pp512 leg")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    model = args.workload or ("llama3-8b-q4_k_m" if max(world, args.gpus) == 1 else "llama3-70b-q4_k_m")
+
+    if args.impl == "reference":
+        return reference_arm(args, model)
+
+    import torch
+    import b200pkg
+    qmm = b200pkg.load()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    assert qmm.lib().b200_device_ok(local_rank) == 1, "not an sm_100 device"
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    mms = matmul_list(model)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234)          # same weights on every rank before slicing
+    n = 1
+    # ---- weights: this rank's row slice of every matrix, resident in HBM
+    weights, slices = [], []
+    for name, t, m, k in mms:
+        lo, hi = qmm.row_split(m, world, rank)
+        full_rows = m
+        # generate only this rank's slice (seeded per matrix so that slices are reproducible)
+        g = torch.Generator(device=dev)
+        g.manual_seed(zlib.crc32(("%s/%d" % (name, rank)).encode()))
+        weights.append(gen_weights(torch, t, hi - lo, k, g, dev) if hi > lo else None)
+        slices.append((lo, hi, full_rows))
+    ks = sorted({k for _, _, _, k in mms})
+    xs = {k: torch.rand((n, k), device=dev, generator=gen) * 2 - 1 for k in ks}
+    # results: one buffer per distinct m; in row-split mode each rank writes its slice and the slices are gathered
+    maxrows = {m: max(qmm.row_split(m, world, r)[1] - qmm.row_split(m, world, r)[0] for r in range(world))
+               for _, _, m, _ in mms}
+    out_local = {m: torch.zeros((n, maxrows[m]), device=dev) for m in maxrows}
+    out_full = {m: torch.zeros((world, n, maxrows[m]), device=dev) for m in maxrows} if world > 1 else None
+
+    def token_step():
+        for (name, t, m, k), w, (lo, hi, _) in zip(mms, weights, slices):
+            if w is not None:
+                qmm.mul_mat(t, w, xs[k], hi - lo, k, out=out_local[m][:, :hi - lo])
+            if world > 1:
+                dist.all_gather_into_tensor(out_full[m], out_local[m])
+
+    step_bytes = sum(gemv_bytes(t, hi - lo, k, n) for (_, t, _, k), (lo, hi, _) in zip(mms, slices) if hi > lo)
+    total_bytes_all_ranks = sum(gemv_bytes(t, m, k, n) for _, t, m, k in mms)
+
+    # ---- warm-up (eager), count launches per step
+    before = qmm.launch_count()
+    token_step()
+    torch.cuda.synchronize()
+    launches_per_step = qmm.launch_count() - before
+    for _ in range(2):
+        token_step()
+    torch.cuda.synchronize()
+
+    stream = torch.cuda.Stream(device=dev)
+    use_graph = not args.no_graph and world == 1
+    if use_graph:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(stream):
+            token_step()
+            stream.synchronize()
+            with torch.cuda.graph(graph, stream=stream):
+                token_step()
+        run = graph.replay
+    else:
+        run = token_step
+
+    def timed(fn, steps, warmup):
+        with torch.cuda.stream(stream):
+            for _ in range(warmup):
+                fn()
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+                torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(steps):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+                torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            tms = torch.tensor([ms], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = float(tms.item())
+        return ms / steps
+
+    with ClockSampler(local_rank) as clk:
+        ms_step = timed(run, args.steps, args.warmup)
+        # make sure the sampler saw the loaded state even for very short runs
+        t_end = time.time() + 0.3
+        while len(clk.samples) < 8 and time.time() < t_end:
+            run()
+        torch.cuda.synchronize()
+    clocks = clk.summary()
+    ms_eager = timed(token_step, max(4, args.steps // 8), 3) if use_graph else ms_step
+
+    # ---- e2e: host buffers, per-matmul H2D -> kernel -> D2H through b200_mul_mat_host (rank-local slice)
+    hx = {k: xs[k].cpu().pin_memory() for k in ks}
+    hout = {m: torch.zeros((n, maxrows[m])).pin_memory() for m in maxrows}
+    h2d = sum(n * k * 4 for (_, _, _, k), w in zip(mms, weights) if w is not None)
+    d2h = sum(n * (hi - lo) * 4 for (lo, hi, _), w in zip(slices, weights) if w is not None)
+
+    def token_step_host():
+        for (name, t, m, k), w, (lo, hi, _) in zip(mms, weights, slices):
+            if w is not None:
+                dst = hout[m] if hi - lo == maxrows[m] else hout[m][:, :hi - lo].contiguous()
+                qmm.mul_mat_host(t, w, hx[k], dst, hi - lo, k)
+        torch.cuda.current_stream().synchronize()   # the caller reads the results of this token on the host
+
+    e2e = None
+    if world == 1:
+        ms_e2e = timed(token_step_host, max(8, args.steps // 4), 3)
+        e2e = {"value": 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": ms_e2e, "api": "b200_mul_mat_host per MUL_MAT (pinned host x -> H2D -> GEMV -> D2H), "
+               "stream sync once per token"}
+    else:
+        # row-split: host activations are broadcast to every rank's device, the gathered result is read back on rank 0
+        def token_step_host_split():
+            for k in ks:
+                xs[k].copy_(hx[k], non_blocking=True)
+            token_step()
+            for m in maxrows:
+                hout[m].copy_(out_full[m][0], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        ms_e2e = timed(token_step_host_split, max(8, args.steps // 4), 3)
+        e2e = {"value": 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": sum(n * k * 4 for k in ks),
+               "d2h_bytes_per_step": sum(n * maxrows[m] * 4 for m in maxrows), "ms_per_step": ms_e2e,
+               "api": "pinned host activations -> H2D once per token -> row-split matmuls + all_gather -> D2H"}
+
+    # ---- pp512 leg (prefill): the same matmuls at n = 512 (output head at n = 1, as llama does for the last token)
+    pp = None
+    if not args.no_pp and world == 1:
+        npp = 512
+        xpp = {k: torch.rand((npp, k), device=dev, generator=gen) * 2 - 1 for k in ks}
+        opp = {m: torch.empty((npp, m), device=dev) for _, _, m, _ in mms[:-1]}
+
+        def prefill_step():
+            for (name, t, m, k), w in zip(mms[:-1], weights[:-1]):
+                qmm.mul_mat(t, w, xpp[k], m, k, out=opp[m])
+            name, t, m, k = mms[-1]
+            qmm.mul_mat(t, weights[-1], xs[k], m, k, out=out_local[m])
+
+        b0 = qmm.launch_count()
+        prefill_step()
+        torch.cuda.synchronize()
+        pp_launches = qmm.launch_count() - b0
+        ms_pp = timed(prefill_step, 3, 1)
+        flops = sum(2.0 * m * k * npp for _, _, m, k in mms[:-1])
+        pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 3,
+              "int8_tops": flops / ms_pp / 1e9, "launches_per_step": pp_launches}
+
+    # ---- cpu baseline (rank 0, N = 1 only): the unmodified reference ggml-cpu on this host
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        threads = host_threads()
+        try:
+            probe = run_reference(model, 2, 1, threads)
+            steps_cpu = int(max(4, min(200, 15e3 / probe["ms_per_step"])))
+            r = run_reference(model, steps_cpu, 1, threads)
+            cpu = {"value": 1e3 / r["ms_per_step"], "unit": "tok/s", "cores": threads, "kind": "reference",
+                   "sample": "%d timed tokens (1 warm-up), each all %d MUL_MATs of %s on ggml-cpu, 3 weight copies per "
+                             "shape cycled" % (steps_cpu, r["nodes"], model),
+                   "ms_per_step": r["ms_per_step"], "weight_gbs": r["weight_gbs"]}
+        except Exception as e:  # noqa: BLE001
+            cpu = {"value": None, "unit": "tok/s", "cores": threads, "kind": "reference", "sample": "failed: " + str(e)[:160]}
+
+    if rank == 0:
+        peak, how = peaks()
+        achieved = step_bytes / ms_step / 1e6   # GB/s per GPU (rank 0's slice)
+        line = {
+            "metric": metric_name(model), "value": 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": model + (" decode, split-mode row over %d GPUs + NCCL all-gather" % world if world > 1
+                                            else " decode"),
+                       "matmuls_per_step": len(mms), "batch": n, "l2": "inputs_exceed_l2 (%.2f GB of weights streamed "
+                       "per step per GPU)" % (sum(w.numel() for w in weights if w is not None) / 1e9),
+                       "launch": "cuda_graph_replay" if use_graph else "eager"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": how, "kernel": "k_gemv (all GEMV launches of the step)",
+                         "algorithmic_bytes_per_step": step_bytes, "launches_per_step": launches_per_step},
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks,
+            "ms_per_step_eager": ms_eager,
+            "pp512": pp,
+            "algorithmic_bytes_per_token_all_gpus": total_bytes_all_ranks,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

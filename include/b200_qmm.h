@@ -120,6 +120,22 @@ B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, con
                              float * dst, int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                              size_t workspace_bytes, b200_stream_t stream);
 
+/*
+ * Same product with HOST activations and a HOST result: the activations are copied host->device, the matmul runs, and
+ * dst is copied device->host, all stream-ordered on `stream` (the caller synchronizes the stream before reading dst).
+ * This is what the ggml scheduler does around a MUL_MAT node whose inputs live in a CPU buffer: copy the split inputs
+ * to the backend (ggml_backend_sched_compute_splits, ggml/src/ggml-backend.cpp:1363-1396, landing in
+ * ggml_backend_cuda_set_tensor_async, ggml/src/ggml-cuda/ggml-cuda.cu:2386-2393), graph_compute, then
+ * ggml_backend_cuda_get_tensor_async (:2395-2402).  Weights stay device-resident as in a ggml weight buffer
+ * (set once through buffer.set_tensor, ggml-cuda.cu:576-582).  bench.py's `e2e` figure is measured through this call.
+ *   x_host / dst_host   host memory, packed [n][k] / [n][m]; pinned memory makes the copies truly asynchronous
+ *   workspace           device scratch of at least b200_mul_mat_host_workspace_size() bytes, 256-byte aligned
+ */
+B200_API size_t b200_mul_mat_host_workspace_size(int type, int64_t m, int64_t n, int64_t k);
+B200_API int    b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const float * x_host,
+                                  float * dst_host, int64_t m, int64_t n, int64_t k, void * workspace,
+                                  size_t workspace_bytes, b200_stream_t stream);
+
 /* ---- MUL_MAT_ID ------------------------------------------------------------------------------------------------ */
 
 /*

@@ -180,6 +180,33 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
     return B200_OK;
 }
 
+static size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
+
+size_t b200_mul_mat_host_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
+    if (!weight_type(type) || m < 0 || n < 0 || k < 0) return 0;
+    return align256((size_t) n * k * 4) + align256((size_t) n * m * 4) + align256(b200_mul_mat_workspace_size(type, m, n, k));
+}
+
+int b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const float * x_host, float * dst_host, int64_t m,
+                      int64_t n, int64_t k, void * workspace, size_t workspace_bytes, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (!weight_type(type)) return B200_ERR_TYPE;
+    if (m < 0 || n < 0 || k < 0) return B200_ERR_SHAPE;
+    if (m == 0 || n == 0) return B200_OK;
+    const size_t need = b200_mul_mat_host_workspace_size(type, m, n, k);
+    if (!workspace || workspace_bytes < need) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
+    float * x_dev   = (float *) workspace;
+    float * dst_dev = (float *) ((uint8_t *) workspace + align256((size_t) n * k * 4));
+    void *  ws      = (uint8_t *) dst_dev + align256((size_t) n * m * 4);
+    if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
+    const int st = b200_mul_mat(type, W, w_row_stride, x_dev, k, dst_dev, m, m, n, k, ws,
+                                b200_mul_mat_workspace_size(type, m, n, k), stream_);
+    if (st != B200_OK) return st;
+    B200_CUDA_TRY(cudaMemcpyAsync(dst_host, dst_dev, (size_t) n * m * 4, cudaMemcpyDeviceToHost, stream));
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------------------- MUL_MAT_ID
 size_t b200_mul_mat_id_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
                                       int64_t n_tokens) {

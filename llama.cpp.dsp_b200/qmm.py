@@ -22,7 +22,7 @@ EXPORTS = [
     "b200_qmm_abi_version", "b200_status_string", "b200_last_cuda_error", "b200_device_ok", "b200_sm_count",
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
-    "b200_mul_mat", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
+    "b200_mul_mat", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_fused", "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
 ]
 
@@ -64,6 +64,9 @@ def lib():
     L.b200_mul_mat_workspace_size.restype = sz
     L.b200_mul_mat_workspace_size.argtypes = [i32, i64, i64, i64]
     L.b200_mul_mat.argtypes = [i32, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
+    L.b200_mul_mat_host_workspace_size.restype = sz
+    L.b200_mul_mat_host_workspace_size.argtypes = [i32, i64, i64, i64]
+    L.b200_mul_mat_host.argtypes = [i32, vp, i64, vp, vp, i64, i64, i64, vp, sz, vp]
     L.b200_mul_mat_id_workspace_size.restype = sz
     L.b200_mul_mat_id_workspace_size.argtypes = [i32, i64, i64, i64, i64, i64]
     L.b200_mul_mat_id.argtypes = [i32, vp, i64, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp,
@@ -179,6 +182,20 @@ def mul_mat(t, w, x, m, k, out=None, stream=None):
     check(lib().b200_mul_mat(t, w.data_ptr(), 0, x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
                              dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
     return dst
+
+
+def mul_mat_host(t, w, x_host, dst_host, m, k, stream=None):
+    """w: uint8 cuda (device-resident weights); x_host [n, k] / dst_host [n, m]: f32 HOST tensors (pin them for truly
+    asynchronous copies).  Stream-ordered H2D -> matmul -> D2H; synchronize the stream before reading dst_host."""
+    _require_cuda(w)
+    if x_host.is_cuda or dst_host.is_cuda:
+        raise B200Error("mul_mat_host takes host activations / results")
+    n = x_host.shape[0]
+    assert x_host.is_contiguous() and dst_host.is_contiguous() and tuple(dst_host.shape) == (n, m)
+    ws, wsz = _workspace(w.device, lib().b200_mul_mat_host_workspace_size(t, m, n, k))
+    check(lib().b200_mul_mat_host(t, w.data_ptr(), 0, x_host.data_ptr(), dst_host.data_ptr(), m, n, k, ws, wsz,
+                                  _stream_ptr(stream)))
+    return dst_host
 
 
 def mul_mat_id(t, w, b, ids, m, k, n_expert, out=None, stream=None):
