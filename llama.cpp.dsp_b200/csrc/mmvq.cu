@@ -28,6 +28,12 @@
 namespace b200 {
 
 __device__ __forceinline__ int dp4a(uint32_t a, uint32_t b, int c) { return __dp4a((int) a, (int) b, c); }
+// unsigned bytes of a  x  signed bytes of b (the high nibbles of packed 4-bit weights are used in place, as 16 * q)
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // ------------------------------------------------------------------------------------------------ q8_1 unit in registers
 // One unit = 64 consecutive weights of a row as the weight format groups them:
@@ -210,9 +216,9 @@ __device__ __forceinline__ void unit_dot(uint32_t row, int ug, int k32, const q8
         const int   sc0 = sc2 & 0xff, sc1 = sc2 >> 8;
         const float mn0 = (float) (mn2 & 0xff), mn1 = (float) (mn2 >> 8);
         const uint32_t v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-        uint32_t lo[8], hi[8];
+        uint32_t lo[8], hi[8];  // hi keeps the nibbles in place (16 * q): the exact >> 4 is applied to the dot product
 #pragma unroll
-        for (int i = 0; i < 8; i++) lo[i] = v[i] & 0x0F0F0F0Fu, hi[i] = (v[i] >> 4) & 0x0F0F0F0Fu;
+        for (int i = 0; i < 8; i++) lo[i] = v[i] & 0x0F0F0F0Fu, hi[i] = v[i] & 0xF0F0F0F0u;
 #pragma unroll
         for (int c = 0; c < NCOLS; c++) {
             int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
@@ -220,10 +226,10 @@ __device__ __forceinline__ void unit_dot(uint32_t row, int ug, int k32, const q8
             for (int i = 0; i < 4; i++) {
                 a0 = dp4a(lo[i], u[c].q[i], a0);
                 a1 = dp4a(lo[4 + i], u[c].q[4 + i], a1);
-                b0 = dp4a(hi[i], u[c].q[8 + i], b0);
-                b1 = dp4a(hi[4 + i], u[c].q[12 + i], b1);
+                b0 = dp4a_us(hi[i], u[c].q[8 + i], b0);
+                b1 = dp4a_us(hi[4 + i], u[c].q[12 + i], b1);
             }
-            const float s = u[c].d[0] * (float) (sc0 * (a0 + a1)) + u[c].d[1] * (float) (sc1 * (b0 + b1));
+            const float s = u[c].d[0] * (float) (sc0 * (a0 + a1)) + u[c].d[1] * (float) (sc1 * ((b0 + b1) >> 4));
             const float t = u[c].s[0] * mn0 + u[c].s[1] * mn1;
             out[c] = d * s - dmin * t;
         }
@@ -278,13 +284,13 @@ __device__ __forceinline__ void unit_dot(uint32_t row, int ug, int k32, const q8
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 a0 = dp4a(v0[i] & 0x0F0F0F0Fu, u[c].q[i], a0);
-                a1 = dp4a((v0[i] >> 4) & 0x0F0F0F0Fu, u[c].q[4 + i], a1);
+                a1 = dp4a_us(v0[i] & 0xF0F0F0F0u, u[c].q[4 + i], a1);   // 16 * high nibbles
                 b0 = dp4a(v1[i] & 0x0F0F0F0Fu, u[c].q[8 + i], b0);
-                b1 = dp4a((v1[i] >> 4) & 0x0F0F0F0Fu, u[c].q[12 + i], b1);
+                b1 = dp4a_us(v1[i] & 0xF0F0F0F0u, u[c].q[12 + i], b1);
             }
             // sum (q - 8) * y = sum q*y - 8 * sum y
-            out[c] = d0 * (u[c].d[0] * (float) (a0 + a1) - 8.0f * u[c].s[0]) +
-                     d1 * (u[c].d[1] * (float) (b0 + b1) - 8.0f * u[c].s[1]);
+            out[c] = d0 * (u[c].d[0] * (float) (a0 + (a1 >> 4)) - 8.0f * u[c].s[0]) +
+                     d1 * (u[c].d[1] * (float) (b0 + (b1 >> 4)) - 8.0f * u[c].s[1]);
         }
     } else if (TYPE == B200_TYPE_Q8_0) {
         // two 34-byte blocks = 68 bytes, 2-byte aligned
@@ -353,6 +359,13 @@ __device__ __forceinline__ void unit_dot(uint32_t row, int ug, int k32, const q8
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
+// Work decomposition inside a CTA:
+//   lane  = one 64-element unit of k (fixed for the whole kernel: its q8_1 activations stay in registers)
+//   warp  = one "chunk" of 32 consecutive units (2048 elements of k)
+//   team  = the T = ceil(units_per_row / 32) warps that together cover a whole row
+//   stage = V consecutive rows (V = 4 or 8), one TMA transaction, owned by team (stage % nteams)
+// so teams work on different stages concurrently and every compute warp runs V unit-dots back to back, then ONE
+// transposing butterfly (V values x 32 lanes -> one row sum per lane group) instead of a shuffle tree per row.
 struct gemv_kargs {
     const uint8_t * W;
     int64_t         w_row_stride, w_expert_stride;
@@ -362,12 +375,11 @@ struct gemv_kargs {
     float *         dst;
     int64_t         dst_col_stride;
     int             m, k;
-    int             nst;          // ring depth
-    int             R;            // rows per stage (multiple of rows-per-iteration, <= 32)
-    int             lpr_log2;     // log2(lanes per row): each warp covers 2^lpr_log2 units of k
-    int             nwc;          // compute warps = ceil(units_per_row / lanes_per_row)
+    int             nst;          // ring depth (>= nteams)
+    int             T;            // warps per team
+    int             nteams;       // teams per CTA
     int             row_pitch;    // bytes between rows inside a stage
-    int             stage_bytes;  // R * row_pitch + slack, multiple of 128
+    int             stage_bytes;  // V * row_pitch + slack, multiple of 128
     const int32_t * ids;
     int64_t         ids_row_stride;
     int             n_used, ne11;
@@ -382,23 +394,56 @@ struct gemv_peers {
     int32_t   epoch;
 };
 
-constexpr int GEMV_MAX_R = 32;
+// Sum V per-lane values over the 32 lanes of a warp with log2(V) exchange steps + the remaining plain steps.
+// On return p[0] holds the warp-wide sum of row `butterfly_row<V>(lane)`; lanes with (lane & (32/V - 1)) == 0 write it.
+template <int V>
+__device__ __forceinline__ void butterfly_rows(float (&p)[V], int lane) {
+    static_assert(V == 4 || V == 8, "V");
+    int mask = 16;
+#pragma unroll
+    for (int n = V / 2; n >= 1; n >>= 1) {
+        const bool up = (lane & mask) != 0;
+#pragma unroll
+        for (int i = 0; i < n; i++) {
+            const float send = up ? p[i] : p[i + n];
+            const float keep = up ? p[i + n] : p[i];
+            p[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
+        }
+        mask >>= 1;
+    }
+#pragma unroll
+    for (; mask >= 1; mask >>= 1) p[0] += __shfl_xor_sync(0xffffffffu, p[0], mask);
+}
+template <int V>
+__device__ __forceinline__ int butterfly_row(int lane) {
+    return V == 8 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
+                  : (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1));
+}
 
-template <int TYPE, int NCOLS, int MINB, bool PEERS>
-__global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv_kargs a, const gemv_peers peers) {
+// Launch shapes: MINB = 2 -> 8 compute warps, two CTAs per SM (<= 112 registers): 1-2 columns, rows of <= 16384.
+//                MINB = 1 -> 3-4 columns: 8 compute warps, one CTA per SM (registers for 4 x 24 activation words);
+//                            1-2 columns: 16 compute warps, one CTA per SM (rows longer than 16384 elements).
+template <int NCOLS, int MINB> struct gemv_shape {
+    static constexpr int NW = (MINB == 2 || NCOLS > 2) ? 8 : 16;
+    static constexpr int THREADS = (NW + 1) * 32;
+};
+
+template <int TYPE, int NCOLS, int V, int MINB>
+__global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, MINB) k_gemv(const gemv_kargs a,
+                                                                                  const gemv_peers peers) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int BYTES = qtraits<TYPE>::bytes;
     constexpr int BLCK  = qtraits<TYPE>::blck;
+    constexpr int NW    = gemv_shape<NCOLS, MINB>::NW;          // compute warps; warp NW is the producer/epilogue warp
 
     const int  lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int  nwc = a.nwc, nst = a.nst, R = a.R;
-    const bool producer = warp == nwc;                          // the last warp issues TMA and writes results
+    const int  nst = a.nst, T = a.T, nteams = a.nteams;
 
-    // shared memory: [stages: nst * stage_bytes][partials: nst * 2 * NCOLS * R * nwc floats][full bars][empty bars]
-    const uint32_t sm_stage = smem_u32(smem);
-    float *        partial  = reinterpret_cast<float *>(smem + (size_t) nst * a.stage_bytes);
-    const int      part_sz  = NCOLS * R * nwc;                  // floats per (slot, parity)
-    const uint32_t bar_full = smem_u32(partial) + (uint32_t) nst * 2 * part_sz * 4;
+    // shared memory: [stages: nst * stage_bytes][partials: nst * 2 * NCOLS * V * T floats][full bars][empty bars]
+    const uint32_t sm_stage  = smem_u32(smem);
+    float *        partial   = reinterpret_cast<float *>(smem + (size_t) nst * a.stage_bytes);
+    const int      part_sz   = NCOLS * V * T;                   // floats per (slot, parity)
+    const uint32_t bar_full  = smem_u32(partial) + (uint32_t) nst * 2 * part_sz * 4;
     const uint32_t bar_empty = bar_full + 8 * nst;
 
     const uint8_t * W   = a.W;
@@ -414,28 +459,27 @@ __global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv
     }
 
     // this CTA's rows and stages
-    const int r_begin = (int) ((int64_t) blockIdx.x * a.m / gridDim.x);
-    const int r_end   = (int) ((int64_t) (blockIdx.x + 1) * a.m / gridDim.x);
-    const int nrows   = r_end - r_begin;
-    const int nstages = (nrows + R - 1) / R;
-    const int row_bytes = a.k / BLCK * BYTES;
+    const int  r_begin   = (int) ((int64_t) blockIdx.x * a.m / gridDim.x);
+    const int  r_end     = (int) ((int64_t) (blockIdx.x + 1) * a.m / gridDim.x);
+    const int  nstages   = (r_end - r_begin + V - 1) / V;
+    const int  row_bytes = a.k / BLCK * BYTES;
     const bool contiguous = a.w_row_stride == row_bytes;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nst; s++) {
             mbar_init(bar_full + 8 * s, 1);
-            mbar_init(bar_empty + 8 * s, nwc);
+            mbar_init(bar_empty + 8 * s, T);
         }
         mbar_fence_init();
     }
     __syncthreads();
     pdl_launch_dependents();
 
-    if (producer) {
+    if (warp == NW) {
         // ---------------------------------------------------------------------------------------- TMA + epilogue warp
         auto issue = [&](int st) {  // all lanes call; stage st -> slot st % nst
             const int      slot = st % nst;
-            const int      r0 = r_begin + st * R, nr = min(R, r_end - r0);
+            const int      r0 = r_begin + st * V, nr = min(V, r_end - r0);
             const uint32_t dstb = sm_stage + slot * a.stage_bytes;
             const uint32_t bar  = bar_full + 8 * slot;
             if (a.dbg == 2) {
@@ -464,21 +508,19 @@ __global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv
                 if (lane < nr) tma_load_1d(dstb + lane * a.row_pitch, (const void *) g0, span, bar);
             }
         };
-        auto finish = [&](int st) {  // sum the per-warp partials of stage st in a fixed order and write the outputs
+        // lane l sums the T per-warp partials of (column l / V, row l % V) in a fixed order: deterministic results
+        const int fv = lane % V, fc = lane / V;
+        auto finish = [&](int st) {
             const int slot = st % nst, par = (st / nst) & 1;
-            const int r0 = r_begin + st * R, nr = min(R, r_end - r0);
-            const float * p = partial + (size_t) (slot * 2 + par) * part_sz;
-            if (lane < nr) {
-#pragma unroll
-                for (int c = 0; c < NCOLS; c++) {
-                    float v = 0.f;
-                    for (int w = 0; w < nwc; w++) v += p[(c * R + lane) * nwc + w];
-                    if (PEERS) {
-                        for (int r = 0; r < a.world; r++)
-                            peers.dst[r][c * a.dst_col_stride + a.row_offset + r0 + lane] = v;
-                    } else {
-                        dst[c * a.dst_col_stride + r0 + lane] = v;
-                    }
+            const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
+            if (fc < NCOLS && fv < nr) {
+                const float * p = partial + (size_t) (slot * 2 + par) * part_sz + (fc * V + fv) * T;
+                float v = 0.f;
+                for (int w = 0; w < T; w++) v += p[w];
+                if (a.world > 1) {
+                    for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
+                } else {
+                    dst[fc * a.dst_col_stride + r0 + fv] = v;
                 }
             }
         };
@@ -487,11 +529,11 @@ __global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv
         pdl_wait();                                             // dst may still be read by the previous kernel
         for (int st = 0; st < nstages; st++) {
             const int slot = st % nst;
-            mbar_wait(bar_empty + 8 * slot, (st / nst) & 1);    // all compute warps are done with stage st
+            mbar_wait(bar_empty + 8 * slot, (st / nst) & 1);    // the owning team is done with stage st
             if (st + nst < nstages) issue(st + nst);            // refill first, then reduce
             finish(st);
         }
-        if (PEERS) {
+        if (a.world > 1) {
             __syncwarp();
             if (lane == 0) {
                 __threadfence_system();
@@ -502,12 +544,11 @@ __global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv
     }
 
     // -------------------------------------------------------------------------------------------- compute warps
-    const int lpr   = 1 << a.lpr_log2;                          // lanes per row
-    const int rpi   = 32 >> a.lpr_log2;                         // rows per warp iteration
-    const int ug    = warp * lpr + (lane & (lpr - 1));          // this lane's unit of k, fixed for the whole kernel
-    const int rsub  = lane >> a.lpr_log2;
-    const int k32   = a.k / 32;
-    const int upr   = (a.k + 63) / 64;                          // units per row
+    const int team = warp / T, wt = warp - team * T;
+    if (team >= nteams) return;                                 // spare warps (NW not a multiple of T)
+    const int  ug   = wt * 32 + lane;                           // this lane's unit of k, fixed for the whole kernel
+    const int  k32  = a.k / 32;
+    const int  upr  = (a.k + 63) / 64;                          // units per row
     const bool have = ug < upr;
 
     pdl_wait();
@@ -532,33 +573,35 @@ __global__ void __launch_bounds__(MINB == 2 ? 288 : 544, MINB) k_gemv(const gemv
         }
     }
 
-    for (int st = 0; st < nstages; st++) {
+    const int      brow  = butterfly_row<V>(lane);
+    const bool     bwrite = (lane & (32 / V - 1)) == 0;
+    const uint32_t row_step = contiguous ? (uint32_t) row_bytes : (uint32_t) a.row_pitch;
+    for (int st = team; st < nstages; st += nteams) {
         const int slot = st % nst, par = (st / nst) & 1;
-        const int r0 = st * R, nr = min(R, nrows - r0);
+        const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
         mbar_wait(bar_full + 8 * slot, par);
-        const uint32_t stage = sm_stage + slot * a.stage_bytes;
-        float * p = partial + (size_t) (slot * 2 + par) * part_sz;
-        for (int rr = rsub; rr < R; rr += rpi) {
+        // first row's address inside the stage (the bulk copy started at the 16-byte boundary below the row)
+        uint32_t rowa = sm_stage + slot * a.stage_bytes;
+        if (contiguous) rowa += (uint32_t) ((uint64_t) (W + (int64_t) r0 * row_bytes) & 15);
+        float acc[NCOLS][V];
+#pragma unroll
+        for (int v = 0; v < V; v++) {
             float out[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
-            if (have && rr < nr && a.dbg != 1) {
-                uint32_t rowa;
-                if (contiguous) {
-                    const uint32_t off = (uint32_t) ((uint64_t) (W + (int64_t) (r_begin + r0) * row_bytes) & 15);
-                    rowa = stage + off + rr * row_bytes;
-                } else {
-                    const uint32_t off = (uint32_t) ((uint64_t) (W + (int64_t) (r_begin + r0 + rr) * a.w_row_stride) & 15);
-                    rowa = stage + rr * a.row_pitch + off;
-                }
-                unit_dot<TYPE, NCOLS>(rowa, ug, k32, u, out);
+            if (have && v < nr && a.dbg != 1) {
+                uint32_t ra = rowa + v * row_step;
+                if (!contiguous) ra += (uint32_t) ((uint64_t) (W + (int64_t) (r0 + v) * a.w_row_stride) & 15);
+                unit_dot<TYPE, NCOLS>(ra, ug, k32, u, out);
             }
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) {
-                float v = out[c];
-                for (int o = lpr >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if ((lane & (lpr - 1)) == 0 && rr < nr) p[(c * R + rr) * nwc + warp] = v;
-            }
+            for (int c = 0; c < NCOLS; c++) acc[c][v] = out[c];
+        }
+        float * p = partial + (size_t) (slot * 2 + par) * part_sz;
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            butterfly_rows<V>(acc[c], lane);
+            if (bwrite) p[(c * V + brow) * T + wt] = acc[c][0];
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + 8 * slot);       // release: partials visible to the epilogue warp
@@ -572,7 +615,7 @@ static int env_int(const char * name, int dflt) {
 }
 
 struct gemv_plan {
-    int lpr_log2, nwc, R, nst, row_pitch, stage_bytes, minb;
+    int T, nteams, V, nst, row_pitch, stage_bytes, minb;
     size_t smem;
 };
 
@@ -592,43 +635,43 @@ static constexpr size_t SMEM_2CTA = 112 * 1024;   // two CTAs (+1 KB reserved ea
 static constexpr size_t SMEM_1CTA = 226 * 1024;
 static constexpr int    WARPS_2CTA = 8, WARPS_1CTA = 16;   // compute warps (one more warp is the producer)
 
-// Choose the k split, stage geometry and ring depth.  Returns false if the shape cannot be planned
-// (k > 32768: more than one unit per lane would be needed).
-static bool make_plan(int type, int64_t k, int ncols, bool contiguous, gemv_plan & P) {
+// Choose team size, rows per stage and ring depth.  `rows_per_cta` steers V: short slabs take V = 4 so that every
+// team of the CTA gets a stage.  Returns false if the shape cannot be planned (k > 32768: T would exceed 16 warps).
+static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t rows_per_cta, gemv_plan & P) {
     const int upr = (int) ((k + 63) / 64);
-    int lg = 2;
-    while (lg < 5 && (upr + (1 << lg) - 1) / (1 << lg) > WARPS_2CTA) lg++;
-    lg = env_int("B200_GEMV_LPR_LOG2", lg);
-    if (lg < 0 || lg > 5) return false;
-    const int nwc = (upr + (1 << lg) - 1) / (1 << lg);
-    if (nwc > WARPS_1CTA) return false;
-    P.minb = (nwc > WARPS_2CTA || ncols > 2) ? 1 : 2;           // 24 registers of activations per column
+    const int T   = (upr + 31) / 32;
+    if (T > (ncols > 2 ? WARPS_2CTA : WARPS_1CTA)) return false;
+    P.T = T;
+    P.minb = (T > WARPS_2CTA || ncols > 2) ? 1 : 2;             // 24 registers of activations per column
     P.minb = env_int("B200_GEMV_MINB", P.minb);
-    if (nwc > WARPS_2CTA) P.minb = 1;
-    P.lpr_log2 = lg, P.nwc = nwc;
-    const int rpi = 32 >> lg;
+    if (T > WARPS_2CTA || ncols > 2) P.minb = 1;
     const int row_bytes = (int) (k / type_block_elems(type)) * type_block_bytes(type);
     P.row_pitch = contiguous ? row_bytes : ((row_bytes + 15 + 15) & ~15);
-    const int target = env_int("B200_GEMV_STAGE_KB", 32) * 1024;
-    const int want   = env_int("B200_GEMV_STAGES", 4);
+    const int want = env_int("B200_GEMV_STAGES", 0);
     for (;;) {
+        const int    nw     = (P.minb == 2 || ncols > 2) ? WARPS_2CTA : WARPS_1CTA;
         const size_t budget = P.minb == 2 ? SMEM_2CTA : SMEM_1CTA;
-        int R = target / P.row_pitch / rpi * rpi;
-        if (R < rpi) R = rpi;
-        if (R > GEMV_MAX_R) R = GEMV_MAX_R / rpi * rpi;
-        for (; R >= rpi; R -= rpi) {
+        P.nteams = nw / T;
+        int vfirst = (rows_per_cta >= (int64_t) P.nteams * 8 && (size_t) 8 * P.row_pitch <= 40 * 1024) ? 8 : 4;
+        vfirst = env_int("B200_GEMV_V", vfirst);
+        for (int V = vfirst; V >= 4; V -= 4) {
             // payload + 15 bytes of leading misalignment + 16 so word reads of a 2-byte-aligned tail stay inside
-            P.stage_bytes = (R * P.row_pitch + 15 + 16 + 127) & ~127;
-            const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * R * nwc * 4 + 16;
+            P.stage_bytes = (V * P.row_pitch + 15 + 16 + 127) & ~127;
+            const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * V * T * 4 + 16;
             int nst = (int) (budget / per_stage);
-            if (nst > want) nst = want;
-            if (nst >= 2 || (R == rpi && nst >= 1)) {
-                P.nst = nst, P.R = R, P.smem = (size_t) nst * per_stage;
+            const int cap = want > 0 ? want : (P.nteams * 2 > 4 ? P.nteams * 2 : 4);
+            if (nst > cap) nst = cap;
+            if (nst >= 2 || (V == 4 && nst >= 1)) {
+                int nteams = P.nteams < nst ? P.nteams : nst;   // a team needs a slot of its own ...
+                nst -= nst % nteams;                            // ... and keeps it: slot s is always used by team
+                                                                // s % nteams, so no warp can run a full mbarrier
+                                                                // phase ahead of the slot's previous user
+                P.nteams = nteams, P.nst = nst, P.V = V, P.smem = (size_t) nst * per_stage;
                 return true;
             }
         }
         if (P.minb == 1) return false;
-        P.minb = 1;                                             // one row does not fit in half an SM: take all of it
+        P.minb = 1;                                             // 4 rows do not fit in half an SM: take all of it
     }
 }
 
@@ -637,20 +680,16 @@ size_t gemv_q8_smem_bytes(int64_t k, int ncols) { (void) k, (void) ncols; return
 int gemv_max_cols(int type, int64_t k) {
     gemv_plan P;
     for (int n = 4; n >= 1; n--)
-        if (make_plan(type, k, n, true, P)) return n;
+        if (make_plan(type, k, n, true, 1 << 20, P)) return n;
     return 0;
 }
 
-template <int TYPE, int NCOLS, int MINB, bool PEERS>
-static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, cudaStream_t stream) {
-    static int  sm_count = 0;
+static int g_sm_count = 0;
+
+template <int TYPE, int NCOLS, int V, int MINB>
+static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaStream_t stream) {
     static bool attr_set = false;
-    if (!sm_count) {
-        int dev = 0;
-        B200_CUDA_TRY(cudaGetDevice(&dev));
-        B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-    }
-    auto kern = k_gemv<TYPE, NCOLS, MINB, PEERS>;
+    auto kern = k_gemv<TYPE, NCOLS, V, MINB>;
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int) (MINB == 2 ? SMEM_2CTA : SMEM_1CTA)));
@@ -661,8 +700,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, cudaStream_t 
     a.x = g.x, a.x_col_stride = g.x_col_stride, a.xq = g.xq;
     a.dst = g.dst, a.dst_col_stride = g.dst_col_stride;
     a.m = (int) g.m, a.k = (int) g.k;
-    a.nst = P.nst, a.R = P.R, a.lpr_log2 = P.lpr_log2, a.nwc = P.nwc, a.row_pitch = P.row_pitch;
-    a.stage_bytes = P.stage_bytes;
+    a.nst = P.nst, a.T = P.T, a.nteams = P.nteams, a.row_pitch = P.row_pitch, a.stage_bytes = P.stage_bytes;
     a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used > 0 ? g.n_used : 1;
     a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
     a.x_token_stride = g.x_token_stride, a.x_slot_stride = g.x_slot_stride;
@@ -670,22 +708,13 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, cudaStream_t 
     a.world = g.world, a.rank = g.rank, a.row_offset = g.row_offset;
     a.dbg = env_int("B200_GEMV_DEBUG", 0);
     gemv_peers peers = {};
-    if (PEERS) {
+    if (g.world > 1) {
         for (int r = 0; r < g.world && r < 16; r++) peers.dst[r] = g.peer_dst[r], peers.flag[r] = g.peer_flag[r];
         peers.epoch = g.epoch;
     }
-    // grid.x: MINB CTAs per SM, but at least rows-per-iteration rows each
-    const int64_t pairs = g.ids ? g.npairs : 1;
-    int gx = sm_count * MINB * env_int("B200_GEMV_WAVES", 1);
-    if (g.ids && pairs > 1) gx = (int) ((gx + pairs - 1) / pairs);  // MUL_MAT_ID: the pairs share the machine
-    const int     rpi = 32 >> P.lpr_log2;
-    const int64_t max_ctas = (g.m + rpi - 1) / rpi;
-    if (gx > max_ctas) gx = (int) max_ctas;
-    if (gx < 1) gx = 1;
-
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) gx, (unsigned) pairs, 1);
-    cfg.blockDim         = dim3((unsigned) (P.nwc + 1) * 32, 1, 1);
+    cfg.gridDim          = dim3((unsigned) gx, (unsigned) (g.ids ? g.npairs : 1), 1);
+    cfg.blockDim         = dim3((unsigned) gemv_shape<NCOLS, MINB>::THREADS, 1, 1);
     cfg.dynamicSmemBytes = P.smem;
     cfg.stream           = stream;
     cudaLaunchAttribute attr[1];
@@ -699,15 +728,30 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, cudaStream_t 
 
 template <int TYPE, int NCOLS>
 static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
-    gemv_plan P;
-    const int row_bytes = (int) (g.k / type_block_elems(TYPE)) * type_block_bytes(TYPE);
-    if (!make_plan(TYPE, g.k, NCOLS, g.w_row_stride == row_bytes, P)) return B200_ERR_UNSUPPORTED;
-    const bool peers = g.world > 1;
-    if (P.minb == 2) {
-        return peers ? launch_gemv_k<TYPE, NCOLS, 2, true>(g, P, stream)
-                     : launch_gemv_k<TYPE, NCOLS, 2, false>(g, P, stream);
+    if (!g_sm_count) {
+        int dev = 0;
+        B200_CUDA_TRY(cudaGetDevice(&dev));
+        B200_CUDA_TRY(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
     }
-    return peers ? launch_gemv_k<TYPE, NCOLS, 1, true>(g, P, stream) : launch_gemv_k<TYPE, NCOLS, 1, false>(g, P, stream);
+    const int     row_bytes  = (int) (g.k / type_block_elems(TYPE)) * type_block_bytes(TYPE);
+    const bool    contiguous = g.w_row_stride == row_bytes;
+    const int64_t pairs      = g.ids ? g.npairs : 1;
+    // first guess of the grid (two CTAs per SM) to learn the slab length, then the plan fixes CTAs per SM
+    gemv_plan P;
+    int64_t gx0 = (int64_t) g_sm_count * 2;
+    if (pairs > 1) gx0 = (gx0 + pairs - 1) / pairs;             // MUL_MAT_ID: the pairs share the machine
+    if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, P)) return B200_ERR_UNSUPPORTED;
+    int64_t gx = (int64_t) g_sm_count * P.minb * env_int("B200_GEMV_WAVES", 1);
+    if (pairs > 1) gx = (gx + pairs - 1) / pairs;
+    const int64_t max_ctas = (g.m + P.V - 1) / P.V;             // at least one stage each
+    if (gx > max_ctas) gx = max_ctas;
+    if (gx < 1) gx = 1;
+    if (P.V == 8) {
+        return P.minb == 2 ? launch_gemv_k<TYPE, NCOLS, 8, 2>(g, P, (int) gx, stream)
+                           : launch_gemv_k<TYPE, NCOLS, 8, 1>(g, P, (int) gx, stream);
+    }
+    return P.minb == 2 ? launch_gemv_k<TYPE, NCOLS, 4, 2>(g, P, (int) gx, stream)
+                       : launch_gemv_k<TYPE, NCOLS, 4, 1>(g, P, (int) gx, stream);
 }
 
 template <int TYPE>
