@@ -398,7 +398,7 @@ struct gemv_peers {
 // On return p[0] holds the warp-wide sum of row `butterfly_row<V>(lane)`; lanes with (lane & (32/V - 1)) == 0 write it.
 template <int V>
 __device__ __forceinline__ void butterfly_rows(float (&p)[V], int lane) {
-    static_assert(V == 4 || V == 8, "V");
+    static_assert(V == 2 || V == 4 || V == 8, "V");
     int mask = 16;
 #pragma unroll
     for (int n = V / 2; n >= 1; n >>= 1) {
@@ -417,20 +417,25 @@ __device__ __forceinline__ void butterfly_rows(float (&p)[V], int lane) {
 template <int V>
 __device__ __forceinline__ int butterfly_row(int lane) {
     return V == 8 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
-                  : (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1));
+         : V == 4 ? (((lane >> 4) & 1) * 2 + ((lane >> 3) & 1))
+                  : ((lane >> 4) & 1);
 }
 
-// Launch shapes: MINB = 2 -> 8 compute warps, two CTAs per SM (<= 112 registers): 1-2 columns, rows of <= 16384.
+// Launch shapes: MINB = 2 -> 8 compute warps, grid of two CTAs per SM; 1-2 columns, rows of <= 16384 elements.
+//                            A single column is compiled for THREE resident CTAs per SM (<= 72 registers, <= 74 KB of
+//                            shared memory): the third slot is where the NEXT matmul's CTAs land under programmatic
+//                            dependent launch, so their barrier set-up and first weight stages overlap this kernel.
 //                MINB = 1 -> 3-4 columns: 8 compute warps, one CTA per SM (registers for 4 x 24 activation words);
 //                            1-2 columns: 16 compute warps, one CTA per SM (rows longer than 16384 elements).
 template <int NCOLS, int MINB> struct gemv_shape {
     static constexpr int NW = (MINB == 2 || NCOLS > 2) ? 8 : 16;
+    static constexpr int RESIDENT = MINB == 2 ? (NCOLS == 1 ? 3 : 2) : 1;
     static constexpr int THREADS = (NW + 1) * 32;
 };
 
 template <int TYPE, int NCOLS, int V, int MINB>
-__global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, MINB) k_gemv(const gemv_kargs a,
-                                                                                  const gemv_peers peers) {
+__global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<NCOLS, MINB>::RESIDENT)
+    k_gemv(const gemv_kargs a, const gemv_peers peers) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int BYTES = qtraits<TYPE>::bytes;
     constexpr int BLCK  = qtraits<TYPE>::blck;
@@ -631,7 +636,8 @@ static int type_block_bytes(int type) {
 }
 static int type_block_elems(int type) { return type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 ? 32 : 256; }
 
-static constexpr size_t SMEM_2CTA = 112 * 1024;   // two CTAs (+1 KB reserved each) fit in 228 KB
+static constexpr size_t SMEM_3CTA = 74 * 1024;    // three CTAs (+1 KB reserved each) fit in 228 KB
+static constexpr size_t SMEM_2CTA = 112 * 1024;   // two CTAs
 static constexpr size_t SMEM_1CTA = 226 * 1024;
 static constexpr int    WARPS_2CTA = 8, WARPS_1CTA = 16;   // compute warps (one more warp is the producer)
 
@@ -650,18 +656,22 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
     const int want = env_int("B200_GEMV_STAGES", 0);
     for (;;) {
         const int    nw     = (P.minb == 2 || ncols > 2) ? WARPS_2CTA : WARPS_1CTA;
-        const size_t budget = P.minb == 2 ? SMEM_2CTA : SMEM_1CTA;
+        const size_t budget = P.minb == 2 ? ((ncols == 1 && env_int("B200_GEMV_RESIDENT", 3) == 3) ? SMEM_3CTA : SMEM_2CTA)
+                                          : SMEM_1CTA;
         P.nteams = nw / T;
-        int vfirst = (rows_per_cta >= (int64_t) P.nteams * 8 && (size_t) 8 * P.row_pitch <= 40 * 1024) ? 8 : 4;
+        // rows per stage: every team of the CTA should get a stage, and the ring should hold >= 3 stages
+        int vfirst = 8;
+        while (vfirst > 2 && (rows_per_cta < (int64_t) P.nteams * vfirst || (size_t) vfirst * P.row_pitch * 3 > budget))
+            vfirst >>= 1;
         vfirst = env_int("B200_GEMV_V", vfirst);
-        for (int V = vfirst; V >= 4; V -= 4) {
+        for (int V = vfirst; V >= 2; V >>= 1) {
             // payload + 15 bytes of leading misalignment + 16 so word reads of a 2-byte-aligned tail stay inside
             P.stage_bytes = (V * P.row_pitch + 15 + 16 + 127) & ~127;
             const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * V * T * 4 + 16;
             int nst = (int) (budget / per_stage);
             const int cap = want > 0 ? want : (P.nteams * 2 > 4 ? P.nteams * 2 : 4);
             if (nst > cap) nst = cap;
-            if (nst >= 2 || (V == 4 && nst >= 1)) {
+            if (nst >= 2 || (V == 2 && nst >= 1)) {
                 int nteams = P.nteams < nst ? P.nteams : nst;   // a team needs a slot of its own ...
                 nst -= nst % nteams;                            // ... and keeps it: slot s is always used by team
                                                                 // s % nteams, so no warp can run a full mbarrier
@@ -671,7 +681,7 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
             }
         }
         if (P.minb == 1) return false;
-        P.minb = 1;                                             // 4 rows do not fit in half an SM: take all of it
+        P.minb = 1;                                             // 2 rows do not fit in half an SM: take all of it
     }
 }
 
@@ -693,6 +703,8 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int) (MINB == 2 ? SMEM_2CTA : SMEM_1CTA)));
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
         attr_set = true;
     }
     gemv_kargs a;
@@ -746,12 +758,21 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     const int64_t max_ctas = (g.m + P.V - 1) / P.V;             // at least one stage each
     if (gx > max_ctas) gx = max_ctas;
     if (gx < 1) gx = 1;
-    if (P.V == 8) {
-        return P.minb == 2 ? launch_gemv_k<TYPE, NCOLS, 8, 2>(g, P, (int) gx, stream)
-                           : launch_gemv_k<TYPE, NCOLS, 8, 1>(g, P, (int) gx, stream);
+    // shapes that are never planned (two CTAs per SM with 3-4 columns) are not instantiated
+    if constexpr (NCOLS <= 2) {
+        if (P.minb == 2) {
+            switch (P.V) {
+                case 8: return launch_gemv_k<TYPE, NCOLS, 8, 2>(g, P, (int) gx, stream);
+                case 4: return launch_gemv_k<TYPE, NCOLS, 4, 2>(g, P, (int) gx, stream);
+                default: return launch_gemv_k<TYPE, NCOLS, 2, 2>(g, P, (int) gx, stream);
+            }
+        }
     }
-    return P.minb == 2 ? launch_gemv_k<TYPE, NCOLS, 4, 2>(g, P, (int) gx, stream)
-                       : launch_gemv_k<TYPE, NCOLS, 4, 1>(g, P, (int) gx, stream);
+    switch (P.V) {
+        case 8: return launch_gemv_k<TYPE, NCOLS, 8, 1>(g, P, (int) gx, stream);
+        case 4: return launch_gemv_k<TYPE, NCOLS, 4, 1>(g, P, (int) gx, stream);
+        default: return launch_gemv_k<TYPE, NCOLS, 2, 1>(g, P, (int) gx, stream);
+    }
 }
 
 template <int TYPE>
