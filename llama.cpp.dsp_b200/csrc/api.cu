@@ -210,10 +210,14 @@ int b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const floa
 }
 
 // ------------------------------------------------------------------------------------------------------- MUL_MAT_ID
+// Activations: the n_tokens * ne11 rows of b are quantized once into the workspace (row (t, j) at index t * ne11 + j),
+// then one GEMV grid with blockIdx.y = (token, slot) pair reads row (t, slot % ne11).  B200_FUSED_QUANT_MAX_K > 0
+// switches rows of k <= that to in-kernel quantization (no workspace).
 size_t b200_mul_mat_id_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
                                       int64_t n_tokens) {
-    (void) type, (void) m, (void) k, (void) n_expert, (void) n_used, (void) n_tokens;
-    return 0;
+    (void) m, (void) n_expert;
+    if (!weight_type(type) || k <= 0 || n_used <= 0 || n_tokens <= 0 || k <= fused_quant_max_k()) return 0;
+    return (size_t) n_tokens * n_used * q8_soa_layout(k).bytes;   // ne11 <= n_used
 }
 
 int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const float * b, int64_t b_token_stride,
@@ -221,12 +225,12 @@ int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const floa
                     int64_t dst_token_stride, int64_t dst_slot_stride, int64_t m, int64_t k, int64_t n_expert,
                     int64_t n_used, int64_t n_tokens, void * workspace, size_t workspace_bytes,
                     b200_stream_t stream_) {
-    (void) workspace, (void) workspace_bytes;
     cudaStream_t stream = (cudaStream_t) stream_;
     int64_t row_stride = 0;
     int st = check_weights(type, as, row_stride, k);
     if (st != B200_OK) return st;
-    if (m < 0 || n_expert <= 0 || n_used < 0 || n_tokens < 0 || ne11 <= 0 || ids_row_stride < n_used)
+    if (m < 0 || n_expert <= 0 || n_used < 0 || n_tokens < 0 || ne11 <= 0 || ne11 > (n_used > 0 ? n_used : 1) ||
+        ids_row_stride < n_used)
         return B200_ERR_SHAPE;
     if (m > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
     if (expert_stride == 0) expert_stride = row_stride * m;
@@ -247,19 +251,31 @@ int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const floa
     g.ids = ids, g.ids_row_stride = ids_row_stride, g.n_used = (int) n_used, g.ne11 = (int) ne11;
     g.x_token_stride = b_token_stride, g.x_slot_stride = b_slot_stride;
     g.dst_token_stride = dst_token_stride, g.dst_slot_stride = dst_slot_stride;
+    const bool      fused = k <= fused_quant_max_k();
+    const q8_layout L     = q8_soa_layout(k);
+    if (!fused) {
+        if (!workspace || workspace_bytes < (size_t) n_tokens * ne11 * L.bytes) return B200_ERR_WORKSPACE;
+        if ((uintptr_t) workspace % 16 != 0) return B200_ERR_ALIGNMENT;
+        // rows (t, j): one strided quantizer launch per slot j keeps the row stride uniform
+        for (int64_t j = 0; j < ne11; j++) {
+            st = launch_quantize_q8_soa_strided(b + j * b_slot_stride, b_token_stride,
+                                                (uint8_t *) workspace + (size_t) j * L.bytes, (int64_t) ne11 * L.bytes, k,
+                                                n_tokens, type == B200_TYPE_IQ4_XS, stream);
+            if (st != B200_OK) return st;
+        }
+    }
     // grid.y is limited to 65535 pairs per launch
-    const int64_t pairs = n_tokens * n_used;
     const int64_t tok_per_launch = 65535 / n_used > 0 ? 65535 / n_used : 1;
     for (int64_t t0 = 0; t0 < n_tokens; t0 += tok_per_launch) {
         const int64_t nt = n_tokens - t0 < tok_per_launch ? n_tokens - t0 : tok_per_launch;
         g.npairs = nt * n_used;
         g.x      = b + t0 * b_token_stride;
+        g.xq     = fused ? nullptr : (const uint8_t *) workspace + (size_t) t0 * ne11 * L.bytes;
         g.dst    = dst + t0 * dst_token_stride;
         g.ids    = ids + t0 * ids_row_stride;
         st = launch_gemv(g, stream);
         if (st != B200_OK) return st;
     }
-    (void) pairs;
     return B200_OK;
 }
 

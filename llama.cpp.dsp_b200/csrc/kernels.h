@@ -10,6 +10,9 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
                               cudaStream_t stream);
 int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
                            cudaStream_t stream);
+// same, with an explicit output row pitch in bytes (>= q8_soa_layout(k).bytes, multiple of 16)
+int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, int64_t y_pitch, int64_t k, int64_t nrows,
+                                   bool interleave, cudaStream_t stream);
 int launch_dequantize_f32(int type, const void * w, int64_t w_stride, float * y, int64_t k, int64_t nrows,
                           cudaStream_t stream);
 

@@ -558,23 +558,20 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 
     pdl_wait();
     q8_unit u[NCOLS];
-    if (have) {
+    {
+        // lanes past the end of the row build a (discarded) copy of the last unit: the Q6_K quantizer shuffles
+        // between neighbouring lanes, so the whole warp has to take the same path
+        const int ugc = have ? ug : upr - 1;
         if (a.xq) {
             const q8_layout L = q8_soa_layout(a.k);
+            const uint8_t * xq = a.xq;
+            if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], a.xq + (size_t) c * L.bytes, L, a.k, ug);
+            for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
         } else {
             const bool vec = ((uintptr_t) x % 16 == 0) && (a.x_col_stride % 4 == 0);
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) make_unit_f32<TYPE>(u[c], x + c * a.x_col_stride, a.k, ug, vec);
-        }
-    } else {
-#pragma unroll
-        for (int c = 0; c < NCOLS; c++) {
-#pragma unroll
-            for (int i = 0; i < 16; i++) u[c].q[i] = 0;
-#pragma unroll
-            for (int i = 0; i < 4; i++) u[c].d[i] = 0.f, u[c].s[i] = 0.f;
+            for (int c = 0; c < NCOLS; c++) make_unit_f32<TYPE>(u[c], x + c * a.x_col_stride, a.k, ugc, vec);
         }
     }
 

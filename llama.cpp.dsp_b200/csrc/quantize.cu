@@ -54,16 +54,16 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
 // Launched with programmatic stream serialization so the GEMV that consumes it can prefetch weights meanwhile.
 template <bool INTERLEAVE>
 __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restrict__ x, int64_t x_stride,
-                                                         uint8_t * __restrict__ y, int64_t k, bool vec) {
+                                                         uint8_t * __restrict__ y, int64_t y_pitch, int64_t k, bool vec) {
     pdl_wait();
     pdl_launch_dependents();
     const q8_layout L = q8_soa_layout(k);
-    quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.y * x_stride, k, y + (int64_t) blockIdx.y * L.bytes, L,
+    quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.y * x_stride, k, y + (int64_t) blockIdx.y * y_pitch, L,
                                     blockIdx.x * 8 + (threadIdx.x >> 5), gridDim.x * 8, threadIdx.x & 31, vec);
 }
 
-int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
-                           cudaStream_t stream) {
+int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, int64_t y_pitch, int64_t k,
+                                   int64_t nrows, bool interleave, cudaStream_t stream) {
     if (k == 0 || nrows == 0) return B200_OK;
     const bool vec = ((uintptr_t) x % 16 == 0) && (x_stride % 4 == 0);
     int64_t done = 0;
@@ -78,13 +78,18 @@ int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t 
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr, cfg.numAttrs = 1;
         const float * xp = x + done * x_stride;
-        uint8_t *     yp = (uint8_t *) y + done * (int64_t) q8_soa_layout(k).bytes;
-        if (interleave) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<true>, xp, x_stride, yp, k, vec));
-        else            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<false>, xp, x_stride, yp, k, vec));
+        uint8_t *     yp = (uint8_t *) y + done * y_pitch;
+        if (interleave) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<true>, xp, x_stride, yp, y_pitch, k, vec));
+        else            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<false>, xp, x_stride, yp, y_pitch, k, vec));
         note_launch();
         done += rows;
     }
     return B200_OK;
+}
+
+int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
+                           cudaStream_t stream) {
+    return launch_quantize_q8_soa_strided(x, x_stride, y, (int64_t) q8_soa_layout(k).bytes, k, nrows, interleave, stream);
 }
 
 // ---------------------------------------------------------------------------------------------- dequantizers

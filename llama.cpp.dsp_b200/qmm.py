@@ -208,7 +208,8 @@ def mul_mat_id(t, w, b, ids, m, k, n_expert, out=None, stream=None):
     n_tokens, ne11, _ = b.shape
     n_used = ids.shape[1]
     dst = out if out is not None else torch.empty((n_tokens, n_used, m), dtype=torch.float32, device=b.device)
+    ws, wsz = _workspace(b.device, lib().b200_mul_mat_id_workspace_size(t, m, k, n_expert, n_used, n_tokens))
     check(lib().b200_mul_mat_id(t, w.data_ptr(), 0, b.data_ptr(), b.stride(0), b.stride(1), ne11, ids.data_ptr(),
                                 ids.stride(0), dst.data_ptr(), dst.stride(0), dst.stride(1), m, k, n_expert, n_used,
-                                n_tokens, None, 0, _stream_ptr(stream)))
+                                n_tokens, ws, wsz, _stream_ptr(stream)))
     return dst
