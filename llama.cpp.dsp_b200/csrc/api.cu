@@ -121,17 +121,16 @@ int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * 
 }
 
 // ---------------------------------------------------------------------------------------------------------- MUL_MAT
-// Activation quantization policy (measured trade-off):
-//  * fused   : every lane of the GEMV quantizes its own 64-element unit from f32 in registers -- one launch per
-//              matmul, but each CTA re-reads the f32 row from L2 (2 * #SM * k * 4 bytes of L2 traffic).
-//  * separate: one small kernel writes the SoA q8_1 row(s) to the workspace, the GEMV loads 1/4 of the bytes.
-// Measured on B200 (profiles/r01): the separate quantizer wins at every size (4096x4096 Q4_K: 6.1 us vs 8.3 us), because
-// its launch overlaps the GEMV's weight prefetch under programmatic dependent launch while the fused prologue is
-// ~600 serial instructions per warp in every CTA.  So fused is opt-in (B200_FUSED_QUANT_MAX_K, default 0 = never);
-// activations are pre-quantized once and then consumed by GEMV launches of up to 4 columns each.
+// Activation quantization policy (measured on B200, profiles/r01):
+//  * fused   : one launch per matmul; every CTA quantizes the f32 row into its shared memory cooperatively (eight
+//              lanes per 32-block, all compute warps), then each lane pulls its 64-element unit into registers.  Costs
+//              #CTA * k * 4 bytes of L2 reads but removes a kernel boundary (~2 us in a dependent chain).
+//  * separate: one small kernel writes the SoA q8_1 row(s) to the workspace, the GEMV loads them from L2.
+// Fused is used for a single column with k <= B200_FUSED_QUANT_MAX_K (default 16384: <= 22 KB of shared memory);
+// everything else is pre-quantized once and then consumed by GEMV launches of up to 4 columns each.
 static int fused_quant_max_k() {
     const char * e = getenv("B200_FUSED_QUANT_MAX_K");
-    return e && *e ? atoi(e) : 0;
+    return e && *e ? atoi(e) : 16384;
 }
 static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
 

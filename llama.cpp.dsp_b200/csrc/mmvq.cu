@@ -147,18 +147,22 @@ __device__ __forceinline__ void make_unit_f32(q8_unit & u, const float * __restr
 }
 
 // Build the unit from activations already quantized into the SoA layout (actquant.cuh) in global memory.
-template <int TYPE>
+template <int TYPE, bool SMEM = false>
 __device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __restrict__ xq, q8_layout L, int k, int ug) {
+    // SMEM: xq points into shared memory (filled by the CTA's cooperative quantizer): no read-only-cache loads
+    auto ld16 = [](const uint8_t * p) { return SMEM ? *reinterpret_cast<const uint4 *>(p) : __ldg(reinterpret_cast<const uint4 *>(p)); };
+    auto ldf2 = [](const float2 * p) { return SMEM ? *p : __ldg(p); };
+    auto lds2 = [](const short2 * p) { return SMEM ? *p : __ldg(p); };
     const float2 * ds  = reinterpret_cast<const float2 *>(xq + L.off_ds);
     const short2 * s16 = reinterpret_cast<const short2 *>(xq + L.off_s16);
     if (TYPE == B200_TYPE_Q6_K) {
         const int b32 = (ug >> 2) * 8 + ((ug >> 1) & 1) * 4, l0 = (ug & 1) * 16;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const uint4 t = __ldg(reinterpret_cast<const uint4 *>(xq + (b32 + j) * 32 + l0));
+            const uint4 t = ld16(xq + (b32 + j) * 32 + l0);
             u.q[4 * j] = t.x, u.q[4 * j + 1] = t.y, u.q[4 * j + 2] = t.z, u.q[4 * j + 3] = t.w;
-            u.d[j] = __ldg(&ds[b32 + j]).x;
-            const short2 ss = __ldg(&s16[b32 + j]);
+            u.d[j] = ldf2(&ds[b32 + j]).x;
+            const short2 ss = lds2(&s16[b32 + j]);
             u.s[j] = (float) (32 * (int) (l0 ? ss.y : ss.x));
         }
     } else {
@@ -167,11 +171,11 @@ __device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __rest
         for (int h = 0; h < 2; h++) {
             const int b = 2 * ug + h;
             if (b < nblk) {
-                const uint4 t0 = __ldg(reinterpret_cast<const uint4 *>(xq + b * 32));
-                const uint4 t1 = __ldg(reinterpret_cast<const uint4 *>(xq + b * 32 + 16));
+                const uint4 t0 = ld16(xq + b * 32);
+                const uint4 t1 = ld16(xq + b * 32 + 16);
                 u.q[8 * h] = t0.x, u.q[8 * h + 1] = t0.y, u.q[8 * h + 2] = t0.z, u.q[8 * h + 3] = t0.w;
                 u.q[8 * h + 4] = t1.x, u.q[8 * h + 5] = t1.y, u.q[8 * h + 6] = t1.z, u.q[8 * h + 7] = t1.w;
-                const float2 dd = __ldg(&ds[b]);
+                const float2 dd = ldf2(&ds[b]);
                 u.d[h] = dd.x, u.s[h] = dd.y;
             } else {
 #pragma unroll
@@ -380,6 +384,7 @@ struct gemv_kargs {
     int             nteams;       // teams per CTA
     int             row_pitch;    // bytes between rows inside a stage
     int             stage_bytes;  // V * row_pitch + slack, multiple of 128
+    int             act_bytes;    // > 0: the CTA quantizes x into this much shared memory (fused quantizer), 128-aligned
     const int32_t * ids;
     int64_t         ids_row_stride;
     int             n_used, ne11;
@@ -444,9 +449,10 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     const int  lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int  nst = a.nst, T = a.T, nteams = a.nteams;
 
-    // shared memory: [stages: nst * stage_bytes][partials: nst * 2 * NCOLS * V * T floats][full bars][empty bars]
-    const uint32_t sm_stage  = smem_u32(smem);
-    float *        partial   = reinterpret_cast<float *>(smem + (size_t) nst * a.stage_bytes);
+    // shared memory: [q8 activations: act_bytes][stages: nst * stage_bytes][partials: nst * 2 * NCOLS * V * T floats]
+    //                [full bars][empty bars]
+    const uint32_t sm_stage  = smem_u32(smem) + a.act_bytes;
+    float *        partial   = reinterpret_cast<float *>(smem + a.act_bytes + (size_t) nst * a.stage_bytes);
     const int      part_sz   = NCOLS * V * T;                   // floats per (slot, parity)
     const uint32_t bar_full  = smem_u32(partial) + (uint32_t) nst * 2 * part_sz * 4;
     const uint32_t bar_empty = bar_full + 8 * nst;
@@ -482,8 +488,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 
     if (warp == NW) {
         // ---------------------------------------------------------------------------------------- TMA + epilogue warp
-        auto issue = [&](int st) {  // all lanes call; stage st -> slot st % nst
-            const int      slot = st % nst;
+        auto issue = [&](int st, int slot) {  // all lanes call; stage st -> ring slot `slot` (= st % nst)
             const int      r0 = r_begin + st * V, nr = min(V, r_end - r0);
             const uint32_t dstb = sm_stage + slot * a.stage_bytes;
             const uint32_t bar  = bar_full + 8 * slot;
@@ -515,8 +520,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         };
         // lane l sums the T per-warp partials of (column l / V, row l % V) in a fixed order: deterministic results
         const int fv = lane % V, fc = lane / V;
-        auto finish = [&](int st) {
-            const int slot = st % nst, par = (st / nst) & 1;
+        auto finish = [&](int st, int slot, int par) {
             const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
             if (fc < NCOLS && fv < nr) {
                 const float * p = partial + (size_t) (slot * 2 + par) * part_sz + (fc * V + fv) * T;
@@ -530,13 +534,14 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
             }
         };
         const int pre = min(nst, nstages);
-        for (int st = 0; st < pre; st++) issue(st);             // weights only: legal before the dependency wait
+        for (int st = 0; st < pre; st++) issue(st, st);         // weights only: legal before the dependency wait
         pdl_wait();                                             // dst may still be read by the previous kernel
+        int slot = 0, par = 0;
         for (int st = 0; st < nstages; st++) {
-            const int slot = st % nst;
-            mbar_wait(bar_empty + 8 * slot, (st / nst) & 1);    // the owning team is done with stage st
-            if (st + nst < nstages) issue(st + nst);            // refill first, then reduce
-            finish(st);
+            mbar_wait(bar_empty + 8 * slot, par);               // the owning team is done with stage st
+            if (st + nst < nstages) issue(st + nst, slot);      // refill first, then reduce
+            finish(st, slot, par);
+            if (++slot == nst) slot = 0, par ^= 1;
         }
         if (a.world > 1) {
             __syncwarp();
@@ -549,55 +554,57 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     }
 
     // -------------------------------------------------------------------------------------------- compute warps
+    const int k32 = a.k / 32;
+    const int upr = (a.k + 63) / 64;                            // units per row
+    const q8_layout L = q8_soa_layout(a.k);
+
+    pdl_wait();                                                 // x is produced by the previous kernel
+    if (a.act_bytes) {
+        // fused quantizer: all NW compute warps (spare ones included) quantize the row into shared memory once,
+        // eight lanes per 32-block, with exactly the arithmetic of the standalone kernel (actquant.cuh)
+        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
+        asm volatile("bar.sync 1, %0;" ::"n"(NW * 32) : "memory");
+    }
     const int team = warp / T, wt = warp - team * T;
     if (team >= nteams) return;                                 // spare warps (NW not a multiple of T)
     const int  ug   = wt * 32 + lane;                           // this lane's unit of k, fixed for the whole kernel
-    const int  k32  = a.k / 32;
-    const int  upr  = (a.k + 63) / 64;                          // units per row
     const bool have = ug < upr;
-
-    pdl_wait();
+    const int  ugc  = have ? ug : upr - 1;                      // lanes past the row end mirror the last unit; their
+                                                                // products are dropped by a select, never multiplied
     q8_unit u[NCOLS];
-    {
-        // lanes past the end of the row build a (discarded) copy of the last unit: the Q6_K quantizer shuffles
-        // between neighbouring lanes, so the whole warp has to take the same path
-        const int ugc = have ? ug : upr - 1;
-        if (a.xq) {
-            const q8_layout L = q8_soa_layout(a.k);
-            const uint8_t * xq = a.xq;
-            if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
+    if (a.act_bytes) {
+        make_unit_q8<TYPE, true>(u[0], smem, L, a.k, ugc);      // the host plans the fused quantizer for one column only
+    } else {
+        const uint8_t * xq = a.xq;
+        if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
-        } else {
-            const bool vec = ((uintptr_t) x % 16 == 0) && (a.x_col_stride % 4 == 0);
-#pragma unroll
-            for (int c = 0; c < NCOLS; c++) make_unit_f32<TYPE>(u[c], x + c * a.x_col_stride, a.k, ugc, vec);
-        }
+        for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
     }
 
-    const int      brow  = butterfly_row<V>(lane);
-    const bool     bwrite = (lane & (32 / V - 1)) == 0;
+    const int      brow     = butterfly_row<V>(lane);
+    const bool     bwrite   = (lane & (32 / V - 1)) == 0;
     const uint32_t row_step = contiguous ? (uint32_t) row_bytes : (uint32_t) a.row_pitch;
+    const uint32_t c1       = contiguous ? 0u : (uint32_t) (a.w_row_stride & 15);
+    int slot = team, par = 0;                                   // slot s is only ever used by team s % nteams
     for (int st = team; st < nstages; st += nteams) {
-        const int slot = st % nst, par = (st / nst) & 1;
         const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
         mbar_wait(bar_full + 8 * slot, par);
-        // first row's address inside the stage (the bulk copy started at the 16-byte boundary below the row)
-        uint32_t rowa = sm_stage + slot * a.stage_bytes;
-        if (contiguous) rowa += (uint32_t) ((uint64_t) (W + (int64_t) r0 * row_bytes) & 15);
+        // row v starts at base + v * row_step + (its global address & 15): every bulk copy began at the 16-byte
+        // boundary below its first byte (one copy per stage when rows are contiguous, one per row otherwise)
+        const uint32_t base = sm_stage + slot * a.stage_bytes;
+        const uint32_t c0   = (uint32_t) ((uint64_t) (W + (int64_t) r0 * a.w_row_stride) & 15);
         float acc[NCOLS][V];
 #pragma unroll
         for (int v = 0; v < V; v++) {
             float out[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
-            if (have && v < nr && a.dbg != 1) {
-                uint32_t ra = rowa + v * row_step;
-                if (!contiguous) ra += (uint32_t) ((uint64_t) (W + (int64_t) (r0 + v) * a.w_row_stride) & 15);
-                unit_dot<TYPE, NCOLS>(ra, ug, k32, u, out);
+            if (v < nr) {                                       // warp-uniform
+                const uint32_t ra = base + v * row_step + ((c0 + v * c1) & 15u);
+                unit_dot<TYPE, NCOLS>(ra, ugc, k32, u, out);
             }
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) acc[c][v] = out[c];
+            for (int c = 0; c < NCOLS; c++) acc[c][v] = have ? out[c] : 0.f;
         }
         float * p = partial + (size_t) (slot * 2 + par) * part_sz;
 #pragma unroll
@@ -607,6 +614,8 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + 8 * slot);       // release: partials visible to the epilogue warp
+        slot += nteams;
+        if (slot >= nst) slot -= nst, par ^= 1;
     }
 }
 
@@ -617,7 +626,7 @@ static int env_int(const char * name, int dflt) {
 }
 
 struct gemv_plan {
-    int T, nteams, V, nst, row_pitch, stage_bytes, minb;
+    int T, nteams, V, nst, row_pitch, stage_bytes, minb, act_bytes;
     size_t smem;
 };
 
@@ -640,7 +649,8 @@ static constexpr int    WARPS_2CTA = 8, WARPS_1CTA = 16;   // compute warps (one
 
 // Choose team size, rows per stage and ring depth.  `rows_per_cta` steers V: short slabs take V = 4 so that every
 // team of the CTA gets a stage.  Returns false if the shape cannot be planned (k > 32768: T would exceed 16 warps).
-static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t rows_per_cta, gemv_plan & P) {
+static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t rows_per_cta, bool fused, gemv_plan & P) {
+    P.act_bytes = fused ? (int) ((q8_soa_layout(k).bytes + 127) & ~127u) : 0;
     const int upr = (int) ((k + 63) / 64);
     const int T   = (upr + 31) / 32;
     if (T > (ncols > 2 ? WARPS_2CTA : WARPS_1CTA)) return false;
@@ -653,8 +663,14 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
     const int want = env_int("B200_GEMV_STAGES", 0);
     for (;;) {
         const int    nw     = (P.minb == 2 || ncols > 2) ? WARPS_2CTA : WARPS_1CTA;
-        const size_t budget = P.minb == 2 ? ((ncols == 1 && env_int("B200_GEMV_RESIDENT", 3) == 3) ? SMEM_3CTA : SMEM_2CTA)
+        const size_t total  = P.minb == 2 ? ((ncols == 1 && env_int("B200_GEMV_RESIDENT", 3) == 3) ? SMEM_3CTA : SMEM_2CTA)
                                           : SMEM_1CTA;
+        if (total <= (size_t) P.act_bytes + 4096) {
+            if (P.minb == 1) return false;
+            P.minb = 1;
+            continue;
+        }
+        const size_t budget = total - P.act_bytes;
         P.nteams = nw / T;
         // rows per stage: every team of the CTA should get a stage, and the ring should hold >= 3 stages
         int vfirst = 8;
@@ -673,7 +689,7 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
                 nst -= nst % nteams;                            // ... and keeps it: slot s is always used by team
                                                                 // s % nteams, so no warp can run a full mbarrier
                                                                 // phase ahead of the slot's previous user
-                P.nteams = nteams, P.nst = nst, P.V = V, P.smem = (size_t) nst * per_stage;
+                P.nteams = nteams, P.nst = nst, P.V = V, P.smem = (size_t) P.act_bytes + (size_t) nst * per_stage;
                 return true;
             }
         }
@@ -687,7 +703,7 @@ size_t gemv_q8_smem_bytes(int64_t k, int ncols) { (void) k, (void) ncols; return
 int gemv_max_cols(int type, int64_t k) {
     gemv_plan P;
     for (int n = 4; n >= 1; n--)
-        if (make_plan(type, k, n, true, 1 << 20, P)) return n;
+        if (make_plan(type, k, n, true, 1 << 20, false, P)) return n;
     return 0;
 }
 
@@ -710,6 +726,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.dst = g.dst, a.dst_col_stride = g.dst_col_stride;
     a.m = (int) g.m, a.k = (int) g.k;
     a.nst = P.nst, a.T = P.T, a.nteams = P.nteams, a.row_pitch = P.row_pitch, a.stage_bytes = P.stage_bytes;
+    a.act_bytes = P.act_bytes;
     a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used > 0 ? g.n_used : 1;
     a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
     a.x_token_stride = g.x_token_stride, a.x_slot_stride = g.x_slot_stride;
@@ -749,7 +766,9 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     gemv_plan P;
     int64_t gx0 = (int64_t) g_sm_count * 2;
     if (pairs > 1) gx0 = (gx0 + pairs - 1) / pairs;             // MUL_MAT_ID: the pairs share the machine
-    if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, P)) return B200_ERR_UNSUPPORTED;
+    const bool fused = g.xq == nullptr;                         // f32 activations: quantize inside the kernel
+    if (fused && NCOLS != 1) return B200_ERR_UNSUPPORTED;
+    if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, fused, P)) return B200_ERR_UNSUPPORTED;
     int64_t gx = (int64_t) g_sm_count * P.minb * env_int("B200_GEMV_WAVES", 1);
     if (pairs > 1) gx = (gx + pairs - 1) / pairs;
     const int64_t max_ctas = (g.m + P.V - 1) / P.V;             // at least one stage each

@@ -204,4 +204,5 @@ def test_launch_counter_counts_kernels(qmm):
     before = qmm.launch_count()
     w = torch.zeros(144 * 16, dtype=torch.uint8, device="cuda")
     qmm.mul_mat(qref.Q4_K, w, torch.ones((1, 256), device="cuda"), 16, 256)
-    assert qmm.launch_count() == before + 2      # q8_1 activation quantizer + GEMV (chained by programmatic launch)
+    # one fused launch (quantizer inside the GEMV) or two (separate q8_1 quantizer chained by programmatic launch)
+    assert qmm.launch_count() - before in (1, 2)

@@ -14,7 +14,8 @@ import b200pkg  # noqa: E402
 import qref  # noqa: E402
 
 qmm = b200pkg.load()
-KNOBS = ["B200_GEMV_STAGES", "B200_GEMV_V", "B200_GEMV_MINB", "B200_PDL", "B200_FUSED_QUANT_MAX_K", "B200_GEMV_WAVES"]
+KNOBS = ["B200_GEMV_STAGES", "B200_GEMV_V", "B200_GEMV_MINB", "B200_PDL", "B200_FUSED_QUANT_MAX_K", "B200_GEMV_WAVES",
+         "B200_GEMV_RESIDENT"]
 
 
 def make_weights(t, m, k, copies, rng):
@@ -61,9 +62,10 @@ def main():
     rng = np.random.default_rng(0)
     shapes = [(4096, 14336), (14336, 4096), (4096, 4096), (1024, 4096)]
     configs = [{}] if quick else [
-        {}, {"B200_PDL": 0}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 8}, {"B200_GEMV_STAGES": 2}, {"B200_GEMV_STAGES": 8},
-        {"B200_GEMV_MINB": 1}, {"B200_FUSED_QUANT_MAX_K": 0}, {"B200_FUSED_QUANT_MAX_K": 100000},
-        {"B200_GEMV_WAVES": 2},
+        {}, {"B200_PDL": 0}, {"B200_GEMV_RESIDENT": 2}, {"B200_GEMV_RESIDENT": 2, "B200_FUSED_QUANT_MAX_K": 0},
+        {"B200_FUSED_QUANT_MAX_K": 0}, {"B200_GEMV_V": 2}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 8},
+        {"B200_GEMV_RESIDENT": 2, "B200_GEMV_V": 4}, {"B200_GEMV_RESIDENT": 2, "B200_GEMV_V": 8},
+        {"B200_GEMV_STAGES": 2}, {"B200_GEMV_MINB": 1}, {"B200_GEMV_WAVES": 2},
     ]
     for name in names:
         t = qref.WEIGHT_TYPES[name]
