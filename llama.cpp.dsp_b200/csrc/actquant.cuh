@@ -69,37 +69,50 @@ __device__ __forceinline__ float4 load_f4(const float * p, bool vec) {
 // Called by `nwarps` warps of a CTA; warp `warp` takes blocks 4*warp + i*4*nwarps .. (+3).
 // INTERLEAVE: store element j of a block at position 2*j (j < 16) or 2*(j-16)+1 (j >= 16), the order in which the
 // IQ4_XS kernel's prmt codebook lookup emits weights.
-template <bool INTERLEAVE>
+// UNROLL: how many of a warp's iterations issue their global loads back to back before any arithmetic (the GEMV's
+// fused prologue uses 4 so that a row costs one L2 round trip instead of one per iteration).
+template <bool INTERLEAVE, int UNROLL = 1>
 __device__ __forceinline__ void quantize_row_q8_soa(const float * __restrict__ x, int64_t k, uint8_t * out,
                                                     q8_layout L, int warp, int nwarps, int lane, bool vec) {
-    const int nb  = (int) (k / 32);
-    const int sub = lane & 7;
-    float2 *  ds  = reinterpret_cast<float2 *>(out + L.off_ds);
-    short2 *  s16 = reinterpret_cast<short2 *>(out + L.off_s16);
-    for (int b0 = 4 * warp; b0 < nb; b0 += 4 * nwarps) {
-        const int  b      = b0 + (lane >> 3);
-        const bool active = b < nb;
-        float4     v      = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (active) v = load_f4(x + (int64_t) b * 32 + 4 * sub, vec);
-        const q8_block_result r = quantize_block32(v);
-        const int other16 = __shfl_xor_sync(0xffffffffu, r.isum16, 4);
-        if (!active) continue;
-        if (INTERLEAVE) {
-            // lanes sub and sub^4 hold elements j = 4*sub+i and j+16: exchange so that each lane owns 4 adjacent pairs
-            const uint32_t peer = __shfl_xor_sync(0xffffffffu, r.q4, 4);
-            const uint32_t lo   = sub < 4 ? r.q4 : peer;   // elements j .. j+3      (j = 4*(sub&3))
-            const uint32_t hi   = sub < 4 ? peer : r.q4;   // elements j+16 .. j+19
-            // sub < 4 writes pairs for j, j+1; sub >= 4 writes pairs for j+2, j+3
-            const uint32_t w = sub < 4 ? __byte_perm(lo, hi, 0x5140) : __byte_perm(lo, hi, 0x7362);
-            const int      pos = 8 * (sub & 3) + (sub < 4 ? 0 : 4);
-            *reinterpret_cast<uint32_t *>(out + (int64_t) b * 32 + pos) = w;
-        } else {
-            *reinterpret_cast<uint32_t *>(out + (int64_t) b * 32 + 4 * sub) = r.q4;
+    const int nb   = (int) (k / 32);
+    const int sub  = lane & 7;
+    const int step = 4 * nwarps;
+    float2 *  ds   = reinterpret_cast<float2 *>(out + L.off_ds);
+    short2 *  s16  = reinterpret_cast<short2 *>(out + L.off_s16);
+    for (int b0 = 4 * warp; b0 < nb; b0 += step * UNROLL) {
+        float4 vv[UNROLL];
+#pragma unroll
+        for (int j = 0; j < UNROLL; j++) {
+            const int b = b0 + j * step + (lane >> 3);
+            vv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (b < nb) vv[j] = load_f4(x + (int64_t) b * 32 + 4 * sub, vec);
         }
-        if (sub == 0) {
-            const float dh = __half2float(__float2half_rn(r.d));
-            ds[b]  = make_float2(dh, dh * (float) r.isum);
-            s16[b] = make_short2((short) r.isum16, (short) other16);
+#pragma unroll
+        for (int j = 0; j < UNROLL; j++) {
+            if (b0 + j * step >= nb) break;                     // warp-uniform
+            const int  b      = b0 + j * step + (lane >> 3);
+            const bool active = b < nb;
+            const q8_block_result r = quantize_block32(vv[j]);
+            const int other16 = __shfl_xor_sync(0xffffffffu, r.isum16, 4);
+            uint32_t w = r.q4;
+            int      pos = 4 * sub;
+            if (INTERLEAVE) {
+                // lanes sub and sub^4 hold elements j = 4*sub+i and j+16: exchange so that each lane owns 4 adjacent
+                // pairs; sub < 4 writes pairs for j, j+1; sub >= 4 writes pairs for j+2, j+3
+                const uint32_t peer = __shfl_xor_sync(0xffffffffu, r.q4, 4);
+                const uint32_t lo   = sub < 4 ? r.q4 : peer;   // elements j .. j+3      (j = 4*(sub&3))
+                const uint32_t hi   = sub < 4 ? peer : r.q4;   // elements j+16 .. j+19
+                w   = sub < 4 ? __byte_perm(lo, hi, 0x5140) : __byte_perm(lo, hi, 0x7362);
+                pos = 8 * (sub & 3) + (sub < 4 ? 0 : 4);
+            }
+            if (active) {
+                *reinterpret_cast<uint32_t *>(out + (int64_t) b * 32 + pos) = w;
+                if (sub == 0) {
+                    const float dh = __half2float(__float2half_rn(r.d));
+                    ds[b]  = make_float2(dh, dh * (float) r.isum);
+                    s16[b] = make_short2((short) r.isum16, (short) other16);
+                }
+            }
         }
     }
 }

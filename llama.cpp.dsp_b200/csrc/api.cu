@@ -121,16 +121,17 @@ int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * 
 }
 
 // ---------------------------------------------------------------------------------------------------------- MUL_MAT
-// Activation quantization policy (measured on B200, profiles/r01):
-//  * fused   : one launch per matmul; every CTA quantizes the f32 row into its shared memory cooperatively (eight
-//              lanes per 32-block, all compute warps), then each lane pulls its 64-element unit into registers.  Costs
-//              #CTA * k * 4 bytes of L2 reads but removes a kernel boundary (~2 us in a dependent chain).
-//  * separate: one small kernel writes the SoA q8_1 row(s) to the workspace, the GEMV loads them from L2.
-// Fused is used for a single column with k <= B200_FUSED_QUANT_MAX_K (default 16384: <= 22 KB of shared memory);
-// everything else is pre-quantized once and then consumed by GEMV launches of up to 4 columns each.
+// Activation quantization policy (measured on B200 with in-kernel timestamps, profiles/r01/gemv_trace_*.log):
+//  * separate: one small kernel writes the SoA q8_1 row(s) to the workspace; it triggers its dependents before waiting,
+//              so under programmatic dependent launch the GEMV's CTAs are resident and have their first weight stages
+//              in shared memory while the previous kernel drains.  Cost: one more kernel boundary (~1.6 us).
+//  * fused   : every CTA quantizes the f32 row into its shared memory cooperatively.  One launch per matmul, but 150-300
+//              CTAs re-reading and re-quantizing the same row cost 2-5 us between the dependency release and the first
+//              dot product (k = 4096: 6.8 us vs 6.0 us per matmul; k = 14336: 18 us vs 12 us).
+// So separate is the default; B200_FUSED_QUANT_MAX_K > 0 opts single-column matmuls with k <= that into the fused path.
 static int fused_quant_max_k() {
     const char * e = getenv("B200_FUSED_QUANT_MAX_K");
-    return e && *e ? atoi(e) : 16384;
+    return e && *e ? atoi(e) : 0;
 }
 static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
 

@@ -391,8 +391,16 @@ struct gemv_kargs {
     int64_t         x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
     int             world, rank;
     int64_t         row_offset;
-    int             dbg;          // profiling aid: 1 = skip the dot products, 2 = skip the TMA loads
+    int             dbg;          // profiling aid: 2 = skip the TMA loads
+    unsigned long long * trace;   // profiling aid: 8 globaltimer stamps per CTA (tools/gemv_trace.py), else nullptr
 };
+__device__ __forceinline__ void trace_stamp(const gemv_kargs & a, int i) {
+    if (a.trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.trace[((size_t) blockIdx.y * gridDim.x + blockIdx.x) * 8 + i] = t;
+    }
+}
 struct gemv_peers {
     float *   dst[16];
     int32_t * flag[16];
@@ -456,6 +464,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     const int      part_sz   = NCOLS * V * T;                   // floats per (slot, parity)
     const uint32_t bar_full  = smem_u32(partial) + (uint32_t) nst * 2 * part_sz * 4;
     const uint32_t bar_empty = bar_full + 8 * nst;
+    int * const    arrived   = reinterpret_cast<int *>(reinterpret_cast<uint8_t *>(partial) + (size_t) nst * 2 * part_sz * 4 + 16 * nst);
 
     const uint8_t * W   = a.W;
     const float *   x   = a.x;
@@ -477,9 +486,11 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     const bool contiguous = a.w_row_stride == row_bytes;
 
     if (threadIdx.x == 0) {
+        trace_stamp(a, 0);                                      // CTA entry
         for (int s = 0; s < nst; s++) {
             mbar_init(bar_full + 8 * s, 1);
-            mbar_init(bar_empty + 8 * s, T);
+            mbar_init(bar_empty + 8 * s, 1);
+            arrived[s] = 0;
         }
         mbar_fence_init();
     }
@@ -518,29 +529,14 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 if (lane < nr) tma_load_1d(dstb + lane * a.row_pitch, (const void *) g0, span, bar);
             }
         };
-        // lane l sums the T per-warp partials of (column l / V, row l % V) in a fixed order: deterministic results
-        const int fv = lane % V, fc = lane / V;
-        auto finish = [&](int st, int slot, int par) {
-            const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
-            if (fc < NCOLS && fv < nr) {
-                const float * p = partial + (size_t) (slot * 2 + par) * part_sz + (fc * V + fv) * T;
-                float v = 0.f;
-                for (int w = 0; w < T; w++) v += p[w];
-                if (a.world > 1) {
-                    for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
-                } else {
-                    dst[fc * a.dst_col_stride + r0 + fv] = v;
-                }
-            }
-        };
         const int pre = min(nst, nstages);
         for (int st = 0; st < pre; st++) issue(st, st);         // weights only: legal before the dependency wait
         pdl_wait();                                             // dst may still be read by the previous kernel
+        if (lane == 0) trace_stamp(a, 5);                       // producer released by the previous grid
         int slot = 0, par = 0;
         for (int st = 0; st < nstages; st++) {
-            mbar_wait(bar_empty + 8 * slot, par);               // the owning team is done with stage st
-            if (st + nst < nstages) issue(st + nst, slot);      // refill first, then reduce
-            finish(st, slot, par);
+            mbar_wait(bar_empty + 8 * slot, par);               // stage st is consumed and its results are written
+            if (st + nst < nstages) issue(st + nst, slot);
             if (++slot == nst) slot = 0, par ^= 1;
         }
         if (a.world > 1) {
@@ -550,6 +546,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 for (int r = 0; r < a.world; r++) atomicAdd_system(peers.flag[r], 1);
             }
         }
+        if (lane == 0) trace_stamp(a, 6);                       // last result written
         return;
     }
 
@@ -559,10 +556,11 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     const q8_layout L = q8_soa_layout(a.k);
 
     pdl_wait();                                                 // x is produced by the previous kernel
+    if (threadIdx.x == 0) trace_stamp(a, 1);
     if (a.act_bytes) {
         // fused quantizer: all NW compute warps (spare ones included) quantize the row into shared memory once,
         // eight lanes per 32-block, with exactly the arithmetic of the standalone kernel (actquant.cuh)
-        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
+        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS, 4>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
         asm volatile("bar.sync 1, %0;" ::"n"(NW * 32) : "memory");
     }
     const int team = warp / T, wt = warp - team * T;
@@ -581,6 +579,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
     }
 
+    if (threadIdx.x == 0) trace_stamp(a, 2);                    // activations in registers
     const int      brow     = butterfly_row<V>(lane);
     const bool     bwrite   = (lane & (32 / V - 1)) == 0;
     const uint32_t row_step = contiguous ? (uint32_t) row_bytes : (uint32_t) a.row_pitch;
@@ -589,6 +588,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     for (int st = team; st < nstages; st += nteams) {
         const int r0 = r_begin + st * V, nr = min(V, r_end - r0);
         mbar_wait(bar_full + 8 * slot, par);
+        if (threadIdx.x == 0 && st == team) trace_stamp(a, 3);  // first weights landed
         // row v starts at base + v * row_step + (its global address & 15): every bulk copy began at the 16-byte
         // boundary below its first byte (one copy per stage when rows are contiguous, one per row otherwise)
         const uint32_t base = sm_stage + slot * a.stage_bytes;
@@ -612,11 +612,37 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
             butterfly_rows<V>(acc[c], lane);
             if (bwrite) p[(c * V + brow) * T + wt] = acc[c][0];
         }
+        // the LAST warp of the team to get here sums the T partials of every (column, row) in a fixed order
+        // (deterministic results), stores them and hands the slot back to the producer
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar_empty + 8 * slot);       // release: partials visible to the epilogue warp
+        int last = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            last = atomicAdd(&arrived[slot], 1) == T - 1;
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last) {
+            if (lane == 0) arrived[slot] = 0;
+            __threadfence_block();
+            const int fv = lane % V, fc = lane / V;
+            if (fc < NCOLS && fv < nr) {
+                const volatile float * q = p + (fc * V + fv) * T;
+                float v = 0.f;
+                for (int w = 0; w < T; w++) v += q[w];
+                if (a.world > 1) {
+                    for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
+                    __threadfence_system();
+                } else {
+                    dst[fc * a.dst_col_stride + r0 + fv] = v;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty + 8 * slot);
+        }
         slot += nteams;
         if (slot >= nst) slot -= nst, par ^= 1;
     }
+    if (threadIdx.x == 0) trace_stamp(a, 4);                    // team 0 finished its last stage
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -655,8 +681,10 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
     const int T   = (upr + 31) / 32;
     if (T > (ncols > 2 ? WARPS_2CTA : WARPS_1CTA)) return false;
     P.T = T;
-    P.minb = (T > WARPS_2CTA || ncols > 2) ? 1 : 2;             // 24 registers of activations per column
-    P.minb = env_int("B200_GEMV_MINB", P.minb);
+    // Measured (profiles/r01/gemv_sweep_*.log): one 16-warp CTA per SM with a 226 KB ring beats two or three 8-warp
+    // CTAs at every Llama shape (fewer redundant activation loads, more teams per CTA), so it is the default;
+    // B200_GEMV_MINB=2 selects the small-CTA shape.
+    P.minb = env_int("B200_GEMV_MINB", 1);
     if (T > WARPS_2CTA || ncols > 2) P.minb = 1;
     const int row_bytes = (int) (k / type_block_elems(type)) * type_block_bytes(type);
     P.row_pitch = contiguous ? row_bytes : ((row_bytes + 15 + 15) & ~15);
@@ -680,7 +708,7 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
         for (int V = vfirst; V >= 2; V >>= 1) {
             // payload + 15 bytes of leading misalignment + 16 so word reads of a 2-byte-aligned tail stay inside
             P.stage_bytes = (V * P.row_pitch + 15 + 16 + 127) & ~127;
-            const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * V * T * 4 + 16;
+            const size_t per_stage = (size_t) P.stage_bytes + 2 * (size_t) ncols * V * T * 4 + 24;
             int nst = (int) (budget / per_stage);
             const int cap = want > 0 ? want : (P.nteams * 2 > 4 ? P.nteams * 2 : 4);
             if (nst > cap) nst = cap;
@@ -733,6 +761,12 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.dst_token_stride = g.dst_token_stride, a.dst_slot_stride = g.dst_slot_stride;
     a.world = g.world, a.rank = g.rank, a.row_offset = g.row_offset;
     a.dbg = env_int("B200_GEMV_DEBUG", 0);
+    a.trace = nullptr;
+    if (const char * tp = getenv("B200_GEMV_TRACE_PTR")) {      // tools/gemv_trace.py: base pointer, one slab per launch
+        static long long seq = 0;
+        const long long  cap = env_int("B200_GEMV_TRACE_LAUNCHES", 0);
+        if (seq < cap) a.trace = (unsigned long long *) strtoull(tp, nullptr, 0) + (size_t) (seq++) * 4096 * 8;
+    }
     gemv_peers peers = {};
     if (g.world > 1) {
         for (int r = 0; r < g.world && r < 16; r++) peers.dst[r] = g.peer_dst[r], peers.flag[r] = g.peer_flag[r];

@@ -55,8 +55,8 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
 template <bool INTERLEAVE>
 __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restrict__ x, int64_t x_stride,
                                                          uint8_t * __restrict__ y, int64_t y_pitch, int64_t k, bool vec) {
+    pdl_launch_dependents();   // first: the consuming GEMV may become resident and prefetch its weights right away
     pdl_wait();
-    pdl_launch_dependents();
     const q8_layout L = q8_soa_layout(k);
     quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.y * x_stride, k, y + (int64_t) blockIdx.y * y_pitch, L,
                                     blockIdx.x * 8 + (threadIdx.x >> 5), gridDim.x * 8, threadIdx.x & 31, vec);
