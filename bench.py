@@ -378,20 +378,62 @@ def main():
         xpp = {k: torch.rand((npp, k), device=dev, generator=gen) * 2 - 1 for k in ks}
         opp = {m: torch.empty((npp, m), device=dev) for _, _, m, _ in mms[:-1]}
 
+        # int8 "prefill planes" of the weights: built once per tensor (the ggml plug-in builds them lazily at first
+        # prefill and keeps them with the weight buffer); +1 byte of HBM per weight
+        t_pl0 = time.time()
+        planes = [qmm.build_plane(t, w, m, k) for (name, t, m, k), w in zip(mms[:-1], weights[:-1])]
+        torch.cuda.synchronize()
+        plane_build_s = time.time() - t_pl0
+        plane_bytes = sum(p_.numel() for p_ in planes)
+
         def prefill_step():
-            for (name, t, m, k), w in zip(mms[:-1], weights[:-1]):
-                qmm.mul_mat(t, w, xpp[k], m, k, out=opp[m])
+            for (name, t, m, k), pl in zip(mms[:-1], planes):
+                qmm.mul_mat_mmq(pl, xpp[k], m, k, out=opp[m])
             name, t, m, k = mms[-1]
             qmm.mul_mat(t, weights[-1], xs[k], m, k, out=out_local[m])
+
+        def prefill_step_transient():   # no cached planes: b200_mul_mat rebuilds each plane in its workspace
+            for (name, t, m, k), w in zip(mms[:-1], weights[:-1]):
+                qmm.mul_mat(t, w, xpp[k], m, k, out=opp[m])
 
         b0 = qmm.launch_count()
         prefill_step()
         torch.cuda.synchronize()
         pp_launches = qmm.launch_count() - b0
-        ms_pp = timed(prefill_step, 3, 1)
+        ms_pp = timed(prefill_step, 5, 2)
+        ms_pp_transient = timed(prefill_step_transient, 2, 1)
         flops = sum(2.0 * m * k * npp for _, _, m, k in mms[:-1])
-        pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 3,
-              "int8_tops": flops / ms_pp / 1e9, "launches_per_step": pp_launches}
+        # int8 tensor-core denominator: measured live with a cuBLASLt int8 GEMM (torch._int_mm), else 2 x measured bf16
+        int8_peak, int8_how = None, None
+        try:
+            A8 = torch.randint(-127, 127, (8192, 8192), dtype=torch.int8, device=dev)
+            B8 = torch.randint(-127, 127, (8192, 8192), dtype=torch.int8, device=dev)
+            for _ in range(3):
+                torch._int_mm(A8, B8)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                torch._int_mm(A8, B8)
+            e1.record()
+            torch.cuda.synchronize()
+            int8_peak = 2.0 * 8192 ** 3 * 10 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+            int8_how = "measured live: torch._int_mm 8192^3 (cuBLASLt int8), 10 back-to-back"
+            del A8, B8
+        except Exception as e:  # noqa: BLE001
+            try:
+                int8_peak = 2.0 * float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+                int8_how = "2 x MEASURED_PEAKS.json bf16_tflops (int8 probe failed: %s)" % str(e)[:60]
+            except Exception:  # noqa: BLE001
+                int8_peak, int8_how = 3180.0, "fallback 2 x 1.59 PFLOP/s"
+        tops = flops / ms_pp / 1e9
+        pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 5,
+              "launches_per_step": pp_launches,
+              "roofline": {"bound": "tensor", "achieved": tops, "peak": int8_peak, "unit": "TOP/s (int8)",
+                           "frac": tops / int8_peak, "peak_source": int8_how, "nominal_int8_tops": 4500.0,
+                           "frac_of_nominal": tops / 4500.0, "kernel": "k_mmq (tcgen05.mma kind::i8, TMEM accumulators)"},
+              "planes": {"cached": True, "bytes": plane_bytes, "build_seconds_once": plane_build_s},
+              "transient_planes": {"value": npp * 1e3 / ms_pp_transient, "unit": "tok/s", "ms_per_step": ms_pp_transient}}
+        del planes
 
     # ---- cpu baseline (rank 0, N = 1 only): the unmodified reference ggml-cpu on this host
     cpu = None

@@ -120,6 +120,30 @@ B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, con
                              float * dst, int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                              size_t workspace_bytes, b200_stream_t stream);
 
+/* ---- batched MUL_MAT on the tensor cores (n > 8) ---------------------------------------------------------------- */
+
+/*
+ * For n > 8 b200_mul_mat runs an int8 tcgen05 GEMM with TMEM accumulators instead of the GEMV.  It consumes an int8
+ * "prefill plane" of the weights: P[i][k] int8 with one fp32 scale per (row, 256-element chunk of k), and quantizes the
+ * activations to int8 with one scale per (column, chunk) -- ggml-cpu's q8_K granularity (ggml/src/ggml-common.h:329-334).
+ * Replaces quantize_mmq_q8_1_cuda + mul_mat_q + mul_mat_q_stream_k_fixup (ggml/src/ggml-cuda/quantize.cu:143-169,
+ * mmq.cuh:2516-2762, mmq.cu:3-97), whose per-32 scale application after every K=32 MMA cannot keep a B200 tensor core
+ * busy.  Results differ from the q8_1 path by rounding only and stay inside the harness bound (NMSE <= 5e-4 vs ggml-cpu).
+ *
+ * The plane depends only on the weights.  Callers that keep weights resident (the ggml plug-in's buffers) build it once
+ * per tensor with b200_mmq_build_plane and pass it to b200_mul_mat_mmq; b200_mul_mat without a plane builds a transient
+ * one in its workspace on every call (correct, slower).
+ */
+B200_API size_t b200_mmq_plane_size(int type, int64_t m, int64_t k);
+B200_API int    b200_mmq_build_plane(int type, const void * W, int64_t w_row_stride, void * plane, size_t plane_bytes,
+                                     int64_t m, int64_t k, b200_stream_t stream);
+B200_API size_t b200_mul_mat_mmq_workspace_size(int64_t m, int64_t n, int64_t k);
+B200_API int    b200_mul_mat_mmq(const void * plane, const float * x, int64_t x_row_stride, float * dst,
+                                 int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
+                                 size_t workspace_bytes, b200_stream_t stream);
+/* smallest n that b200_mul_mat sends to the tensor-core path (MMVQ_MAX_BATCH_SIZE + 1, ggml-cuda/mmvq.cuh:3) */
+B200_API int    b200_mmq_min_batch(void);
+
 /*
  * Same product with HOST activations and a HOST result: the activations are copied host->device, the matmul runs, and
  * dst is copied device->host, all stream-ordered on `stream` (the caller synchronizes the stream before reading dst).

@@ -47,4 +47,12 @@ size_t gemv_q8_smem_bytes(int64_t k, int ncols);
 int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring
 int    launch_gemv(const gemv_args & a, cudaStream_t stream);
 
+// ---- batched matmul on tcgen05 (mmq.cu): int8 "prefill plane" of a weight tensor + the GEMM that consumes it
+size_t mmq_plane_bytes(int64_t m, int64_t k);
+size_t mmq_workspace_bytes(int64_t n, int64_t k);
+int    launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
+                          cudaStream_t stream);
+int    launch_mmq(const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
+                  int64_t n, int64_t k, void * workspace, cudaStream_t stream);
+
 }  // namespace b200

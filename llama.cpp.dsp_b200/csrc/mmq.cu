@@ -1,0 +1,437 @@
+// mmq.cu -- batched (n > 8) quantized matmul on the 5th-generation tensor cores: tcgen05.mma kind::i8 with TMEM
+// accumulators, TMA-fed shared-memory tiles, fp32 scale-accumulate epilogue.  The prefill hot path.
+//
+// Replaces (reference): quantize_mmq_q8_1 + mul_mat_q<type,mmq_x,8,need_check> + load_tiles_* + vec_dot_*_mma +
+// mul_mat_q_stream_k_fixup as used by ggml_cuda_op_mul_mat_q (ggml/src/ggml-cuda/quantize.cu:40-127,143-169;
+// mmq.cuh:231-284,563-616,1338-1432,1608-1688,2243-2301,648-727,759-835,1723-1831,2516-2762; mmq.cu:3-97).
+//
+// Design (B200-first, not a port):
+//  * The reference applies one fp32 scale per 32 weights x one per 32 activations after EVERY K=32 mma.sync, on CUDA
+//    cores.  On B200 an M128 x N256 x K32 int8 MMA takes ~128 clocks while scaling its 32768 outputs takes ~1500 FMA-pipe
+//    clocks, so that scheme is capped near 10 % of the tensor peak.  Here scales are made SEPARABLE over
+//    256-element chunks of k: weights are re-expressed once per tensor as an int8 "prefill plane" with one fp32 scale
+//    per (row, chunk) -- w ~= s[i][c] * P[i][k] -- and activations are quantized with one scale per (column, chunk) --
+//    x ~= t[j][c] * Q[j][k], the same granularity ggml-cpu's q8_K uses for the K-quants (ggml-common.h:329-334).  Eight
+//    K=32 MMAs accumulate a chunk in TMEM as int32; the epilogue then does acc[i][j] += s[i][c] * t[j][c] * D[i][j] in
+//    fp32 registers while the tensor core works on the next chunk in the other TMEM buffer.
+//    Cost: +1 byte of HBM per weight for the plane (built lazily, cached by the caller; B200 has 180 GB) and a rounding
+//    error of ~3e-5 .. 1e-4 NMSE against ggml-cpu (bar 5e-4; tests/test_gpu_parity.py measures it).
+//  * Warp roles (one CTA per SM, 320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA
+//    issuer, warps 2..9 = epilogue (each owns 32 TMEM lanes x half of the tile's columns).
+#include "actquant.cuh"
+#include "dequant.cuh"
+#include "kernels.h"
+
+#include <cuda.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------ layouts
+constexpr int MMQ_KC = 256;   // scale granularity along k (one TMEM accumulation chunk)
+constexpr int MMQ_BM = 128;   // rows of W per CTA tile (= TMEM lanes)
+constexpr int MMQ_BK = 128;   // int8 elements per shared-memory stage row (= one 128-byte swizzle atom)
+
+static inline int64_t mmq_kpad(int64_t k) { return (k + MMQ_KC - 1) / MMQ_KC * MMQ_KC; }
+static inline size_t  align256(size_t v) { return (v + 255) & ~(size_t) 255; }
+
+// plane = [P: m x kpad int8, row-major][s: m x nchunks f32]
+size_t mmq_plane_bytes(int64_t m, int64_t k) {
+    const int64_t kp = mmq_kpad(k);
+    return align256((size_t) m * kp) + align256((size_t) m * (kp / MMQ_KC) * 4);
+}
+// activation scratch = [Q: n x kpad int8][t: nchunks x npad f32]   (npad = n rounded up to 4: float4 loads)
+static inline int64_t mmq_npad(int64_t n) { return (n + 3) & ~(int64_t) 3; }
+size_t mmq_act_bytes(int64_t n, int64_t k) {
+    const int64_t kp = mmq_kpad(k);
+    return align256((size_t) n * kp) + align256((size_t) (kp / MMQ_KC) * mmq_npad(n) * 4);
+}
+
+// ------------------------------------------------------------------------------------------------ plane builder
+// One thread per (row, 32-element group): dequantize the group bit-exactly, find the chunk's amax over the 8 threads
+// of the chunk, re-quantize to int8 with s = amax / 127.
+template <int TYPE>
+__global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict__ w, int64_t w_stride,
+                                                     int8_t * __restrict__ P, float * __restrict__ S, int64_t m, int64_t k,
+                                                     int64_t kp) {
+    const int64_t gpr = kp / 32;
+    const int64_t g   = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const bool    in  = g < gpr * m;
+    const int64_t row = in ? g / gpr : 0;
+    const int64_t gi  = in ? g % gpr : 0;
+    float v[32];
+    if (in && gi * 32 < k) {
+        dequant_group32<TYPE>(w + row * w_stride, gi, v);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = 0.f;
+    }
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i++) amax = fmaxf(amax, fabsf(v[i]));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    if (!in) return;
+    const float s  = amax / 127.0f;
+    const float is = s > 0.f ? 1.0f / s : 0.f;
+    uint32_t out[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int a = __float2int_rn(v[4 * i] * is), b = __float2int_rn(v[4 * i + 1] * is);
+        const int c = __float2int_rn(v[4 * i + 2] * is), d = __float2int_rn(v[4 * i + 3] * is);
+        out[i] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (c & 0xff) << 16) |
+                 ((uint32_t) (d & 0xff) << 24);
+    }
+    uint4 * dst = reinterpret_cast<uint4 *>(P + row * kp + gi * 32);
+    dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
+    dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    if ((gi & 7) == 0) S[row * (kp / MMQ_KC) + gi / 8] = s;
+}
+
+// ------------------------------------------------------------------------------------------------ activation quantizer
+// One warp per (column j, chunk c): 8 floats per lane, t = amax / 127, Q = rint(x / t).
+__global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ x, int64_t x_stride, int8_t * __restrict__ Q,
+                                                     float * __restrict__ Tt, int64_t n, int64_t k, int64_t kp,
+                                                     int64_t npad) {
+    const int     lane = threadIdx.x & 31;
+    const int64_t wid  = (int64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nch  = kp / MMQ_KC;
+    if (wid >= n * nch) return;
+    const int64_t j = wid / nch, c = wid % nch;
+    const int64_t e0 = c * MMQ_KC + lane * 8;
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) v[i] = e0 + i < k ? x[j * x_stride + e0 + i] : 0.f;
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    const float t  = amax / 127.0f;
+    const float it = t > 0.f ? 1.0f / t : 0.f;
+    uint32_t o2[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int a = __float2int_rn(v[4 * h] * it), b = __float2int_rn(v[4 * h + 1] * it);
+        const int cc = __float2int_rn(v[4 * h + 2] * it), d = __float2int_rn(v[4 * h + 3] * it);
+        o2[h] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (cc & 0xff) << 16) |
+                ((uint32_t) (d & 0xff) << 24);
+    }
+    *reinterpret_cast<uint2 *>(Q + j * kp + e0) = make_uint2(o2[0], o2[1]);
+    if (lane == 0) Tt[c * npad + j] = t;
+}
+
+// ------------------------------------------------------------------------------------------------ PTX helpers (sm_100a)
+__device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap * map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            dst_smem),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap * map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_result) {  // whole warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {  // whole warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], int8 x int8 -> int32, M x N x 32 per instruction; issued by ONE thread
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrive on an mbarrier when all previously issued MMAs of this thread have completed (implies fence::before_thread_sync)
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread t of the warp gets lane (taddr.lane + t), columns taddr.col .. +31
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows of 128 bytes, 8-row groups 1024 bytes apart
+// (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30), SBO >> 4 at [32,46), version 1 at [46,48),
+// layout SWIZZLE_128B = 2 at [61,64))
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
+    return (uint64_t) ((saddr & 0x3FFFFu) >> 4) | ((uint64_t) 1 << 16) | ((uint64_t) (1024 >> 4) << 32) |
+           ((uint64_t) 1 << 46) | ((uint64_t) 2 << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): D = S32 (2 at [4,6)), A = B = signed int8 (1 at [7,10) and
+// [10,13)), both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+__host__ __device__ constexpr uint32_t idesc_i8(int M, int N) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------ the GEMM kernel
+struct mmq_kargs {
+    const float * S;      // weight scales  [m][nch]
+    const float * Tt;     // activation scales [nch][npad] (+ slack: tiles may overhang)
+    float *       dst;    // [n][dst_stride], m contiguous
+    int64_t       dst_stride;
+    int           m, n, nch, npad;
+};
+
+template <int BN> struct mmq_shape {
+    static constexpr int NS      = BN == 256 ? 4 : 6;                 // shared-memory stages
+    static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // 16 KB
+    static constexpr int B_BYTES = BN * MMQ_BK;
+    static constexpr int STAGE   = A_BYTES + B_BYTES;
+    static constexpr int SMEM    = NS * STAGE + 1024;                 // + alignment slack (128-byte swizzle: 1024)
+    static constexpr int THREADS = 320;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensorMap mapA,
+                                                const __grid_constant__ CUtensorMap mapB, const mmq_kargs a) {
+    using SH = mmq_shape<BN>;
+    constexpr int NS = SH::NS;
+    extern __shared__ uint8_t mmq_smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * NS + 4];
+    __shared__ uint32_t tmem_slot;
+
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
+                   bar_tempty = bar_tfull + 16;
+    const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;
+    const int nch = a.nch, nkb = 2 * nch;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
+        for (int b = 0; b < 2; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, 8);
+        mbar_fence_init();
+        prefetch_tmap(&mapA);
+        prefetch_tmap(&mapB);
+    }
+    if (warp == 1) tmem_alloc<2 * BN>(smem_u32(&tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();                                                 // activations come from the quantizer kernel before us
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; kb++) {
+                const int s = kb % NS, ph = (kb / NS) & 1;
+                mbar_wait(bar_empty + 8 * s, ph ^ 1);
+                const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
+                mbar_expect_tx(bar_full + 8 * s, SH::STAGE);
+                tma_load_2d(sa, &mapA, kb * MMQ_BK, m0, bar_full + 8 * s);
+                tma_load_2d(sb, &mapB, kb * MMQ_BK, n0, bar_full + 8 * s);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_i8(MMQ_BM, BN);
+            for (int c = 0; c < nch; c++) {
+                const int buf = c & 1;
+                mbar_wait(bar_tempty + 8 * buf, ((c >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+                tc_fence_after();
+                for (int h = 0; h < 2; h++) {
+                    const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
+                    mbar_wait(bar_full + 8 * s, ph);
+                    tc_fence_after();
+                    const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
+                    const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
+#pragma unroll
+                    for (int kk = 0; kk < MMQ_BK / 32; kk++)   // +32 bytes along k inside the swizzle atom = +2 (>> 4)
+                        mma_i8(tmem + buf * BN, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) ((h | kk) != 0));
+                    mma_commit(bar_empty + 8 * s);               // stage reusable once these MMAs have read it
+                }
+                mma_commit(bar_tfull + 8 * buf);                 // chunk accumulated
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------------------------------ epilogue warps
+        constexpr int CW = BN / 2;                               // columns per warp
+        const int q = warp & 3, half = (warp - 2) >> 2;          // TMEM lane quarter (hardware: warp id % 4), column half
+        const int row = m0 + q * 32 + lane, col0 = half * CW;
+        float acc[CW];
+#pragma unroll
+        for (int i = 0; i < CW; i++) acc[i] = 0.f;
+        for (int c = 0; c < nch; c++) {
+            const int   buf = c & 1;
+            const float sic = row < a.m ? __ldg(a.S + (int64_t) row * nch + c) : 0.f;
+            const float4 * tp = reinterpret_cast<const float4 *>(a.Tt + (int64_t) c * a.npad + n0 + col0);
+            mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int g = 0; g < CW / 32; g++) {
+                uint32_t r[32];
+                tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0 + g * 32, r);
+                tmem_ld_wait();
+                if (g == CW / 32 - 1) {                          // accumulator fully read: hand it back to the tensor core
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                }
+#pragma unroll
+                for (int i4 = 0; i4 < 8; i4++) {
+                    const float4 t = __ldg(tp + g * 8 + i4);
+                    acc[g * 32 + 4 * i4 + 0] = fmaf((float) (int) r[4 * i4 + 0], sic * t.x, acc[g * 32 + 4 * i4 + 0]);
+                    acc[g * 32 + 4 * i4 + 1] = fmaf((float) (int) r[4 * i4 + 1], sic * t.y, acc[g * 32 + 4 * i4 + 1]);
+                    acc[g * 32 + 4 * i4 + 2] = fmaf((float) (int) r[4 * i4 + 2], sic * t.z, acc[g * 32 + 4 * i4 + 2]);
+                    acc[g * 32 + 4 * i4 + 3] = fmaf((float) (int) r[4 * i4 + 3], sic * t.w, acc[g * 32 + 4 * i4 + 3]);
+                }
+            }
+        }
+        if (row < a.m) {
+#pragma unroll
+            for (int i = 0; i < CW; i++) {
+                const int j = n0 + col0 + i;
+                if (j < a.n) a.dst[(int64_t) j * a.dst_stride + row] = acc[i];   // lanes = consecutive rows: coalesced
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<2 * BN>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+static encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void *                           p = nullptr;
+        cudaDriverEntryPointQueryResult  qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn) p;
+    }
+    return fn;
+}
+
+// row-major int8 matrix [rows][kp] -> tiles of box_rows x 128 bytes, 128-byte swizzle, zero fill outside
+static int make_map(CUtensorMap * map, const void * base, int64_t rows, int64_t kp, int box_rows) {
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) return B200_ERR_CUDA;
+    const cuuint64_t dims[2]    = {(cuuint64_t) kp, (cuuint64_t) rows};
+    const cuuint64_t strides[1] = {(cuuint64_t) kp};
+    const cuuint32_t box[2]     = {(cuuint32_t) MMQ_BK, (cuuint32_t) box_rows};
+    const cuuint32_t estr[2]    = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(g_last_cuda_error, sizeof(g_last_cuda_error), "cuTensorMapEncodeTiled failed: %d", (int) r);
+        return B200_ERR_CUDA;
+    }
+    return B200_OK;
+}
+
+int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
+                       cudaStream_t stream) {
+    if (m == 0 || k == 0) return B200_OK;
+    const int64_t kp = mmq_kpad(k);
+    int8_t *      P  = (int8_t *) plane;
+    float *       S  = (float *) ((uint8_t *) plane + align256((size_t) m * kp));
+    const int64_t total = (kp / 32) * m;
+    const unsigned grid = (unsigned) ((total + 255) / 256);
+    const uint8_t * wp = (const uint8_t *) W;
+    switch (type) {
+        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        default: return B200_ERR_TYPE;
+    }
+    note_launch();
+    return check_cuda(cudaGetLastError(), "k_plane_build");
+}
+
+// workspace of the GEMM proper: quantized activations + their scales (+ slack for overhanging tiles)
+size_t mmq_workspace_bytes(int64_t n, int64_t k) { return mmq_act_bytes(n, k) + 2048; }
+
+template <int BN>
+static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
+    static bool attr_set = false;
+    auto kern = k_mmq<BN>;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_shape<BN>::SMEM));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) ((a.m + MMQ_BM - 1) / MMQ_BM), (unsigned) ((a.n + BN - 1) / BN), 1);
+    cfg.blockDim         = dim3(mmq_shape<BN>::THREADS, 1, 1);
+    cfg.dynamicSmemBytes = mmq_shape<BN>::SMEM;
+    cfg.stream           = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a));
+    note_launch();
+    return B200_OK;
+}
+
+int launch_mmq(const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m, int64_t n,
+               int64_t k, void * workspace, cudaStream_t stream) {
+    if (m == 0 || n == 0) return B200_OK;
+    static int sm_count = 0;
+    if (!sm_count) {
+        int dev = 0;
+        B200_CUDA_TRY(cudaGetDevice(&dev));
+        B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
+    int8_t * Q  = (int8_t *) workspace;
+    float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
+    {
+        const int64_t warps = n * nch;
+        k_quantize_x8<<<(unsigned) ((warps + 7) / 8), 256, 0, stream>>>(x, x_stride, Q, Tt, n, k, kp, npad);
+        note_launch();
+        B200_CUDA_TRY(cudaGetLastError());
+    }
+    // tile width: 256 columns unless that leaves most SMs idle
+    const int64_t mt = (m + MMQ_BM - 1) / MMQ_BM;
+    const char *  e  = getenv("B200_MMQ_BN");
+    int bn = e && *e ? atoi(e) : ((n <= 128 || mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
+    CUtensorMap mapA, mapB;
+    int st = make_map(&mapA, plane, m, kp, MMQ_BM);
+    if (st != B200_OK) return st;
+    st = make_map(&mapB, Q, n, kp, bn);
+    if (st != B200_OK) return st;
+    mmq_kargs a;
+    a.S   = (const float *) ((const uint8_t *) plane + align256((size_t) m * kp));
+    a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
+    a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad;
+    return bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, stream) : launch_mmq_bn<128>(mapA, mapB, a, stream);
+}
+
+}  // namespace b200

@@ -22,7 +22,8 @@ EXPORTS = [
     "b200_qmm_abi_version", "b200_status_string", "b200_last_cuda_error", "b200_device_ok", "b200_sm_count",
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
-    "b200_mul_mat", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
+    "b200_mul_mat", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
+    "b200_mul_mat_mmq", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_fused", "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
 ]
 
@@ -64,6 +65,12 @@ def lib():
     L.b200_mul_mat_workspace_size.restype = sz
     L.b200_mul_mat_workspace_size.argtypes = [i32, i64, i64, i64]
     L.b200_mul_mat.argtypes = [i32, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
+    L.b200_mmq_plane_size.restype = sz
+    L.b200_mmq_plane_size.argtypes = [i32, i64, i64]
+    L.b200_mmq_build_plane.argtypes = [i32, vp, i64, vp, sz, i64, i64, vp]
+    L.b200_mul_mat_mmq_workspace_size.restype = sz
+    L.b200_mul_mat_mmq_workspace_size.argtypes = [i64, i64, i64]
+    L.b200_mul_mat_mmq.argtypes = [vp, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
     L.b200_mul_mat_host_workspace_size.restype = sz
     L.b200_mul_mat_host_workspace_size.argtypes = [i32, i64, i64, i64]
     L.b200_mul_mat_host.argtypes = [i32, vp, i64, vp, vp, i64, i64, i64, vp, sz, vp]
@@ -181,6 +188,29 @@ def mul_mat(t, w, x, m, k, out=None, stream=None):
     ws, wsz = _workspace(x.device, lib().b200_mul_mat_workspace_size(t, m, n, k))
     check(lib().b200_mul_mat(t, w.data_ptr(), 0, x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
                              dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
+    return dst
+
+
+def build_plane(t, w, m, k, stream=None):
+    """int8 prefill plane of a weight tensor (built once per tensor, +1 byte per weight): uint8 cuda tensor"""
+    import torch
+    _require_cuda(w)
+    nbytes = lib().b200_mmq_plane_size(t, m, k)
+    plane = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+    check(lib().b200_mmq_build_plane(t, w.data_ptr(), 0, plane.data_ptr(), nbytes, m, k, _stream_ptr(stream)))
+    return plane
+
+
+def mul_mat_mmq(plane, x, m, k, out=None, stream=None):
+    """tensor-core batched matmul against a prepared plane; x: [n, k] f32 cuda -> dst [n, m] f32"""
+    import torch
+    _require_cuda(plane, x)
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] == k
+    n = x.shape[0]
+    dst = out if out is not None else torch.empty((n, m), dtype=torch.float32, device=x.device)
+    ws, wsz = _workspace(x.device, lib().b200_mul_mat_mmq_workspace_size(m, n, k))
+    check(lib().b200_mul_mat_mmq(plane.data_ptr(), x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
+                                 dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
     return dst
 
 

@@ -143,3 +143,33 @@ def random_blocks(t, nrows, k, rng, scale=0.02):
     else:
         raise ValueError(t)
     return raw.reshape(nrows, -1)
+
+
+def mul_mat_plane(t, w, x, m, k, kc=256):
+    """numpy restatement of the tensor-core path's arithmetic (llama.cpp.dsp_b200/csrc/mmq.cu): weights dequantized
+    bit-exactly, re-expressed as int8 with one f32 scale per (row, 256-chunk); activations int8 with one scale per
+    (column, chunk); exact integer chunk dot products; f32 scale-accumulate in chunk order.  -> f32 [n, m]"""
+    f32 = np.float32
+    x = np.ascontiguousarray(x, dtype=f32).reshape(-1, k)
+    n = x.shape[0]
+    kp = (k + kc - 1) // kc * kc
+    Wf = np.zeros((m, kp), dtype=f32)
+    Wf[:, :k] = dequantize(t, w, k)
+    Xf = np.zeros((n, kp), dtype=f32)
+    Xf[:, :k] = x
+
+    def q8(a):
+        c = a.reshape(a.shape[0], kp // kc, kc)
+        s = (np.abs(c).max(-1) / f32(127.0)).astype(f32)
+        inv = np.where(s > 0, f32(1.0) / np.where(s > 0, s, f32(1.0)), f32(0.0)).astype(f32)
+        q = np.rint((c * inv[:, :, None]).astype(f32)).astype(np.int32)
+        return q, s
+
+    P, S = q8(Wf)
+    Q, T = q8(Xf)
+    acc = np.zeros((n, m), dtype=f32)
+    for c in range(kp // kc):
+        D = (Q[:, c, :].astype(np.int64) @ P[:, c, :].astype(np.int64).T).astype(f32)        # [n, m], exact
+        st = (S[None, :, c] * T[:, None, c]).astype(f32)
+        acc = (D.astype(np.float64) * st.astype(np.float64) + acc.astype(np.float64)).astype(f32)   # one fma rounding
+    return acc

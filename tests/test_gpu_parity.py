@@ -86,7 +86,9 @@ def check_mul_mat(qmm, t, w, x, m, k):
     torch.cuda.synchronize()
     got = got.cpu().numpy()
     assert np.isfinite(got).all()
-    tight = qref.mul_mat(t, w, x, m, k, "q8_1")
+    n = x.reshape(-1, k).shape[0]
+    # n <= 8: dp4a GEMV with q8_1 activations; n > 8: int8 tensor-core path with per-256 scales (qref.mul_mat_plane)
+    tight = qref.mul_mat(t, w, x, m, k, "q8_1") if n < qmm.lib().b200_mmq_min_batch() else qref.mul_mat_plane(t, w, x, m, k)
     cpu = qref.mul_mat(t, w, x, m, k, "cpu")
     assert qref.nmse(tight, got) < NMSE_TIGHT, ("tight", qref.nmse(tight, got))
     assert qref.nmse(cpu, got) < NMSE_HARNESS, ("harness", qref.nmse(cpu, got))
@@ -152,6 +154,45 @@ def test_mul_mat_realistic_quantized_weights_vs_exact(qmm, name, t):
     got = qmm.mul_mat(t, dev(w), dev(x), m, k).cpu().numpy()
     exact = qref.mul_mat(t, w, x, m, k, "f64")
     assert qref.nmse(exact, got) < NMSE_HARNESS
+
+
+# ------------------------------------------------------------------------------------------------ MMQ (tcgen05 int8)
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("m,k,n", [(128, 256, 16), (16, 256, 9), (300, 1024, 33), (257, 2048, 129), (512, 4096, 512),
+                                   (1000, 512, 300)])
+def test_mmq_prepared_plane(qmm, name, t, m, k, n):
+    """tensor-core path against a prepared plane: tight vs the numpy restatement of its arithmetic (catches descriptor /
+    swizzle / pipeline bugs), harness bound vs ggml-cpu semantics and vs the exact f64 product"""
+    rng = np.random.default_rng(m + k + n)
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    wd = dev(w)
+    plane = qmm.build_plane(t, wd, m, k)
+    got = qmm.mul_mat_mmq(plane, dev(x), m, k).cpu().numpy()
+    assert np.isfinite(got).all()
+    assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got) < NMSE_TIGHT
+    assert qref.nmse(qref.mul_mat(t, w, x, m, k, "cpu"), got) < NMSE_HARNESS
+    assert qref.nmse(qref.mul_mat(t, w, x, m, k, "f64"), got) < NMSE_HARNESS
+
+
+@pytest.mark.parametrize("name,t", [("q4_0", qref.Q4_0), ("q8_0", qref.Q8_0)])
+def test_mmq_k_not_multiple_of_chunk(qmm, name, t):
+    rng = np.random.default_rng(3)
+    m, k, n = 64, 96 + 256, 20
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    check_mul_mat(qmm, t, w, x, m, k)
+
+
+def test_mmq_normal_weights_through_real_quantizer(qmm, golden):
+    # golden weights went through the reference's own quantizer from N(0,1) data: the realistic error case
+    for name, t in TYPES:
+        w, x = golden["w_" + name], golden["mm_x"]
+        m, k = w.shape[0], x.shape[1]
+        xx = np.tile(x, (12, 1))[:17]
+        got = qmm.mul_mat(t, dev(w), dev(xx), m, k).cpu().numpy()
+        cpu = qref.mul_mat(t, w, xx, m, k, "cpu")
+        assert qref.nmse(cpu, got) < NMSE_HARNESS, (name, qref.nmse(cpu, got))
 
 
 # ------------------------------------------------------------------------------------------------ full-size properties
