@@ -38,10 +38,12 @@ constexpr int MMQ_BK = 128;   // int8 elements per shared-memory stage row (= on
 static inline int64_t mmq_kpad(int64_t k) { return (k + MMQ_KC - 1) / MMQ_KC * MMQ_KC; }
 static inline size_t  align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
-// plane = [P: m x kpad int8, row-major][s: m x nchunks f32]
+// plane = [P: m x kpad int8, row-major][s: nchunks x mpad f32, chunk-major so that a tile's 128 row scales of one chunk
+// are one contiguous bulk copy]   (mpad = m rounded up to the tile height)
+static inline int64_t mmq_mpad(int64_t m) { return (m + MMQ_BM - 1) / MMQ_BM * MMQ_BM; }
 size_t mmq_plane_bytes(int64_t m, int64_t k) {
     const int64_t kp = mmq_kpad(k);
-    return align256((size_t) m * kp) + align256((size_t) m * (kp / MMQ_KC) * 4);
+    return align256((size_t) m * kp) + align256((size_t) mmq_mpad(m) * (kp / MMQ_KC) * 4);
 }
 // activation scratch = [Q: n x kpad int8][t: nchunks x npad f32]   (npad = n rounded up to 4: float4 loads)
 static inline int64_t mmq_npad(int64_t n) { return (n + 3) & ~(int64_t) 3; }
@@ -56,7 +58,7 @@ size_t mmq_act_bytes(int64_t n, int64_t k) {
 template <int TYPE>
 __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict__ w, int64_t w_stride,
                                                      int8_t * __restrict__ P, float * __restrict__ S, int64_t m, int64_t k,
-                                                     int64_t kp) {
+                                                     int64_t kp, int64_t mpad) {
     const int64_t gpr = kp / 32;
     const int64_t g   = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const bool    in  = g < gpr * m;
@@ -89,7 +91,7 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
     uint4 * dst = reinterpret_cast<uint4 *>(P + row * kp + gi * 32);
     dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
     dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
-    if ((gi & 7) == 0) S[row * (kp / MMQ_KC) + gi / 8] = s;
+    if ((gi & 7) == 0) S[(gi / 8) * mpad + row] = s;
 }
 
 // ------------------------------------------------------------------------------------------------ activation quantizer
@@ -190,11 +192,11 @@ __host__ __device__ constexpr uint32_t idesc_i8(int M, int N) {
 
 // ------------------------------------------------------------------------------------------------ the GEMM kernel
 struct mmq_kargs {
-    const float * S;      // weight scales  [m][nch]
+    const float * S;      // weight scales  [nch][mpad]
     const float * Tt;     // activation scales [nch][npad] (+ slack: tiles may overhang)
     float *       dst;    // [n][dst_stride], m contiguous
     int64_t       dst_stride;
-    int           m, n, nch, npad;
+    int           m, n, nch, npad, mpad;
 };
 
 template <int BN> struct mmq_shape {
@@ -202,7 +204,9 @@ template <int BN> struct mmq_shape {
     static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // 16 KB
     static constexpr int B_BYTES = BN * MMQ_BK;
     static constexpr int STAGE   = A_BYTES + B_BYTES;
-    static constexpr int SMEM    = NS * STAGE + 1024;                 // + alignment slack (128-byte swizzle: 1024)
+    static constexpr int NSC     = 4;                                 // ring of per-chunk scale vectors
+    static constexpr int SC_FLTS = MMQ_BM + BN;                       // [128 row scales][BN column scales]
+    static constexpr int SMEM    = NS * STAGE + NSC * SC_FLTS * 4 + 1024;   // + alignment slack (128-byte swizzle: 1024)
     static constexpr int THREADS = 320;
 };
 
@@ -212,19 +216,21 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
     using SH = mmq_shape<BN>;
     constexpr int NS = SH::NS;
     extern __shared__ uint8_t mmq_smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * NS + 4];
+    __shared__ __align__(8) uint64_t bars[2 * NS + 4 + 2 * SH::NSC];
     __shared__ uint32_t tmem_slot;
 
     const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
-                   bar_tempty = bar_tfull + 16;
+                   bar_tempty = bar_tfull + 16, bar_sfull = bar_tempty + 16, bar_sempty = bar_sfull + 8 * SH::NSC;
+    const uint32_t scales = tiles + NS * SH::STAGE;             // shared address of the scale ring
     const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;
     const int nch = a.nch, nkb = 2 * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
         for (int b = 0; b < 2; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, 8);
+        for (int b = 0; b < SH::NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, 8);
         mbar_fence_init();
         prefetch_tmap(&mapA);
         prefetch_tmap(&mapB);
@@ -241,6 +247,14 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             for (int kb = 0; kb < nkb; kb++) {
+                if ((kb & 1) == 0) {                             // this chunk's scale vectors, ahead of its tiles
+                    const int c = kb >> 1, b = c % SH::NSC;
+                    mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
+                    const uint32_t sd = scales + b * SH::SC_FLTS * 4;
+                    mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
+                    tma_load_1d(sd, a.S + (int64_t) c * a.mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + n0, BN * 4, bar_sfull + 8 * b);
+                }
                 const int s = kb % NS, ph = (kb / NS) & 1;
                 mbar_wait(bar_empty + 8 * s, ph ^ 1);
                 const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
@@ -279,10 +293,13 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
         float acc[CW];
 #pragma unroll
         for (int i = 0; i < CW; i++) acc[i] = 0.f;
+        const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         for (int c = 0; c < nch; c++) {
-            const int   buf = c & 1;
-            const float sic = row < a.m ? __ldg(a.S + (int64_t) row * nch + c) : 0.f;
-            const float4 * tp = reinterpret_cast<const float4 *>(a.Tt + (int64_t) c * a.npad + n0 + col0);
+            const int buf = c & 1, sb = c % SH::NSC;
+            mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1);
+            const float *  sv  = sring + sb * SH::SC_FLTS;
+            const float    sic = sv[q * 32 + lane];
+            const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);   // warp-uniform: broadcast reads
             mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
             tc_fence_after();
 #pragma unroll
@@ -297,13 +314,15 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
                 }
 #pragma unroll
                 for (int i4 = 0; i4 < 8; i4++) {
-                    const float4 t = __ldg(tp + g * 8 + i4);
+                    const float4 t = tp[g * 8 + i4];
                     acc[g * 32 + 4 * i4 + 0] = fmaf((float) (int) r[4 * i4 + 0], sic * t.x, acc[g * 32 + 4 * i4 + 0]);
                     acc[g * 32 + 4 * i4 + 1] = fmaf((float) (int) r[4 * i4 + 1], sic * t.y, acc[g * 32 + 4 * i4 + 1]);
                     acc[g * 32 + 4 * i4 + 2] = fmaf((float) (int) r[4 * i4 + 2], sic * t.z, acc[g * 32 + 4 * i4 + 2]);
                     acc[g * 32 + 4 * i4 + 3] = fmaf((float) (int) r[4 * i4 + 3], sic * t.w, acc[g * 32 + 4 * i4 + 3]);
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);     // scale vectors consumed
         }
         if (row < a.m) {
 #pragma unroll
@@ -360,15 +379,15 @@ int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane,
     const int64_t kp = mmq_kpad(k);
     int8_t *      P  = (int8_t *) plane;
     float *       S  = (float *) ((uint8_t *) plane + align256((size_t) m * kp));
-    const int64_t total = (kp / 32) * m;
+    const int64_t total = (kp / 32) * m, mpad = mmq_mpad(m);
     const unsigned grid = (unsigned) ((total + 255) / 256);
     const uint8_t * wp = (const uint8_t *) W;
     switch (type) {
-        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
-        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
-        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
-        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
-        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp); break;
+        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
+        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
+        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
+        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
+        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
         default: return B200_ERR_TYPE;
     }
     note_launch();
@@ -430,7 +449,7 @@ int launch_mmq(const void * plane, const float * x, int64_t x_stride, float * ds
     mmq_kargs a;
     a.S   = (const float *) ((const uint8_t *) plane + align256((size_t) m * kp));
     a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
-    a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad;
+    a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
     return bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, stream) : launch_mmq_bn<128>(mapA, mapB, a, stream);
 }
 
