@@ -388,7 +388,7 @@ def main():
 
         def prefill_step():
             for (name, t, m, k), pl in zip(mms[:-1], planes):
-                qmm.mul_mat_mmq(pl, xpp[k], m, k, out=opp[m])
+                qmm.mul_mat_mmq(t, pl, xpp[k], m, k, out=opp[m])
             name, t, m, k = mms[-1]
             qmm.mul_mat(t, weights[-1], xs[k], m, k, out=out_local[m])
 

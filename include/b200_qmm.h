@@ -132,13 +132,14 @@ B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, con
  *
  * The plane depends only on the weights.  Callers that keep weights resident (the ggml plug-in's buffers) build it once
  * per tensor with b200_mmq_build_plane and pass it to b200_mul_mat_mmq; b200_mul_mat without a plane builds a transient
- * one in its workspace on every call (correct, slower).
+ * one in its workspace on every call (correct, slower).  Q8_0 keeps TWO planes (value + residual, ~15 bits) and runs the
+ * GEMM twice, because one int8 per-256 plane would discard the dynamic range of its per-32 scales.
  */
 B200_API size_t b200_mmq_plane_size(int type, int64_t m, int64_t k);
 B200_API int    b200_mmq_build_plane(int type, const void * W, int64_t w_row_stride, void * plane, size_t plane_bytes,
                                      int64_t m, int64_t k, b200_stream_t stream);
 B200_API size_t b200_mul_mat_mmq_workspace_size(int64_t m, int64_t n, int64_t k);
-B200_API int    b200_mul_mat_mmq(const void * plane, const float * x, int64_t x_row_stride, float * dst,
+B200_API int    b200_mul_mat_mmq(int type, const void * plane, const float * x, int64_t x_row_stride, float * dst,
                                  int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                                  size_t workspace_bytes, b200_stream_t stream);
 /* smallest n that b200_mul_mat sends to the tensor-core path (MMVQ_MAX_BATCH_SIZE + 1, ggml-cuda/mmvq.cuh:3) */

@@ -143,7 +143,7 @@ static size_t ws_align(size_t v) { return (v + 255) & ~(size_t) 255; }
 
 size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     if (!weight_type(type) || k <= 0 || n <= 0 || m <= 0) return 0;
-    if (n >= mmq_min_batch()) return ws_align(mmq_plane_bytes(m, k)) + mmq_workspace_bytes(n, k);
+    if (n >= mmq_min_batch()) return ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k)) + mmq_workspace_bytes(n, k);
     if (use_fused_quant(n, k)) return 0;
     return (size_t) n * q8_soa_layout(k).bytes;
 }
@@ -151,14 +151,14 @@ size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
 int    b200_mmq_min_batch(void) { return mmq_min_batch(); }
 size_t b200_mmq_plane_size(int type, int64_t m, int64_t k) {
     if (!weight_type(type) || m < 0 || k < 0 || k % blck_of(type) != 0) return 0;
-    return mmq_plane_bytes(m, k);
+    return mmq_nplanes(type) * mmq_plane_bytes(m, k);
 }
 int b200_mmq_build_plane(int type, const void * W, int64_t w_row_stride, void * plane, size_t plane_bytes, int64_t m,
                          int64_t k, b200_stream_t stream) {
     int st = check_weights(type, W, w_row_stride, k);
     if (st != B200_OK) return st;
     if (m < 0) return B200_ERR_SHAPE;
-    if (!plane || plane_bytes < mmq_plane_bytes(m, k)) return B200_ERR_WORKSPACE;
+    if (!plane || plane_bytes < mmq_nplanes(type) * mmq_plane_bytes(m, k)) return B200_ERR_WORKSPACE;
     if ((uintptr_t) plane % 256 != 0) return B200_ERR_ALIGNMENT;
     return launch_plane_build(type, W, w_row_stride, plane, m, k, (cudaStream_t) stream);
 }
@@ -166,15 +166,16 @@ size_t b200_mul_mat_mmq_workspace_size(int64_t m, int64_t n, int64_t k) {
     (void) m;
     return n > 0 && k > 0 ? mmq_workspace_bytes(n, k) : 0;
 }
-int b200_mul_mat_mmq(const void * plane, const float * x, int64_t x_row_stride, float * dst, int64_t dst_row_stride,
+int b200_mul_mat_mmq(int type, const void * plane, const float * x, int64_t x_row_stride, float * dst, int64_t dst_row_stride,
                      int64_t m, int64_t n, int64_t k, void * workspace, size_t workspace_bytes, b200_stream_t stream) {
+    if (!weight_type(type)) return B200_ERR_TYPE;
     if (m < 0 || n < 0 || k <= 0 || x_row_stride < k || dst_row_stride < m) return B200_ERR_SHAPE;
     if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
     if (m == 0 || n == 0) return B200_OK;
     if (!plane || (uintptr_t) plane % 256 != 0) return B200_ERR_ALIGNMENT;
     if (!workspace || workspace_bytes < mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
     if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
-    return launch_mmq(plane, x, x_row_stride, dst, dst_row_stride, m, n, k, workspace, (cudaStream_t) stream);
+    return launch_mmq(type, plane, x, x_row_stride, dst, dst_row_stride, m, n, k, workspace, (cudaStream_t) stream);
 }
 
 int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x, int64_t x_row_stride, float * dst,
@@ -192,12 +193,12 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
         return B200_OK;
     }
     if (n >= mmq_min_batch()) {  // tensor-core path with a transient plane carved from the workspace
-        const size_t pb = ws_align(mmq_plane_bytes(m, k));
+        const size_t pb = ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k));
         if (!workspace || workspace_bytes < pb + mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
         if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
         st = launch_plane_build(type, W, w_row_stride, workspace, m, k, stream);
         if (st != B200_OK) return st;
-        return launch_mmq(workspace, x, x_row_stride, dst, dst_row_stride, m, n, k, (uint8_t *) workspace + pb, stream);
+        return launch_mmq(type, workspace, x, x_row_stride, dst, dst_row_stride, m, n, k, (uint8_t *) workspace + pb, stream);
     }
     const int maxc = gemv_max_cols(type, k);
     if (maxc < 1) return B200_ERR_UNSUPPORTED;

@@ -52,7 +52,8 @@ size_t mmq_plane_bytes(int64_t m, int64_t k);
 size_t mmq_workspace_bytes(int64_t n, int64_t k);
 int    launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
                           cudaStream_t stream);
-int    launch_mmq(const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
+int    mmq_nplanes(int type);   // int8 planes per weight tensor (2 for Q8_0: value + residual)
+int    launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                   int64_t n, int64_t k, void * workspace, cudaStream_t stream);
 
 }  // namespace b200

@@ -45,6 +45,8 @@ size_t mmq_plane_bytes(int64_t m, int64_t k) {
     const int64_t kp = mmq_kpad(k);
     return align256((size_t) m * kp) + align256((size_t) mmq_mpad(m) * (kp / MMQ_KC) * 4);
 }
+// Q8_0 keeps two planes (value + residual); everything else one
+int mmq_nplanes(int type) { return type == B200_TYPE_Q8_0 ? 2 : 1; }
 // activation scratch = [Q: n x kpad int8][t: nchunks x npad f32]   (npad = n rounded up to 4: float4 loads)
 static inline int64_t mmq_npad(int64_t n) { return (n + 3) & ~(int64_t) 3; }
 size_t mmq_act_bytes(int64_t n, int64_t k) {
@@ -55,10 +57,13 @@ size_t mmq_act_bytes(int64_t n, int64_t k) {
 // ------------------------------------------------------------------------------------------------ plane builder
 // One thread per (row, 32-element group): dequantize the group bit-exactly, find the chunk's amax over the 8 threads
 // of the chunk, re-quantize to int8 with s = amax / 127.
-template <int TYPE>
+// RESID: build the plane of the residual w - s0 * P0 left by a first plane (P0, S0): two int8 planes give ~15 bits
+// of weight precision, used for Q8_0 whose 8-bit blocks would otherwise lose their per-32 scales' dynamic range.
+template <int TYPE, bool RESID>
 __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict__ w, int64_t w_stride,
                                                      int8_t * __restrict__ P, float * __restrict__ S, int64_t m, int64_t k,
-                                                     int64_t kp, int64_t mpad) {
+                                                     int64_t kp, int64_t mpad, const int8_t * __restrict__ P0,
+                                                     const float * __restrict__ S0) {
     const int64_t gpr = kp / 32;
     const int64_t g   = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const bool    in  = g < gpr * m;
@@ -70,6 +75,12 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
     } else {
 #pragma unroll
         for (int i = 0; i < 32; i++) v[i] = 0.f;
+    }
+    if (RESID && in) {
+        const float    s0 = S0[(gi / 8) * mpad + row];
+        const int8_t * p0 = P0 + row * kp + gi * 32;
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = __fsub_rn(v[i], __fmul_rn(s0, (float) p0[i]));
     }
     float amax = 0.f;
 #pragma unroll
@@ -197,6 +208,7 @@ struct mmq_kargs {
     float *       dst;    // [n][dst_stride], m contiguous
     int64_t       dst_stride;
     int           m, n, nch, npad, mpad;
+    int           accumulate;   // dst += result (second plane of a two-plane weight)
 };
 
 template <int BN> struct mmq_shape {
@@ -328,7 +340,10 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
 #pragma unroll
             for (int i = 0; i < CW; i++) {
                 const int j = n0 + col0 + i;
-                if (j < a.n) a.dst[(int64_t) j * a.dst_stride + row] = acc[i];   // lanes = consecutive rows: coalesced
+                if (j < a.n) {                                   // lanes = consecutive rows: coalesced
+                    float * d = a.dst + (int64_t) j * a.dst_stride + row;
+                    *d = a.accumulate ? acc[i] + *d : acc[i];
+                }
             }
         }
     }
@@ -383,14 +398,21 @@ int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane,
     const unsigned grid = (unsigned) ((total + 255) / 256);
     const uint8_t * wp = (const uint8_t *) W;
     switch (type) {
-        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
-        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
-        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
-        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
-        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad); break;
+        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
+        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
+        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
+        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
+        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
         default: return B200_ERR_TYPE;
     }
     note_launch();
+    if (mmq_nplanes(type) == 2) {  // residual plane right behind the first one
+        uint8_t * plane2 = (uint8_t *) plane + mmq_plane_bytes(m, k);
+        int8_t *  P2 = (int8_t *) plane2;
+        float *   S2 = (float *) (plane2 + align256((size_t) m * kp));
+        k_plane_build<B200_TYPE_Q8_0, true><<<grid, 256, 0, stream>>>(wp, w_stride, P2, S2, m, k, kp, mpad, P, S);
+        note_launch();
+    }
     return check_cuda(cudaGetLastError(), "k_plane_build");
 }
 
@@ -419,8 +441,8 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
     return B200_OK;
 }
 
-int launch_mmq(const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m, int64_t n,
-               int64_t k, void * workspace, cudaStream_t stream) {
+int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
+               int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
     if (m == 0 || n == 0) return B200_OK;
     static int sm_count = 0;
     if (!sm_count) {
@@ -442,15 +464,21 @@ int launch_mmq(const void * plane, const float * x, int64_t x_stride, float * ds
     const char *  e  = getenv("B200_MMQ_BN");
     int bn = e && *e ? atoi(e) : ((n <= 128 || mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
     CUtensorMap mapA, mapB;
-    int st = make_map(&mapA, plane, m, kp, MMQ_BM);
+    int st = make_map(&mapB, Q, n, kp, bn);
     if (st != B200_OK) return st;
-    st = make_map(&mapB, Q, n, kp, bn);
-    if (st != B200_OK) return st;
-    mmq_kargs a;
-    a.S   = (const float *) ((const uint8_t *) plane + align256((size_t) m * kp));
-    a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
-    a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
-    return bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, stream) : launch_mmq_bn<128>(mapA, mapB, a, stream);
+    for (int pl = 0; pl < mmq_nplanes(type); pl++) {
+        const uint8_t * pb = (const uint8_t *) plane + (size_t) pl * mmq_plane_bytes(m, k);
+        st = make_map(&mapA, pb, m, kp, MMQ_BM);
+        if (st != B200_OK) return st;
+        mmq_kargs a;
+        a.S   = (const float *) (pb + align256((size_t) m * kp));
+        a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
+        a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
+        a.accumulate = pl > 0;
+        st = bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, stream) : launch_mmq_bn<128>(mapA, mapB, a, stream);
+        if (st != B200_OK) return st;
+    }
+    return B200_OK;
 }
 
 }  // namespace b200

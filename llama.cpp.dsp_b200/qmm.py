@@ -70,7 +70,7 @@ def lib():
     L.b200_mmq_build_plane.argtypes = [i32, vp, i64, vp, sz, i64, i64, vp]
     L.b200_mul_mat_mmq_workspace_size.restype = sz
     L.b200_mul_mat_mmq_workspace_size.argtypes = [i64, i64, i64]
-    L.b200_mul_mat_mmq.argtypes = [vp, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
+    L.b200_mul_mat_mmq.argtypes = [i32, vp, vp, i64, vp, i64, i64, i64, i64, vp, sz, vp]
     L.b200_mul_mat_host_workspace_size.restype = sz
     L.b200_mul_mat_host_workspace_size.argtypes = [i32, i64, i64, i64]
     L.b200_mul_mat_host.argtypes = [i32, vp, i64, vp, vp, i64, i64, i64, vp, sz, vp]
@@ -201,7 +201,7 @@ def build_plane(t, w, m, k, stream=None):
     return plane
 
 
-def mul_mat_mmq(plane, x, m, k, out=None, stream=None):
+def mul_mat_mmq(t, plane, x, m, k, out=None, stream=None):
     """tensor-core batched matmul against a prepared plane; x: [n, k] f32 cuda -> dst [n, m] f32"""
     import torch
     _require_cuda(plane, x)
@@ -209,7 +209,7 @@ def mul_mat_mmq(plane, x, m, k, out=None, stream=None):
     n = x.shape[0]
     dst = out if out is not None else torch.empty((n, m), dtype=torch.float32, device=x.device)
     ws, wsz = _workspace(x.device, lib().b200_mul_mat_mmq_workspace_size(m, n, k))
-    check(lib().b200_mul_mat_mmq(plane.data_ptr(), x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
+    check(lib().b200_mul_mat_mmq(t, plane.data_ptr(), x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
                                  dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
     return dst
 

@@ -165,11 +165,19 @@ def mul_mat_plane(t, w, x, m, k, kc=256):
         q = np.rint((c * inv[:, :, None]).astype(f32)).astype(np.int32)
         return q, s
 
-    P, S = q8(Wf)
     Q, T = q8(Xf)
-    acc = np.zeros((n, m), dtype=f32)
-    for c in range(kp // kc):
-        D = (Q[:, c, :].astype(np.int64) @ P[:, c, :].astype(np.int64).T).astype(f32)        # [n, m], exact
-        st = (S[None, :, c] * T[:, None, c]).astype(f32)
-        acc = (D.astype(np.float64) * st.astype(np.float64) + acc.astype(np.float64)).astype(f32)   # one fma rounding
-    return acc
+
+    def gemm(P, S, acc):
+        for c in range(kp // kc):
+            D = (Q[:, c, :].astype(np.int64) @ P[:, c, :].astype(np.int64).T).astype(f32)        # [n, m], exact
+            st = (S[None, :, c] * T[:, None, c]).astype(f32)
+            acc = (D.astype(np.float64) * st.astype(np.float64) + acc.astype(np.float64)).astype(f32)   # one fma rounding
+        return acc
+
+    P, S = q8(Wf)
+    out = gemm(P, S, np.zeros((n, m), dtype=f32))
+    if t == Q8_0:   # second plane: the residual w - s * P, accumulated onto the first pass (dst = acc + dst)
+        W1 = (S[:, :, None] * P.astype(f32)).astype(f32).reshape(m, kp)
+        P2, S2 = q8((Wf - W1).astype(f32))
+        out = (gemm(P2, S2, np.zeros((n, m), dtype=f32)) + out).astype(f32)
+    return out

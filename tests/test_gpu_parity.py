@@ -168,7 +168,7 @@ def test_mmq_prepared_plane(qmm, name, t, m, k, n):
     x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
     wd = dev(w)
     plane = qmm.build_plane(t, wd, m, k)
-    got = qmm.mul_mat_mmq(plane, dev(x), m, k).cpu().numpy()
+    got = qmm.mul_mat_mmq(t, plane, dev(x), m, k).cpu().numpy()
     assert np.isfinite(got).all()
     assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got) < NMSE_TIGHT
     assert qref.nmse(qref.mul_mat(t, w, x, m, k, "cpu"), got) < NMSE_HARNESS
@@ -184,15 +184,28 @@ def test_mmq_k_not_multiple_of_chunk(qmm, name, t):
     check_mul_mat(qmm, t, w, x, m, k)
 
 
-def test_mmq_normal_weights_through_real_quantizer(qmm, golden):
-    # golden weights went through the reference's own quantizer from N(0,1) data: the realistic error case
-    for name, t in TYPES:
-        w, x = golden["w_" + name], golden["mm_x"]
-        m, k = w.shape[0], x.shape[1]
-        xx = np.tile(x, (12, 1))[:17]
-        got = qmm.mul_mat(t, dev(w), dev(xx), m, k).cpu().numpy()
-        cpu = qref.mul_mat(t, w, xx, m, k, "cpu")
-        assert qref.nmse(cpu, got) < NMSE_HARNESS, (name, qref.nmse(cpu, got))
+@pytest.mark.parametrize("name,t", [("q4_0", qref.Q4_0), ("q8_0", qref.Q8_0)])
+@pytest.mark.parametrize("dist", ["normal", "heavy_tail", "act_outliers"])
+def test_mmq_realistic_weights_through_quantizer(qmm, name, t, dist):
+    """weights that went through the reference quantizer (oracle restatement, pinned bit-exact) from Gaussian and from
+    heavy-tailed (Student-t, df = 4) data.  Q8_0 is the type whose per-32 scales a single per-256 plane would flatten: it
+    must hold the harness bound through its residual plane.
+    act_outliers (six activation channels scaled 30x) is the KNOWN GAP of the per-256 activation scale for the 32-block
+    types: ggml-cpu quantizes their activations per 32 (q8_0), so the tensor-core path is coarser there (K-quants use
+    per-256 q8_K on the CPU too).  The reference harness never generates such data (uniform(-1,1),
+    tests/test-backend-ops.cpp:39-61); the bound asserted for it is the documented 2e-3, not the harness bound."""
+    rng = np.random.default_rng(11)
+    m, k, n = 256, 2048, 24
+    wf = (rng.standard_t(4, (m, k)) if dist == "heavy_tail" else rng.normal(0, 1, (m, k))).astype(np.float32)
+    w = qref.quantize(t, wf)
+    x = rng.normal(0, 1, (n, k)).astype(np.float32)
+    if dist == "act_outliers":
+        x[:, rng.choice(k, 6, replace=False)] *= 30
+    got = qmm.mul_mat(t, dev(w), dev(x), m, k).cpu().numpy()
+    assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got) < NMSE_TIGHT
+    cpu = qref.mul_mat(t, w, x, m, k, "cpu")
+    bound = 2e-3 if dist == "act_outliers" else NMSE_HARNESS
+    assert qref.nmse(cpu, got) < bound, qref.nmse(cpu, got)
 
 
 # ------------------------------------------------------------------------------------------------ full-size properties

@@ -20,7 +20,7 @@ for name, m, k, n in [("q4_K", 128, 256, 16), ("q4_K", 128, 512, 128), ("q4_K", 
     w = qref.random_blocks(t, m, k, rng)
     x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
     plane = qmm.build_plane(t, torch.from_numpy(w).cuda(), m, k)
-    got = qmm.mul_mat_mmq(plane, torch.from_numpy(x).cuda(), m, k)
+    got = qmm.mul_mat_mmq(t, plane, torch.from_numpy(x).cuda(), m, k)
     torch.cuda.synchronize()
     got = got.cpu().numpy()
     want = qref.mul_mat_plane(t, w, x, m, k)
@@ -44,11 +44,11 @@ for name in ("q4_K", "q6_K"):
             for bn in ("128", "256"):
                 os.environ["B200_MMQ_BN"] = bn
                 for _ in range(3):
-                    qmm.mul_mat_mmq(plane, x, m, k, out=out)
+                    qmm.mul_mat_mmq(t, plane, x, m, k, out=out)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 for _ in range(20):
-                    qmm.mul_mat_mmq(plane, x, m, k, out=out)
+                    qmm.mul_mat_mmq(t, plane, x, m, k, out=out)
                 e1.record()
                 torch.cuda.synchronize()
                 us = e0.elapsed_time(e1) * 1e3 / 20

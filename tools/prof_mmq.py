@@ -23,14 +23,14 @@ w = torch.from_numpy(qref.random_blocks(t, m, k, rng)).cuda()
 plane = qmm.build_plane(t, w, m, k)
 x = torch.rand((n, k), device="cuda") * 2 - 1
 out = torch.empty((n, m), device="cuda")
-qmm.mul_mat_mmq(plane, x, m, k, out=out)
+qmm.mul_mat_mmq(t, plane, x, m, k, out=out)
 torch.cuda.synchronize()
 s = torch.cuda.Stream()
 g = torch.cuda.CUDAGraph()
 with torch.cuda.stream(s):
     with torch.cuda.graph(g, stream=s):
         for _ in range(reps):
-            qmm.mul_mat_mmq(plane, x, m, k, out=out)
+            qmm.mul_mat_mmq(t, plane, x, m, k, out=out)
 g.replay()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
