@@ -140,10 +140,12 @@ static int mmq_min_batch() {
     return e && *e ? atoi(e) : 9;
 }
 static size_t ws_align(size_t v) { return (v + 255) & ~(size_t) 255; }
+// batches above MMVQ_MAX_BATCH_SIZE go to the tensor cores; so do rows too long for one GEMV CTA (k > 32768)
+static bool use_mmq(int type, int64_t n, int64_t k) { return n >= mmq_min_batch() || gemv_max_cols(type, k) < 1; }
 
 size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     if (!weight_type(type) || k <= 0 || n <= 0 || m <= 0) return 0;
-    if (n >= mmq_min_batch()) return ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k)) + mmq_workspace_bytes(n, k);
+    if (use_mmq(type, n, k)) return ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k)) + mmq_workspace_bytes(n, k);
     if (use_fused_quant(n, k)) return 0;
     return (size_t) n * q8_soa_layout(k).bytes;
 }
@@ -192,7 +194,7 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
         B200_CUDA_TRY(cudaMemset2DAsync(dst, dst_row_stride * 4, 0, m * 4, n, stream));
         return B200_OK;
     }
-    if (n >= mmq_min_batch()) {  // tensor-core path with a transient plane carved from the workspace
+    if (use_mmq(type, n, k)) {  // tensor-core path with a transient plane carved from the workspace
         const size_t pb = ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k));
         if (!workspace || workspace_bytes < pb + mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
         if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
@@ -201,7 +203,6 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
         return launch_mmq(type, workspace, x, x_row_stride, dst, dst_row_stride, m, n, k, (uint8_t *) workspace + pb, stream);
     }
     const int maxc = gemv_max_cols(type, k);
-    if (maxc < 1) return B200_ERR_UNSUPPORTED;
 
     gemv_args g = {};
     g.type = type, g.W = (const uint8_t *) W, g.w_row_stride = w_row_stride;

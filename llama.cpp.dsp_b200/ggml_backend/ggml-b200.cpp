@@ -22,12 +22,15 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <climits>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
-#include <unordered_map>
+#include <tuple>
 #include <vector>
 
 #define B200_MAX_DEVICES 16
@@ -84,16 +87,25 @@ static int b200_device_count() {
 // ---------------------------------------------------------------------------------------------------- device buffer
 // replaces ggml_backend_cuda_buffer_* (ggml-cuda.cu:516-633).  The buffer also owns the int8 "prefill planes" of the
 // quantized weights that live in it (built lazily by the first batched matmul, dropped when the tensor is rewritten).
+struct b200_plane_key {
+    const void * w;          // first byte of the (sub-)matrix: tensor->data + i02*nb02 + i03*nb03
+    int64_t      row_stride; // nb01
+    int64_t      m, k;
+    int          type;
+    bool operator<(const b200_plane_key & o) const {
+        return std::tie(w, row_stride, m, k, type) < std::tie(o.w, o.row_stride, o.m, o.k, o.type);
+    }
+};
 struct b200_plane {
-    void * ptr;
-    size_t bytes;
+    void * ptr  = nullptr;   // NULL until the matrix has been seen twice (or the buffer holds weights)
+    int    uses = 0;
 };
 
 struct b200_buffer_context {
     int    device;
     void * base;
-    std::mutex                               mtx;
-    std::unordered_map<const void *, b200_plane> planes;   // key: tensor->data
+    std::mutex                             mtx;
+    std::map<b200_plane_key, b200_plane>   planes;
 
     b200_buffer_context(int device, void * base) : device(device), base(base) {}
     ~b200_buffer_context() {
@@ -101,23 +113,44 @@ struct b200_buffer_context {
         for (auto & kv : planes) cudaFree(kv.second.ptr);
         CUDA_CHECK(cudaFree(base));
     }
-    void drop_plane(const void * data) {
-        std::lock_guard<std::mutex> lock(mtx);
-        auto it = planes.find(data);
-        if (it != planes.end()) {
-            set_device(device);
-            CUDA_CHECK(cudaDeviceSynchronize());   // a matmul may still be reading it
-            cudaFree(it->second.ptr);
-            planes.erase(it);
-        }
-    }
-    void drop_all_planes() {
+    // forget every plane whose matrix starts inside [data, data + size): called before those bytes are rewritten
+    void drop_planes(const void * data, size_t size) {
         std::lock_guard<std::mutex> lock(mtx);
         if (planes.empty()) return;
+        b200_plane_key lo = {data, INT64_MIN, INT64_MIN, INT64_MIN, INT32_MIN};
+        auto it  = planes.lower_bound(lo);
+        bool synced = false;
+        while (it != planes.end() && (const char *) it->first.w < (const char *) data + size) {
+            if (it->second.ptr) {
+                if (!synced) {
+                    set_device(device);
+                    CUDA_CHECK(cudaDeviceSynchronize());   // a matmul may still be reading it
+                    synced = true;
+                }
+                cudaFree(it->second.ptr);
+            }
+            it = planes.erase(it);
+        }
+    }
+    // The int8 plane of a weight matrix for the tensor-core path, or NULL when this call should use a transient one:
+    // matrices in a weights buffer get a plane at first use, anything else at its second use without a write between.
+    const void * get_plane(const b200_plane_key & key, bool weights, cudaStream_t stream) {
+        std::lock_guard<std::mutex> lock(mtx);
+        b200_plane & e = planes[key];
+        e.uses++;
+        if (e.ptr) return e.ptr;
+        if (!weights && e.uses < 2) return nullptr;
+        const size_t bytes = b200_mmq_plane_size(key.type, key.m, key.k);
+        if (bytes == 0) return nullptr;
         set_device(device);
-        CUDA_CHECK(cudaDeviceSynchronize());
-        for (auto & kv : planes) cudaFree(kv.second.ptr);
-        planes.clear();
+        if (cudaMalloc(&e.ptr, bytes) != cudaSuccess) {   // no room for the cache: keep working with transient planes
+            (void) cudaGetLastError();
+            e.ptr = nullptr;
+            return nullptr;
+        }
+        B200_CHECK(b200_mmq_build_plane(key.type, key.w, key.row_stride, e.ptr, bytes, key.m, key.k, stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));        // other backend streams may use it next
+        return e.ptr;
     }
 };
 
@@ -135,7 +168,7 @@ static enum ggml_status b200_buffer_init_tensor(ggml_backend_buffer_t buffer, gg
 static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, uint8_t value, size_t offset,
                                       size_t size) {
     auto * ctx = (b200_buffer_context *) buffer->context;
-    ctx->drop_plane(tensor->data);
+    ctx->drop_planes(tensor->data, ggml_nbytes(tensor));
     set_device(ctx->device);
     CUDA_CHECK(cudaMemsetAsync((char *) tensor->data + offset, value, size, cudaStreamPerThread));
     CUDA_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
@@ -144,7 +177,7 @@ static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor 
 static void b200_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset,
                                    size_t size) {
     auto * ctx = (b200_buffer_context *) buffer->context;
-    ctx->drop_plane(tensor->data);
+    ctx->drop_planes(tensor->data, ggml_nbytes(tensor));
     set_device(ctx->device);
     CUDA_CHECK(cudaMemcpyAsync((char *) tensor->data + offset, data, size, cudaMemcpyHostToDevice, cudaStreamPerThread));
     CUDA_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
@@ -164,7 +197,7 @@ static bool b200_buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tens
     if (!b200_buffer_is_ours(src->buffer)) return false;   // host sources go through set_tensor
     auto * sctx = (b200_buffer_context *) src->buffer->context;
     auto * dctx = (b200_buffer_context *) buffer->context;
-    dctx->drop_plane(dst->data);
+    dctx->drop_planes(dst->data, ggml_nbytes(dst));
     if (sctx->device == dctx->device) {
         set_device(dctx->device);
         CUDA_CHECK(cudaMemcpyAsync(dst->data, src->data, ggml_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
@@ -177,7 +210,7 @@ static bool b200_buffer_cpy_tensor(ggml_backend_buffer_t buffer, const ggml_tens
 
 static void b200_buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     auto * ctx = (b200_buffer_context *) buffer->context;
-    ctx->drop_all_planes();
+    ctx->drop_planes(ctx->base, buffer->size);
     set_device(ctx->device);
     CUDA_CHECK(cudaDeviceSynchronize());
     CUDA_CHECK(cudaMemset(ctx->base, value, buffer->size));
@@ -261,3 +294,421 @@ static ggml_backend_buffer_type_t b200_buffer_type(int device) {
     return &types[device];
 }
 
+// ---------------------------------------------------------------------------------------------------- backend (stream)
+// replaces ggml_backend_cuda_* (ggml-cuda.cu:2374-2831).  One CUDA stream and one grow-only scratch allocation per
+// backend instance; everything graph_compute launches is ordered on that stream, so the scratch is reused node to node.
+struct b200_backend_context {
+    int          device;
+    std::string  name;
+    cudaStream_t stream    = nullptr;
+    void *       workspace = nullptr;
+    size_t       workspace_bytes = 0;
+
+    explicit b200_backend_context(int device) : device(device), name("B200_" + std::to_string(device)) {
+        set_device(device);
+        CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    }
+    ~b200_backend_context() {
+        set_device(device);
+        cudaStreamSynchronize(stream);
+        if (workspace) cudaFree(workspace);
+        cudaStreamDestroy(stream);
+    }
+    void * scratch(size_t bytes) {
+        if (bytes <= workspace_bytes) return workspace;
+        if (workspace) {
+            CUDA_CHECK(cudaStreamSynchronize(stream));   // kernels in flight still read the old one
+            CUDA_CHECK(cudaFree(workspace));
+        }
+        workspace_bytes = (bytes + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+        CUDA_CHECK(cudaMalloc(&workspace, workspace_bytes));
+        return workspace;
+    }
+};
+
+static const char * b200_backend_get_name(ggml_backend_t backend) { return ((b200_backend_context *) backend->context)->name.c_str(); }
+
+static void b200_backend_free(ggml_backend_t backend) {
+    delete (b200_backend_context *) backend->context;
+    delete backend;
+}
+
+static void b200_backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * tensor, const void * data, size_t offset,
+                                          size_t size) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    ggml_backend_buffer_t buf = tensor->view_src ? tensor->view_src->buffer : tensor->buffer;
+    GGML_ASSERT(b200_buffer_is_ours(buf) && "unsupported buffer type");
+    ((b200_buffer_context *) buf->context)->drop_planes(tensor->data, ggml_nbytes(tensor));
+    set_device(ctx->device);
+    CUDA_CHECK(cudaMemcpyAsync((char *) tensor->data + offset, data, size, cudaMemcpyHostToDevice, ctx->stream));
+}
+
+static void b200_backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor, void * data, size_t offset,
+                                          size_t size) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    ggml_backend_buffer_t buf = tensor->view_src ? tensor->view_src->buffer : tensor->buffer;
+    GGML_ASSERT(b200_buffer_is_ours(buf) && "unsupported buffer type");
+    set_device(ctx->device);
+    CUDA_CHECK(cudaMemcpyAsync(data, (const char *) tensor->data + offset, size, cudaMemcpyDeviceToHost, ctx->stream));
+}
+
+static void b200_backend_synchronize(ggml_backend_t backend) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    set_device(ctx->device);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+}
+
+// GGML_OP_MUL_MAT: dst[i13][i12][j][i] = sum_c src0[i13/r3][i12/r2][i][c] * src1[i13][i12][j][c]
+// (ggml_compute_forward_mul_mat's broadcast rule, ggml/src/ggml-cpu/ggml-cpu.c:1266-1300; the CUDA backend's dispatcher
+// for the same node is ggml_cuda_mul_mat, ggml-cuda.cu:1877-1938)
+static void b200_compute_mul_mat(b200_backend_context * ctx, ggml_tensor * dst) {
+    const ggml_tensor * src0 = dst->src[0];
+    const ggml_tensor * src1 = dst->src[1];
+    GGML_TENSOR_BINARY_OP_LOCALS
+
+    const int     type = (int) src0->type;
+    const int64_t m = ne01, k = ne00;
+    const int64_t r2 = ne12 / ne02, r3 = ne13 / ne03;
+    if (ggml_nelements(dst) == 0) return;
+
+    // a weight broadcast over dim 2 of contiguous activations is one matmul with r2 * ne11 columns
+    const bool    merge = r2 > 1 && nb12 == (size_t) ne11 * nb11 && nb2 == (size_t) ne1 * nb1;
+    const int64_t n     = merge ? ne11 * r2 : ne11;
+    const int64_t n12   = merge ? ne02 : ne12;
+
+    ggml_backend_buffer_t wbuf = src0->view_src ? src0->view_src->buffer : src0->buffer;
+    const bool mmq     = n >= b200_mmq_min_batch();
+    const bool weights = wbuf->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS;
+
+    const size_t ws_bytes = std::max(b200_mul_mat_workspace_size(type, m, n, k), b200_mul_mat_mmq_workspace_size(m, n, k));
+    void *       ws       = ws_bytes ? ctx->scratch(ws_bytes) : nullptr;
+
+    for (int64_t i13 = 0; i13 < ne13; i13++) {
+        for (int64_t i12 = 0; i12 < n12; i12++) {
+            const int64_t i03 = i13 / r3;
+            const int64_t i02 = merge ? i12 : i12 / r2;
+            const int64_t j12 = merge ? i12 * r2 : i12;   // first dim-2 index of src1 / dst covered by this matmul
+            const char *  W   = (const char *) src0->data + i02 * nb02 + i03 * nb03;
+            const float * x   = (const float *) ((const char *) src1->data + j12 * nb12 + i13 * nb13);
+            float *       y   = (float *) ((char *) dst->data + j12 * nb2 + i13 * nb3);
+
+            const void * plane = nullptr;
+            if (mmq) {
+                b200_plane_key key = {W, (int64_t) nb01, m, k, type};
+                plane = ((b200_buffer_context *) wbuf->context)->get_plane(key, weights, ctx->stream);
+            }
+            if (plane) {
+                B200_CHECK(b200_mul_mat_mmq(type, plane, x, nb11 / 4, y, nb1 / 4, m, n, k, ws, ctx->workspace_bytes, ctx->stream));
+            } else {
+                B200_CHECK(b200_mul_mat(type, W, nb01, x, nb11 / 4, y, nb1 / 4, m, n, k, ws, ctx->workspace_bytes, ctx->stream));
+            }
+        }
+    }
+}
+
+// GGML_OP_MUL_MAT_ID: dst[t][s] = as[ids[t][s]] * b[t][s % ne11]  (ggml.c:2771-2799).  One call, ids stay on the device.
+static void b200_compute_mul_mat_id(b200_backend_context * ctx, ggml_tensor * dst) {
+    const ggml_tensor * src0 = dst->src[0];
+    const ggml_tensor * src1 = dst->src[1];
+    const ggml_tensor * ids  = dst->src[2];
+    GGML_TENSOR_BINARY_OP_LOCALS
+
+    const int     type     = (int) src0->type;
+    const int64_t m = ne01, k = ne00, n_expert = ne02;
+    const int64_t n_used   = ids->ne[0];
+    const int64_t n_tokens = ids->ne[1];
+    if (ggml_nelements(dst) == 0) return;
+
+    const size_t ws_bytes = b200_mul_mat_id_workspace_size(type, m, k, n_expert, n_used, n_tokens);
+    void *       ws       = ws_bytes ? ctx->scratch(ws_bytes) : nullptr;
+    B200_CHECK(b200_mul_mat_id(type, src0->data, nb02, (const float *) src1->data, nb12 / 4, nb11 / 4, ne11,
+                               (const int32_t *) ids->data, ids->nb[1] / 4, (float *) dst->data, nb2 / 4, nb1 / 4, m, k,
+                               n_expert, n_used, n_tokens, ws, ctx->workspace_bytes, ctx->stream));
+}
+
+static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    set_device(ctx->device);
+    for (int i = 0; i < cgraph->n_nodes; i++) {
+        ggml_tensor * node = cgraph->nodes[i];
+        if (ggml_is_empty(node)) continue;
+        switch (node->op) {
+            case GGML_OP_NONE:
+            case GGML_OP_RESHAPE:
+            case GGML_OP_VIEW:
+            case GGML_OP_PERMUTE:
+            case GGML_OP_TRANSPOSE:
+                break;
+            case GGML_OP_MUL_MAT:
+                b200_compute_mul_mat(ctx, node);
+                break;
+            case GGML_OP_MUL_MAT_ID:
+                b200_compute_mul_mat_id(ctx, node);
+                break;
+            default:
+                // supports_op said no; the scheduler never sends such a node here (same abort as ggml-cuda.cu:2652-2655)
+                GGML_LOG_ERROR("%s: op not supported %s (%s)\n", __func__, node->name, ggml_op_name(node->op));
+                GGML_ABORT("B200 backend: unsupported op");
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+struct b200_event_context {
+    int         device;
+    cudaEvent_t event;
+};
+
+static void b200_backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    set_device(ctx->device);
+    CUDA_CHECK(cudaEventRecord(((b200_event_context *) event->context)->event, ctx->stream));
+}
+
+static void b200_backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    auto * ctx = (b200_backend_context *) backend->context;
+    set_device(ctx->device);
+    CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ((b200_event_context *) event->context)->event, 0));
+}
+
+static const ggml_backend_i b200_backend_interface = {
+    /* .get_name           = */ b200_backend_get_name,
+    /* .free               = */ b200_backend_free,
+    /* .set_tensor_async   = */ b200_backend_set_tensor_async,
+    /* .get_tensor_async   = */ b200_backend_get_tensor_async,
+    /* .cpy_tensor_async   = */ NULL,
+    /* .synchronize        = */ b200_backend_synchronize,
+    /* .graph_plan_create  = */ NULL,
+    /* .graph_plan_free    = */ NULL,
+    /* .graph_plan_update  = */ NULL,
+    /* .graph_plan_compute = */ NULL,
+    /* .graph_compute      = */ b200_backend_graph_compute,
+    /* .event_record       = */ b200_backend_event_record,
+    /* .event_wait         = */ b200_backend_event_wait,
+};
+
+static ggml_guid_t b200_backend_guid() {
+    static ggml_guid guid = {0xb2, 0x00, 0x51, 0x0a, 0x74, 0xc6, 0x05, 0x7d, 0x3e, 0x6d, 0x71, 0x38, 0x6d, 0x6d, 0x51, 0x01};
+    return &guid;
+}
+
+// ---------------------------------------------------------------------------------------------------- device
+// replaces ggml_backend_cuda_device_* (ggml-cuda.cu:2885-3339)
+static const char * b200_device_get_name(ggml_backend_dev_t dev) { return ((b200_device_context *) dev->context)->name.c_str(); }
+static const char * b200_device_get_description(ggml_backend_dev_t dev) { return ((b200_device_context *) dev->context)->description.c_str(); }
+
+static void b200_device_get_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    set_device(((b200_device_context *) dev->context)->device);
+    CUDA_CHECK(cudaMemGetInfo(free, total));
+}
+
+static enum ggml_backend_dev_type b200_device_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+
+static void b200_device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    props->name        = b200_device_get_name(dev);
+    props->description = b200_device_get_description(dev);
+    props->type        = b200_device_get_type(dev);
+    b200_device_get_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = {
+        /* .async                 = */ true,
+        /* .host_buffer           = */ false,
+        /* .buffer_from_host_ptr  = */ false,
+        /* .events                = */ true,
+    };
+}
+
+static ggml_backend_t b200_device_init_backend(ggml_backend_dev_t dev, const char * params) {
+    (void) params;
+    auto * dctx = (b200_device_context *) dev->context;
+    return new ggml_backend{
+        /* .guid      = */ b200_backend_guid(),
+        /* .interface = */ b200_backend_interface,
+        /* .device    = */ dev,
+        /* .context   = */ new b200_backend_context(dctx->device),
+    };
+}
+
+static ggml_backend_buffer_type_t b200_device_get_buffer_type(ggml_backend_dev_t dev) {
+    return b200_buffer_type(((b200_device_context *) dev->context)->device);
+}
+
+// Which nodes this backend computes.  Everything else is answered "no" and stays with the scheduler's other backends
+// (ggml_backend_sched assigns by supports_op, ggml/src/ggml-backend.cpp:701-742) -- there is no CPU code in this plug-in.
+static bool b200_device_supports_op(ggml_backend_dev_t dev, const ggml_tensor * op) {
+    // every source that already has storage must live in one of this device's buffers (ggml-cuda.cu:2964-2976)
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        const ggml_tensor * s = op->src[i];
+        if (s && s->buffer && (!b200_buffer_is_ours(s->buffer) || s->buffer->buft->device != dev)) return false;
+    }
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_VIEW:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT:
+        case GGML_OP_MUL_MAT_ID: {
+            const ggml_tensor * a = op->src[0];
+            const ggml_tensor * b = op->src[1];
+            if (!a || !b || !b200_type_on_path(a->type)) return false;
+            if (b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+            // rows of k contiguous elements on both sides; row / matrix strides are free (permuted and viewed operands)
+            if (a->nb[0] != ggml_type_size(a->type) || b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
+            if (b->nb[1] % 16 != 0 || b->nb[2] % 16 != 0 || b->nb[3] % 16 != 0) return false;   // float4 loads of x
+            if (op->nb[1] % sizeof(float) != 0 || op->nb[1] < (size_t) op->ne[0] * sizeof(float)) return false;
+            if (a->ne[0] > INT32_MAX || a->ne[1] > INT32_MAX) return false;
+            if (op->op == GGML_OP_MUL_MAT_ID) {
+                const ggml_tensor * ids = op->src[2];
+                if (!ids || ids->type != GGML_TYPE_I32 || ids->nb[0] != sizeof(int32_t)) return false;
+                if (a->ne[0] > 32768) return false;   // one GEMV CTA spans a row; longer rows only exist for MUL_MAT
+                if (a->ne[3] != 1 || b->ne[3] != 1) return false;
+            }
+            return true;
+        }
+        default:
+            return false;
+    }
+}
+
+static bool b200_device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return buft->iface.get_name == b200_buft_get_name && buft->device == dev;
+}
+
+static int64_t b200_op_batch_size(const ggml_tensor * op) {
+    switch (op->op) {
+        case GGML_OP_MUL_MAT: return op->ne[1];
+        case GGML_OP_MUL_MAT_ID: return op->ne[2];
+        default: return 0;
+    }
+}
+
+// same threshold as ggml_backend_cuda_device_offload_op (ggml-cuda.cu:3285-3291): worth copying CPU-resident weights over
+// for batches of 32 tokens and more
+static bool b200_device_offload_op(ggml_backend_dev_t, const ggml_tensor * op) { return b200_op_batch_size(op) >= 32; }
+
+static ggml_backend_event_t b200_device_event_new(ggml_backend_dev_t dev) {
+    auto * dctx = (b200_device_context *) dev->context;
+    set_device(dctx->device);
+    auto * e = new b200_event_context{dctx->device, nullptr};
+    CUDA_CHECK(cudaEventCreateWithFlags(&e->event, cudaEventDisableTiming));
+    return new ggml_backend_event{
+        /* .device  = */ dev,
+        /* .context = */ e,
+    };
+}
+
+static void b200_device_event_free(ggml_backend_dev_t, ggml_backend_event_t event) {
+    auto * e = (b200_event_context *) event->context;
+    set_device(e->device);
+    CUDA_CHECK(cudaEventDestroy(e->event));
+    delete e;
+    delete event;
+}
+
+static void b200_device_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) {
+    auto * e = (b200_event_context *) event->context;
+    set_device(e->device);
+    CUDA_CHECK(cudaEventSynchronize(e->event));
+}
+
+static const ggml_backend_device_i b200_device_interface = {
+    /* .get_name             = */ b200_device_get_name,
+    /* .get_description      = */ b200_device_get_description,
+    /* .get_memory           = */ b200_device_get_memory,
+    /* .get_type             = */ b200_device_get_type,
+    /* .get_props            = */ b200_device_get_props,
+    /* .init_backend         = */ b200_device_init_backend,
+    /* .get_buffer_type      = */ b200_device_get_buffer_type,
+    /* .get_host_buffer_type = */ NULL,
+    /* .buffer_from_host_ptr = */ NULL,
+    /* .supports_op          = */ b200_device_supports_op,
+    /* .supports_buft        = */ b200_device_supports_buft,
+    /* .offload_op           = */ b200_device_offload_op,
+    /* .event_new            = */ b200_device_event_new,
+    /* .event_free           = */ b200_device_event_free,
+    /* .event_synchronize    = */ b200_device_event_synchronize,
+};
+
+// ---------------------------------------------------------------------------------------------------- registry
+// replaces ggml_backend_cuda_reg_* (ggml-cuda.cu:3341-3506)
+struct b200_reg_context {
+    std::vector<ggml_backend_dev_t> devices;
+};
+
+static const char * b200_reg_get_name(ggml_backend_reg_t) { return "B200"; }
+static size_t       b200_reg_get_device_count(ggml_backend_reg_t reg) { return ((b200_reg_context *) reg->context)->devices.size(); }
+
+static ggml_backend_dev_t b200_reg_get_device(ggml_backend_reg_t reg, size_t index) {
+    auto * ctx = (b200_reg_context *) reg->context;
+    GGML_ASSERT(index < ctx->devices.size());
+    return ctx->devices[index];
+}
+
+static ggml_backend_feature * b200_get_features(ggml_backend_reg_t) {
+    static ggml_backend_feature features[] = {
+        {"ARCH", "sm_100a"},
+        {"GEMV", "TMA bulk + dp4a"},
+        {"MMQ", "tcgen05 i8 + TMEM"},
+        {nullptr, nullptr},
+    };
+    return features;
+}
+
+static void * b200_reg_get_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) b200_get_features;
+    // "ggml_backend_split_buffer_type" is not offered: rows are split one PROCESS per GPU (b200_row_split +
+    // NCCL all-gather / b200_mul_mat_rowsplit_fused), not inside one backend instance -- see DESIGN.md (e)
+    return nullptr;
+}
+
+static const ggml_backend_reg_i b200_reg_interface = {
+    /* .get_name         = */ b200_reg_get_name,
+    /* .get_device_count = */ b200_reg_get_device_count,
+    /* .get_device       = */ b200_reg_get_device,
+    /* .get_proc_address = */ b200_reg_get_proc_address,
+};
+
+static ggml_backend_reg_t b200_reg() {
+    static ggml_backend_reg reg;
+    static std::once_flag   once;
+    std::call_once(once, [] {
+        auto * ctx = new b200_reg_context;
+        reg = ggml_backend_reg{
+            /* .api_version = */ GGML_BACKEND_API_VERSION,
+            /* .iface       = */ b200_reg_interface,
+            /* .context     = */ ctx,
+        };
+        for (int i = 0; i < b200_device_count(); i++) {
+            cudaDeviceProp prop;
+            CUDA_CHECK(cudaGetDeviceProperties(&prop, i));
+            auto * dctx = new b200_device_context{i, "B200_" + std::to_string(i), prop.name};
+            ctx->devices.push_back(new ggml_backend_device{
+                /* .iface   = */ b200_device_interface,
+                /* .reg     = */ &reg,
+                /* .context = */ dctx,
+            });
+        }
+    });
+    return &reg;
+}
+
+// public entry points, named after the reference's per-backend headers (ggml/include/ggml-cuda.h:26-47)
+extern "C" {
+GGML_BACKEND_API ggml_backend_reg_t ggml_backend_b200_reg(void) { return b200_reg(); }
+GGML_BACKEND_API int                ggml_backend_b200_get_device_count(void) { return b200_device_count(); }
+GGML_BACKEND_API bool ggml_backend_is_b200(ggml_backend_t backend) { return backend && ggml_guid_matches(backend->guid, b200_backend_guid()); }
+GGML_BACKEND_API ggml_backend_t ggml_backend_b200_init(int device) {
+    if (device < 0 || device >= b200_device_count()) {
+        GGML_LOG_ERROR("%s: invalid device %d\n", __func__, device);
+        return nullptr;
+    }
+    return b200_device_init_backend(b200_reg_get_device(b200_reg(), device), nullptr);
+}
+GGML_BACKEND_API ggml_backend_buffer_type_t ggml_backend_b200_buffer_type(int device) { return b200_buffer_type(device); }
+}
+
+static int b200_score() { return b200_device_count() > 0 ? 100 : 0; }
+
+GGML_BACKEND_DL_IMPL(ggml_backend_b200_reg)
+GGML_BACKEND_DL_SCORE_IMPL(b200_score)
