@@ -226,6 +226,9 @@ def main():
     ap.add_argument("--workload", default=None, choices=list(MODELS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pp", action="store_true", help="skip the pp512 leg")
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
+                    help="N>1: how the row slices come together (fused = peer stores from the GEMV epilogue)")
+    ap.add_argument("--no-single", action="store_true", help="N>1: skip the same-workload single-GPU leg on rank 0")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
@@ -279,6 +282,7 @@ def main():
             if world > 1:
                 dist.all_gather_into_tensor(out_full[m], out_local[m])
 
+    weight_bytes_local = sum(w.numel() for w in weights if w is not None)
     step_bytes = sum(gemv_bytes(t, hi - lo, k, n) for (_, t, _, k), (lo, hi, _) in zip(mms, slices) if hi > lo)
     total_bytes_all_ranks = sum(gemv_bytes(t, m, k, n) for _, t, m, k in mms)
 
@@ -292,7 +296,8 @@ def main():
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
-    use_graph = not args.no_graph and world == 1
+    # one CUDA graph per token (NCCL collectives are capturable too); B200_BENCH_GRAPH_MULTI=0 keeps N>1 eager
+    use_graph = not args.no_graph and (world == 1 or os.environ.get("B200_BENCH_GRAPH_MULTI", "1") == "1")
     if use_graph:
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.stream(stream):
@@ -338,6 +343,103 @@ def main():
     clocks = clk.summary()
     ms_eager = timed(token_step, max(4, args.steps // 8), 3) if use_graph else ms_step
 
+    # ---- N > 1: the fused path -- each GEMV stores its rows into every rank's dst over NVLink, a stream wait-value
+    #      replaces the collective (b200_mul_mat_rowsplit_fused + b200_rowsplit_wait).  When it runs, it is the headline
+    #      and the NCCL all-gather figure above is kept beside it as the baseline.
+    collective, nccl_leg = "nccl_all_gather", None
+    if world > 1 and args.collective == "fused":
+        from llama_cpp_dsp_b200.rowsplit import PeerBuffers, RowSplit, mul_mat_row_split_fused, row_split_wait
+        per_m = sorted({m for _, _, m, _ in mms})
+        peers = {m: PeerBuffers(n, m, 1, world, rank, dev) for m in per_m}
+        splits = {m: RowSplit(m, world, rank) for m in per_m}
+        fws = torch.empty(max(qmm.lib().b200_mul_mat_rowsplit_workspace_size(t, n, k) for _, t, _, k in mms) + 256,
+                          dtype=torch.uint8, device=dev)
+        # dependency groups of the decode graph: {q,k,v} -> {attn_output} -> {gate,up} -> {down} -> next layer ... ->
+        # output.  Matmuls of one group read the same x and are independent; the first matmul of a group needs the
+        # previous group's results whole on this rank.  One sync block per group.
+        def group_of(name):
+            base = name.split(".")[0]
+            return {"attn_q": "qkv", "attn_k": "qkv", "attn_v": "qkv", "ffn_gate": "gu", "ffn_up": "gu"}.get(base, base)
+        groups = []
+        for (name, t, m, k), w in zip(mms, weights):
+            key = (group_of(name), name.split(".")[-1])
+            if not groups or groups[-1][0] != key:
+                groups.append((key, []))
+            groups[-1][1].append((t, m, k, w))
+        gsync = PeerBuffers(1, 1, len(groups), world, rank, dev)
+        dist.barrier()
+
+        def token_step_fused():
+            prev, prev_calls = None, 0
+            for gi, (_, members) in enumerate(groups):
+                ps = gsync.ptr_sync[gi]
+                for j, (t, m, k, w) in enumerate(members):
+                    mul_mat_row_split_fused(t, w, xs[k], splits[m], k, peers[m].ptr_dst, ps, m, fws,
+                                            wait_sync=prev if j == 0 else None, wait_calls=prev_calls)
+                prev, prev_calls = ps, len(members)
+            row_split_wait(prev, rank, world, calls=prev_calls)
+
+        token_step_fused()
+        torch.cuda.synchronize()
+        dist.barrier()
+        # cross-check against the all-gather path before timing anything
+        token_step()
+        torch.cuda.synchronize()
+        problems = []
+        for m in per_m:
+            ref_full = torch.cat([out_full[m][r, :, :hi - lo] for r, (lo, hi) in enumerate(splits[m].ranges)], dim=1)
+            if not torch.equal(ref_full, peers[m].dst):
+                bad = (ref_full != peers[m].dst).nonzero()[:, 1]
+                i0 = int(bad.min())
+                problems.append("m=%d: %d elements differ, rows %d..%d (own rows %d..%d); got %s want %s" % (
+                    m, bad.numel(), i0, int(bad.max()), splits[m].lo, splits[m].hi,
+                    peers[m].dst[0, i0:i0 + 3].tolist(), ref_full[0, i0:i0 + 3].tolist()))
+        everyone = [None] * world
+        dist.all_gather_object(everyone, problems)
+        anybad = any(everyone)
+        if anybad and os.environ.get("B200_BENCH_DIAG"):
+            for m in per_m:
+                sp = splits[m]
+                plo, phi = sp.ranges[1 - rank] if world == 2 else sp.ranges[0]
+                hits, own = [], []
+                for (name, t, mm_, k), w in zip(mms, weights):
+                    if mm_ != m:
+                        continue
+                    qmm.mul_mat(t, w, xs[k], sp.rows, k, out=out_local[m][:, :sp.rows])
+                    dist.all_gather_into_tensor(out_full[m], out_local[m])
+                    full = torch.cat([out_full[m][r, :, :hi - lo] for r, (lo, hi) in enumerate(sp.ranges)], dim=1)
+                    if torch.equal(full[:, plo:phi], peers[m].dst[:, plo:phi]):
+                        hits.append(name)
+                    if torch.equal(full[:, sp.lo:sp.hi], peers[m].dst[:, sp.lo:sp.hi]):
+                        own.append(name)
+                print("DIAG rank %d m=%d peer rows match: %s ; own rows match: %s" % (rank, m, hits[-3:], own[-3:]),
+                      file=sys.stderr, flush=True)
+        if anybad:
+            print("bench.py: rank %d: fused row-split result differs from the all-gather result: %s"
+                  % (rank, "; ".join(problems) or "(this rank is fine)"), file=sys.stderr, flush=True)
+            dist.barrier()
+            os._exit(3)
+        run_f = token_step_fused
+        fused_graph = False
+        if use_graph:
+            gf = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(stream):
+                token_step_fused()
+                stream.synchronize()
+                with torch.cuda.graph(gf, stream=stream):
+                    token_step_fused()
+            run_f, fused_graph = gf.replay, True
+        dist.barrier()
+        with ClockSampler(local_rank) as clk2:
+            ms_fused = timed(run_f, args.steps, args.warmup)
+        fused_info = {"sync_groups_per_step": len(groups), "stream_waits_per_step": 1,
+                      "in_kernel_waits_per_step": len(groups) - 1}
+        nccl_leg = {"value": 1e3 / ms_step, "unit": "tok/s", "ms_per_step": ms_step,
+                    "launch": "cuda_graph_replay" if use_graph else "eager",
+                    "note": "same slices, dist.all_gather_into_tensor per matmul (the non-fused baseline)"}
+        ms_step, clocks, collective = ms_fused, clk2.summary(), "fused_peer_store"
+        use_graph = fused_graph
+
     # ---- e2e: host buffers, per-matmul H2D -> kernel -> D2H through b200_mul_mat_host (rank-local slice)
     hx = {k: xs[k].cpu().pin_memory() for k in ks}
     hout = {m: torch.zeros((n, maxrows[m])).pin_memory() for m in maxrows}
@@ -362,14 +464,22 @@ def main():
         def token_step_host_split():
             for k in ks:
                 xs[k].copy_(hx[k], non_blocking=True)
-            token_step()
-            for m in maxrows:
-                hout[m].copy_(out_full[m][0], non_blocking=True)
+            if collective == "fused_peer_store":
+                token_step_fused()
+                for m in maxrows:
+                    hfull[m].copy_(peers[m].dst, non_blocking=True)
+            else:
+                token_step()
+                for m in maxrows:
+                    hout[m].copy_(out_full[m][0], non_blocking=True)
             torch.cuda.current_stream().synchronize()
+        hfull = {m: torch.zeros((n, m)).pin_memory() for m in maxrows}
         ms_e2e = timed(token_step_host_split, max(8, args.steps // 4), 3)
+        fusedp = collective == "fused_peer_store"
         e2e = {"value": 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": sum(n * k * 4 for k in ks),
-               "d2h_bytes_per_step": sum(n * maxrows[m] * 4 for m in maxrows), "ms_per_step": ms_e2e,
-               "api": "pinned host activations -> H2D once per token -> row-split matmuls + all_gather -> D2H"}
+               "d2h_bytes_per_step": sum(n * (m if fusedp else maxrows[m]) * 4 for m in maxrows), "ms_per_step": ms_e2e,
+               "api": "pinned host activations -> H2D once per token -> row-split matmuls (%s) -> D2H of the last "
+                      "result per distinct m" % collective}
 
     # ---- pp512 leg (prefill): the same matmuls at n = 512 (output head at n = 1, as llama does for the last token)
     pp = None
@@ -435,6 +545,45 @@ def main():
               "transient_planes": {"value": npp * 1e3 / ms_pp_transient, "unit": "tok/s", "ms_per_step": ms_pp_transient}}
         del planes
 
+    # ---- N > 1: the SAME workload on ONE GPU (rank 0 alone, the other ranks wait), so that the line carries the
+    #      row-split speed-up measured in the same run on the same box (the driver's own N=1 run uses the 8B workload)
+    single = None
+    if world > 1 and not args.no_single:
+        if rank == 0:
+            del weights
+            torch.cuda.empty_cache()
+            full = [gen_weights(torch, t, m, k, gen, dev) for _, t, m, k in mms]
+            outs = {m: torch.zeros((n, m), device=dev) for _, _, m, _ in mms}
+
+            def token_step_1gpu():
+                for (name, t, m, k), w in zip(mms, full):
+                    qmm.mul_mat(t, w, xs[k], m, k, out=outs[m])
+            with torch.cuda.stream(stream):
+                token_step_1gpu()
+                stream.synchronize()
+                g1 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g1, stream=stream):
+                    token_step_1gpu()
+                for _ in range(3):
+                    g1.replay()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                k1 = max(8, args.steps // 4)
+                e0.record(stream)
+                for _ in range(k1):
+                    g1.replay()
+                e1.record(stream)
+                torch.cuda.synchronize()
+            ms1 = e0.elapsed_time(e1) / k1
+            single = {"value": 1e3 / ms1, "unit": "tok/s", "ms_per_step": ms1, "steps": k1, "n_gpus": 1,
+                      "speedup_of_this_run": ms1 / ms_step,
+                      "hbm_gbs": total_bytes_all_ranks / ms1 / 1e6,
+                      "note": "same workload, all rows on rank 0's GPU, CUDA-graph replay, measured in this run"}
+            del full, g1
+            torch.cuda.empty_cache()
+            weights = []
+        dist.barrier()
+
     # ---- cpu baseline (rank 0, N = 1 only): the unmodified reference ggml-cpu on this host
     cpu = None
     if world == 1 and not args.no_cpu:
@@ -457,10 +606,10 @@ def main():
             "metric": metric_name(model), "value": 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": model + (" decode, split-mode row over %d GPUs + NCCL all-gather" % world if world > 1
+            "config": {"workload": model + (" decode, split-mode row over %d GPUs, %s" % (world, collective) if world > 1
                                             else " decode"),
                        "matmuls_per_step": len(mms), "batch": n, "l2": "inputs_exceed_l2 (%.2f GB of weights streamed "
-                       "per step per GPU)" % (sum(w.numel() for w in weights if w is not None) / 1e9),
+                       "per step per GPU)" % (weight_bytes_local / 1e9),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": how, "kernel": "k_gemv (all GEMV launches of the step)",
@@ -471,12 +620,19 @@ def main():
             "clocks": clocks,
             "ms_per_step_eager": ms_eager,
             "pp512": pp,
+            "single_gpu_same_workload": single,
+            "nccl_all_gather_baseline": nccl_leg,
+            "fused_row_split": fused_info if nccl_leg else None,
             "algorithmic_bytes_per_token_all_gpus": total_bytes_all_ranks,
         }
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        # CUDA graphs that captured NCCL collectives make destroy_process_group hang at exit (seen on the 2-GPU box):
+        # every rank has printed / synchronized, so leave without the teardown
+        os._exit(0)
 
 
 if __name__ == "__main__":

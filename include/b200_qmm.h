@@ -194,27 +194,46 @@ B200_API int b200_row_split(int64_t m, int world, int rank, const float * tensor
 
 /*
  * Row-split MUL_MAT with the all-gather FUSED into the GEMV epilogue: every rank computes rows [row_low,row_high) of
- * dst and stores them straight into every peer's dst buffer over NVLink (peer_dst[r] = rank r's dst, mapped through
- * CUDA IPC / peer access), then signals a per-call flag.  Replaces the broadcast + strided peer-copy + event
- * choreography of ggml_cuda_op_mul_mat in split mode, ggml/src/ggml-cuda/ggml-cuda.cu:1560-1700.
- * A plain NCCL all-gather of the slices produced by b200_mul_mat (dst = local slice) is the non-fused alternative.
+ * dst and stores them straight into every rank's dst buffer over NVLink (peer_dst[r] = rank r's dst, mapped through
+ * CUDA IPC / peer access); the last CTA to finish bumps every rank's arrival counter once.  No collective launch.
+ * Replaces the broadcast + strided peer-copy + event choreography of ggml_cuda_op_mul_mat in split mode,
+ * ggml/src/ggml-cuda/ggml-cuda.cu:1560-1700.  A plain NCCL all-gather of the slices produced by b200_mul_mat
+ * (dst = local slice) is the non-fused alternative.
  *
- *   W         this rank's row slice (rows row_low..row_high of the full matrix), packed
- *   x         device f32 [n][k], identical on every rank
- *   peer_dst  host array of `world` device pointers; entry r is rank r's full [n][m] dst (entry `rank` is local)
- *   flags     host array of `world` device pointers to int32 arrival counters (one per rank, zero-initialised)
- *   epoch     strictly increasing per call on a given (dst, flags) pair
+ *   W          this rank's row slice (rows row_low..row_high of the full matrix), packed
+ *   x          device f32 [n][k], identical on every rank; n <= 4, k <= 32768
+ *   peer_dst   host array of `world` device pointers; entry r is rank r's full [n][m] dst (entry `rank` is local)
+ *   peer_sync  host array of `world` device pointers; entry r is rank r's sync block: two int32, 8-byte aligned,
+ *              zero-initialised -- [0] arrival counter, [1] scratch owned by rank r's kernels
+ *   wait_sync, wait_arrivals
+ *              NULL, or THIS rank's sync block of the earlier fused call(s) whose result x was computed from, and the
+ *              number of arrivals that makes that result whole: the activation quantizer of this call then waits
+ *              in-kernel (bounded spin on the arrival counter, the
+ *              producers run on other GPUs) until that result is whole, and this call re-arms the block -- the chained
+ *              form of b200_rowsplit_wait without a stream operation between the two matmuls.  A timeout (~2 s) leaves
+ *              -1 in wait_sync[1] instead of hanging.
+ *   workspace  device scratch of b200_mul_mat_rowsplit_workspace_size(type, n, k) bytes
+ *
+ * Completion: every fused call of every rank counts one ARRIVAL on each rank's block, so dst on THIS rank is whole once
+ * `world` arrivals are in (`world * c` when c fused calls -- independent matmuls such as q/k/v -- share the block).
+ * b200_rowsplit_wait(peer_sync[rank], arrivals, stream) makes later work on the stream wait for that (stream memory
+ * operations -- no spinning kernel) and re-arms the counter.  Reuse rule for a sync block: between two fused calls on the same block every rank must have issued a
+ * fused call + wait on a DIFFERENT block (alternate between two blocks, or use one per matmul of the graph).
  */
+B200_API size_t b200_mul_mat_rowsplit_workspace_size(int type, int64_t n, int64_t k);
 B200_API int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64_t x_row_stride,
-                                         float * const * peer_dst, int32_t * const * flags, int32_t epoch,
+                                         float * const * peer_dst, int32_t * const * peer_sync,
                                          int64_t dst_row_stride, int64_t m, int64_t row_low, int64_t row_high,
-                                         int64_t n, int64_t k, int world, int rank, void * workspace,
-                                         size_t workspace_bytes, b200_stream_t stream);
+                                         int64_t n, int64_t k, int world, int rank, int32_t * wait_sync,
+                                         int wait_arrivals, void * workspace, size_t workspace_bytes,
+                                         b200_stream_t stream);
+B200_API int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream);
 
-/* CUDA IPC helpers so that one-process-per-GPU hosts (torchrun) can exchange peer buffers without torch types */
-B200_API int b200_ipc_get_handle(void * device_ptr, void * handle_out_64_bytes);
-B200_API int b200_ipc_open_handle(const void * handle_64_bytes, void ** device_ptr_out);
-B200_API int b200_ipc_close_handle(void * device_ptr);
+/* CUDA IPC helpers so that one-process-per-GPU hosts (torchrun) can exchange peer buffers without torch types.
+ * The handle names the allocation device_ptr lies in; *offset_out is device_ptr's offset inside it. */
+B200_API int b200_ipc_get_handle(void * device_ptr, void * handle_out_64_bytes, int64_t * offset_out);
+B200_API int b200_ipc_open_handle(const void * handle_64_bytes, int64_t offset, void ** device_ptr_out);
+B200_API int b200_ipc_close_handle(void * device_ptr, int64_t offset);
 
 #ifdef __cplusplus
 }

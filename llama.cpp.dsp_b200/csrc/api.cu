@@ -3,6 +3,8 @@
 #include "actquant.cuh"
 #include "kernels.h"
 
+#include <cuda.h>
+
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -57,6 +59,18 @@ static int check_weights(int type, const void * W, int64_t & stride, int64_t k) 
 }  // namespace b200
 
 using namespace b200;
+
+struct rowsplit_signal_args {
+    int32_t * flag[16];
+    int       world;
+};
+// the arrival of a rank that owns no rows of this matrix (or of the world == 1 degenerate case)
+static __global__ void k_rowsplit_signal(const rowsplit_signal_args a) {
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        for (int r = 0; r < a.world; r++) atomicAdd_system(a.flag[r], B200_ARRIVAL_UNIT);
+    }
+}
 
 extern "C" {
 
@@ -349,49 +363,123 @@ int b200_row_split(int64_t m, int world, int rank, const float * tensor_split, i
 }
 
 int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64_t x_row_stride,
-                                float * const * peer_dst, int32_t * const * flags, int32_t epoch,
-                                int64_t dst_row_stride, int64_t m, int64_t row_low, int64_t row_high, int64_t n,
-                                int64_t k, int world, int rank, void * workspace, size_t workspace_bytes,
+                                float * const * peer_dst, int32_t * const * peer_sync, int64_t dst_row_stride,
+                                int64_t m, int64_t row_low, int64_t row_high, int64_t n, int64_t k, int world, int rank,
+                                int32_t * wait_sync, int wait_arrivals, void * workspace, size_t workspace_bytes,
                                 b200_stream_t stream_) {
-    (void) workspace, (void) workspace_bytes;
     cudaStream_t stream = (cudaStream_t) stream_;
     int64_t row_stride = 0;
     int st = check_weights(type, W, row_stride, k);
     if (st != B200_OK) return st;
     if (world < 1 || world > 16 || rank < 0 || rank >= world || row_low < 0 || row_high < row_low || row_high > m)
         return B200_ERR_SHAPE;
-    if (n != 1 || k <= 0) return B200_ERR_UNSUPPORTED;
-    if (gemv_max_cols(type, k) < n) return B200_ERR_UNSUPPORTED;
+    if (n < 1 || k <= 0 || x_row_stride < k || dst_row_stride < m) return B200_ERR_SHAPE;
+    if (!peer_dst || !peer_sync) return B200_ERR_SHAPE;
+    if (gemv_max_cols(type, k) < n) return B200_ERR_UNSUPPORTED;   // one launch = one arrival: n <= 4, k <= 32768
+    for (int r = 0; r < world; r++)
+        if (!peer_dst[r] || !peer_sync[r] || (uintptr_t) peer_sync[r] % 8 != 0) return B200_ERR_ALIGNMENT;
+    if (wait_sync && wait_arrivals < 1) return B200_ERR_SHAPE;
+    if (row_high == row_low) {  // nothing to compute on this rank, but the peers still count its arrival
+        if (wait_sync) {        // ... and the dependency on the previous result is kept (stream-ordered wait + re-arm)
+            st = b200_rowsplit_wait(wait_sync, wait_arrivals, stream_);
+            if (st != B200_OK) return st;
+        }
+        rowsplit_signal_args sa = {};
+        sa.world = world;
+        for (int r = 0; r < world; r++) sa.flag[r] = peer_sync[r];
+        k_rowsplit_signal<<<1, 32, 0, stream>>>(sa);
+        B200_CUDA_TRY(cudaGetLastError());
+        note_launch();
+        return B200_OK;
+    }
+    const q8_layout L = q8_soa_layout(k);
+    if (!workspace || workspace_bytes < (size_t) n * L.bytes) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 16 != 0) return B200_ERR_ALIGNMENT;
+    st = launch_quantize_q8_soa(x, x_row_stride, workspace, k, n, type == B200_TYPE_IQ4_XS, stream, wait_sync,
+                                wait_arrivals * B200_ARRIVAL_UNIT);
+    if (st != B200_OK) return st;
     gemv_args g = {};
     g.type = type, g.W = (const uint8_t *) W, g.w_row_stride = row_stride;
-    g.x = x, g.x_col_stride = x_row_stride, g.dst = peer_dst[rank], g.dst_col_stride = dst_row_stride;
+    g.xq = (const uint8_t *) workspace, g.x_col_stride = x_row_stride, g.dst = peer_dst[rank] + row_low;
+    g.dst_col_stride = dst_row_stride;
     g.m = row_high - row_low, g.k = k, g.ncols = (int) n;
-    g.world = world > 1 ? world : 2, g.rank = rank, g.row_offset = row_low, g.epoch = epoch;
-    if (world == 1) {  // degenerate: plain local matmul at the row offset
+    g.rank = rank, g.row_offset = row_low;
+    if (world == 1) {  // degenerate: a plain local matmul at the row offset, plus the arrival
         g.world = 1;
-        g.dst   = peer_dst[0] + row_low;
-        return launch_gemv(g, stream);
+        st = launch_gemv(g, stream);
+        if (st != B200_OK) return st;
+        if (wait_sync) B200_CUDA_TRY(cudaMemsetAsync(wait_sync, 0, 4, stream));   // re-arm (no peers to race with)
+        rowsplit_signal_args sa = {};
+        sa.world = 1, sa.flag[0] = peer_sync[0];
+        k_rowsplit_signal<<<1, 32, 0, stream>>>(sa);
+        B200_CUDA_TRY(cudaGetLastError());
+        note_launch();
+        return B200_OK;
     }
     g.world = world;
-    for (int r = 0; r < world; r++) g.peer_dst[r] = peer_dst[r], g.peer_flag[r] = flags[r];
+    g.local_count = peer_sync[rank] + 1;
+    g.rearm = wait_sync;
+    for (int r = 0; r < world; r++) g.peer_dst[r] = peer_dst[r], g.peer_flag[r] = peer_sync[r];
     return launch_gemv(g, stream);
 }
 
-int b200_ipc_get_handle(void * device_ptr, void * handle_out) {
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
-    cudaIpcMemHandle_t h;
-    B200_CUDA_TRY(cudaIpcGetMemHandle(&h, device_ptr));
-    memcpy(handle_out, &h, sizeof(h));
+size_t b200_mul_mat_rowsplit_workspace_size(int type, int64_t n, int64_t k) {
+    if (!weight_type(type) || n <= 0 || k <= 0) return 0;
+    return (size_t) n * q8_soa_layout(k).bytes;
+}
+
+// stream-ordered: later work on `stream` starts only after all `world` ranks' slices have landed in this rank's dst;
+// then the counter is re-armed.  No kernel spins: these are stream memory operations (cuStreamWaitValue32 /
+// cuStreamWriteValue32), capturable in CUDA graphs.
+int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream) {
+    typedef CUresult (*memop_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+    static memop_fn wait_fn = nullptr, write_fn = nullptr;
+    if (!wait_fn || !write_fn) {
+        void * p = nullptr, * q = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &qr) != cudaSuccess || !p) return B200_ERR_CUDA;
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &q, cudaEnableDefault, &qr) != cudaSuccess || !q) return B200_ERR_CUDA;
+        wait_fn = (memop_fn) p, write_fn = (memop_fn) q;
+    }
+    if (!sync_local || arrivals < 1 || arrivals > (INT32_MAX / B200_ARRIVAL_UNIT)) return B200_ERR_SHAPE;
+    if (wait_fn((CUstream) stream, (CUdeviceptr) sync_local, (cuuint32_t) arrivals * B200_ARRIVAL_UNIT,
+                CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
+        return B200_ERR_CUDA;
+    if (write_fn((CUstream) stream, (CUdeviceptr) sync_local, 0, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS)
+        return B200_ERR_CUDA;
     return B200_OK;
 }
-int b200_ipc_open_handle(const void * handle, void ** device_ptr_out) {
+
+int b200_ipc_get_handle(void * device_ptr, void * handle_out, int64_t * offset_out) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    // an IPC handle names the whole ALLOCATION the pointer lies in (a caching allocator hands out interior pointers)
+    typedef CUresult (*range_fn)(CUdeviceptr *, size_t *, CUdeviceptr);
+    static range_fn fn = nullptr;
+    if (!fn) {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &qr) != cudaSuccess || !p) return B200_ERR_CUDA;
+        fn = (range_fn) p;
+    }
+    CUdeviceptr base = 0;
+    size_t      size = 0;
+    if (fn(&base, &size, (CUdeviceptr) device_ptr) != CUDA_SUCCESS) return B200_ERR_CUDA;
+    cudaIpcMemHandle_t h;
+    B200_CUDA_TRY(cudaIpcGetMemHandle(&h, (void *) base));
+    memcpy(handle_out, &h, sizeof(h));
+    if (offset_out) *offset_out = (int64_t) ((CUdeviceptr) device_ptr - base);
+    return B200_OK;
+}
+int b200_ipc_open_handle(const void * handle, int64_t offset, void ** device_ptr_out) {
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, sizeof(h));
-    B200_CUDA_TRY(cudaIpcOpenMemHandle(device_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    void * base = nullptr;
+    B200_CUDA_TRY(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    *device_ptr_out = (char *) base + offset;
     return B200_OK;
 }
-int b200_ipc_close_handle(void * device_ptr) {
-    B200_CUDA_TRY(cudaIpcCloseMemHandle(device_ptr));
+int b200_ipc_close_handle(void * device_ptr, int64_t offset) {
+    B200_CUDA_TRY(cudaIpcCloseMemHandle((char *) device_ptr - offset));
     return B200_OK;
 }
 

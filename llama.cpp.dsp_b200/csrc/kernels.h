@@ -6,13 +6,19 @@
 
 namespace b200 {
 
+// one fused row-split launch of one rank adds exactly this much to every rank's arrival counter (its CTAs add 1 each,
+// the last one the remainder), so counters compare against arrivals * UNIT whatever the grids were
+#define B200_ARRIVAL_UNIT 4096
+
 int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows,
                               cudaStream_t stream);
+// wait_sync != nullptr: the kernel first waits (bounded spin) until wait_sync[0] >= wait_target -- row-split arrivals
 int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
-                           cudaStream_t stream);
+                           cudaStream_t stream, int32_t * wait_sync = nullptr, int wait_target = 0);
 // same, with an explicit output row pitch in bytes (>= q8_soa_layout(k).bytes, multiple of 16)
 int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, int64_t y_pitch, int64_t k, int64_t nrows,
-                                   bool interleave, cudaStream_t stream);
+                                   bool interleave, cudaStream_t stream, int32_t * wait_sync = nullptr,
+                                   int wait_target = 0);
 int launch_dequantize_f32(int type, const void * w, int64_t w_stride, float * y, int64_t k, int64_t nrows,
                           cudaStream_t stream);
 
@@ -40,8 +46,9 @@ struct gemv_args {
     int            world, rank;
     int64_t        row_offset;
     float *        peer_dst[16];
-    int32_t *      peer_flag[16];
-    int32_t        epoch;
+    int32_t *      peer_flag[16];   // every rank's arrival counter
+    int32_t *      local_count;     // this rank's CTA-completion counter (zero between launches)
+    int32_t *      rearm;           // arrival counter the quantizer of this launch waited on: reset by the last CTA
 };
 size_t gemv_q8_smem_bytes(int64_t k, int ncols);
 int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring

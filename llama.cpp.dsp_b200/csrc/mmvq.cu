@@ -404,7 +404,8 @@ __device__ __forceinline__ void trace_stamp(const gemv_kargs & a, int i) {
 struct gemv_peers {
     float *   dst[16];
     int32_t * flag[16];
-    int32_t   epoch;
+    int32_t * local;
+    int32_t * rearm;
 };
 
 // Sum V per-lane values over the 32 lanes of a warp with log2(V) exchange steps + the remaining plain steps.
@@ -542,8 +543,21 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         if (a.world > 1) {
             __syncwarp();
             if (lane == 0) {
+                // every row of this CTA is stored in every peer; the "empty" arrivals (release.cta) ordered those
+                // stores before this lane, so ONE system-scope fence per CTA publishes them.  Each CTA then adds 1 to
+                // every rank's arrival counter and the last one tops the launch up to B200_ARRIVAL_UNIT, so a rank's
+                // launch always counts UNIT whatever its grid size; the consumer side is the next call's quantizer
+                // (wait_sync) or a stream wait-value (b200_rowsplit_wait).
                 __threadfence_system();
-                for (int r = 0; r < a.world; r++) atomicAdd_system(peers.flag[r], 1);
+                const int total = (int) (gridDim.x * gridDim.y);
+                int add = 1;
+                if (atomicAdd(peers.local, 1) == total - 1) {
+                    atomicExch(peers.local, 0);
+                    if (peers.rearm) atomicExch(peers.rearm, 0);   // every CTA of this rank is past the wait on it
+                    add += B200_ARRIVAL_UNIT - total;
+                }
+                for (int r = 0; r < a.world; r++)
+                    asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(peers.flag[r]), "r"(add) : "memory");
             }
         }
         if (lane == 0) trace_stamp(a, 6);                       // last result written
@@ -630,8 +644,11 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 float v = 0.f;
                 for (int w = 0; w < T; w++) v += q[w];
                 if (a.world > 1) {
+                    // no fence here: the stage's "empty" arrival (release.cta) orders these stores before the
+                    // producer lane's single system-scope fence at the end of the CTA (a fence per stage costs an
+                    // NVLink round trip each: measured 49 us per matmul instead of ~10)
                     for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
-                    __threadfence_system();
+                    if (a.dbg & 4) __threadfence_system();      // experiment: fence per stage
                 } else {
                     dst[fc * a.dst_col_stride + r0 + fv] = v;
                 }
@@ -770,7 +787,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     gemv_peers peers = {};
     if (g.world > 1) {
         for (int r = 0; r < g.world && r < 16; r++) peers.dst[r] = g.peer_dst[r], peers.flag[r] = g.peer_flag[r];
-        peers.epoch = g.epoch;
+        peers.local = g.local_count, peers.rearm = g.rearm;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) gx, (unsigned) (g.ids ? g.npairs : 1), 1);

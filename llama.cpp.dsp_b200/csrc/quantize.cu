@@ -55,16 +55,36 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
 // Launched with programmatic stream serialization so the GEMV that consumes it can prefetch weights meanwhile.
 template <bool INTERLEAVE>
 __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restrict__ x, int64_t x_stride,
-                                                         uint8_t * __restrict__ y, int64_t y_pitch, int64_t k, bool vec) {
+                                                         uint8_t * __restrict__ y, int64_t y_pitch, int64_t k, bool vec,
+                                                         int32_t * wait_sync, int wait_target) {
     pdl_launch_dependents();   // first: the consuming GEMV may become resident and prefetch its weights right away
     pdl_wait();
+    if (wait_sync) {
+        // row-split: x is only whole once `wait_target` ranks' slices have landed (their GEMVs bump wait_sync[0] over
+        // NVLink).  The producers are kernels on OTHER GPUs, so this cannot starve them; the spin is bounded anyway
+        // (~2 s) and leaves a mark in wait_sync[1] instead of hanging the stream.
+        if (threadIdx.x == 0) {
+            const long long t0 = clock64();
+            int v;
+            for (;;) {
+                asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(wait_sync) : "memory");
+                if (v >= wait_target) break;
+                if (clock64() - t0 > (1ll << 32)) {
+                    atomicExch(wait_sync + 1, -1);
+                    break;
+                }
+            }
+        }
+        __syncthreads();
+    }
     const q8_layout L = q8_soa_layout(k);
     quantize_row_q8_soa<INTERLEAVE>(x + blockIdx.y * x_stride, k, y + (int64_t) blockIdx.y * y_pitch, L,
                                     blockIdx.x * 8 + (threadIdx.x >> 5), gridDim.x * 8, threadIdx.x & 31, vec);
 }
 
 int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, int64_t y_pitch, int64_t k,
-                                   int64_t nrows, bool interleave, cudaStream_t stream) {
+                                   int64_t nrows, bool interleave, cudaStream_t stream, int32_t * wait_sync,
+                                   int wait_target) {
     if (k == 0 || nrows == 0) return B200_OK;
     const bool vec = ((uintptr_t) x % 16 == 0) && (x_stride % 4 == 0);
     int64_t done = 0;
@@ -80,8 +100,8 @@ int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, 
         cfg.attrs = attr, cfg.numAttrs = 1;
         const float * xp = x + done * x_stride;
         uint8_t *     yp = (uint8_t *) y + done * y_pitch;
-        if (interleave) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<true>, xp, x_stride, yp, y_pitch, k, vec));
-        else            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<false>, xp, x_stride, yp, y_pitch, k, vec));
+        if (interleave) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<true>, xp, x_stride, yp, y_pitch, k, vec, wait_sync, wait_target));
+        else            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_q8_soa<false>, xp, x_stride, yp, y_pitch, k, vec, wait_sync, wait_target));
         note_launch();
         done += rows;
     }
@@ -89,8 +109,9 @@ int launch_quantize_q8_soa_strided(const float * x, int64_t x_stride, void * y, 
 }
 
 int launch_quantize_q8_soa(const float * x, int64_t x_stride, void * y, int64_t k, int64_t nrows, bool interleave,
-                           cudaStream_t stream) {
-    return launch_quantize_q8_soa_strided(x, x_stride, y, (int64_t) q8_soa_layout(k).bytes, k, nrows, interleave, stream);
+                           cudaStream_t stream, int32_t * wait_sync, int wait_target) {
+    return launch_quantize_q8_soa_strided(x, x_stride, y, (int64_t) q8_soa_layout(k).bytes, k, nrows, interleave, stream,
+                                          wait_sync, wait_target);
 }
 
 // ---------------------------------------------------------------------------------------------- dequantizers

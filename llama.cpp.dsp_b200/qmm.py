@@ -24,7 +24,8 @@ EXPORTS = [
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
     "b200_mul_mat", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
     "b200_mul_mat_mmq", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
-    "b200_mul_mat_rowsplit_fused", "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
+    "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
+    "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
 ]
 
 
@@ -79,11 +80,14 @@ def lib():
     L.b200_mul_mat_id.argtypes = [i32, vp, i64, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp,
                                   sz, vp]
     L.b200_row_split.argtypes = [i64, i32, i32, vp, C.POINTER(i64), C.POINTER(i64)]
-    L.b200_mul_mat_rowsplit_fused.argtypes = [i32, vp, vp, i64, vp, vp, i32, i64, i64, i64, i64, i64, i64, i32, i32,
-                                              vp, sz, vp]
-    L.b200_ipc_get_handle.argtypes = [vp, vp]
-    L.b200_ipc_open_handle.argtypes = [vp, C.POINTER(vp)]
-    L.b200_ipc_close_handle.argtypes = [vp]
+    L.b200_mul_mat_rowsplit_workspace_size.restype = sz
+    L.b200_mul_mat_rowsplit_workspace_size.argtypes = [i32, i64, i64]
+    L.b200_mul_mat_rowsplit_fused.argtypes = [i32, vp, vp, i64, vp, vp, i64, i64, i64, i64, i64, i64, i32, i32,
+                                              vp, i32, vp, sz, vp]
+    L.b200_rowsplit_wait.argtypes = [vp, i32, vp]
+    L.b200_ipc_get_handle.argtypes = [vp, vp, C.POINTER(i64)]
+    L.b200_ipc_open_handle.argtypes = [vp, i64, C.POINTER(vp)]
+    L.b200_ipc_close_handle.argtypes = [vp, i64]
     _lib = L
     return L
 
