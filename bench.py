@@ -228,6 +228,8 @@ def main():
     ap.add_argument("--no-pp", action="store_true", help="skip the pp512 leg")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: how the row slices come together (fused = peer stores from the GEMV epilogue)")
+    ap.add_argument("--per-node", action="store_true",
+                    help="N=1: one b200_mul_mat call per MUL_MAT node instead of b200_mul_mat_multi per src1 group")
     ap.add_argument("--no-single", action="store_true", help="N>1: skip the same-workload single-GPU leg on rank 0")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
     args = ap.parse_args()
@@ -275,12 +277,43 @@ def main():
     out_local = {m: torch.zeros((n, maxrows[m]), device=dev) for m in maxrows}
     out_full = {m: torch.zeros((world, n, maxrows[m]), device=dev) for m in maxrows} if world > 1 else None
 
-    def token_step():
+    def token_step_per_node():
         for (name, t, m, k), w, (lo, hi, _) in zip(mms, weights, slices):
             if w is not None:
                 qmm.mul_mat(t, w, xs[k], hi - lo, k, out=out_local[m][:, :hi - lo])
             if world > 1:
                 dist.all_gather_into_tensor(out_full[m], out_local[m])
+
+    # N = 1: MUL_MATs that read the same activations (q/k/v of a layer; gate/up) go through ONE b200_mul_mat_multi call:
+    # x quantized once, same-type matrices in one launch.  Same nodes, same results; --per-node keeps one call per node.
+    token_step = token_step_per_node
+    grouping = "one b200_mul_mat per MUL_MAT node"
+    if world == 1 and not args.per_node:
+        def group_of(name):
+            base = name.split(".")[0]
+            return {"attn_q": "qkv", "attn_k": "qkv", "attn_v": "qkv", "ffn_gate": "gu", "ffn_up": "gu"}.get(base, base)
+        node_groups = []
+        for (name, t, m, k), w in zip(mms, weights):
+            key = (group_of(name), name.split(".")[-1])
+            if not node_groups or node_groups[-1][0] != key:
+                node_groups.append((key, k, []))
+            node_groups[-1][2].append((name.split(".")[0], t, m, w))
+        out_node = {}
+        calls = []
+        for _, k, members in node_groups:
+            outs = []
+            for base, t, m, w in members:
+                if base not in out_node:
+                    out_node[base] = torch.zeros((n, m), device=dev)
+                outs.append(out_node[base])
+            calls.append((qmm.MultiMatMul([t for _, t, _, _ in members], [w for _, _, _, w in members],
+                                          [m for _, _, m, _ in members], k, outs, n), xs[k]))
+
+        def token_step_grouped():
+            for call, x in calls:
+                call(x)
+        token_step = token_step_grouped
+        grouping = "b200_mul_mat_multi per group of nodes sharing src1 (%d calls for %d nodes)" % (len(calls), len(mms))
 
     weight_bytes_local = sum(w.numel() for w in weights if w is not None)
     step_bytes = sum(gemv_bytes(t, hi - lo, k, n) for (_, t, _, k), (lo, hi, _) in zip(mms, slices) if hi > lo)
@@ -342,6 +375,26 @@ def main():
         torch.cuda.synchronize()
     clocks = clk.summary()
     ms_eager = timed(token_step, max(4, args.steps // 8), 3) if use_graph else ms_step
+    per_node = None
+    if world == 1 and token_step is not token_step_per_node:
+        # the same token with one call (one quantizer + one GEMV launch) per MUL_MAT node, for comparison
+        b0 = qmm.launch_count()
+        token_step_per_node()
+        torch.cuda.synchronize()
+        l_node = qmm.launch_count() - b0
+        run_n = token_step_per_node
+        if use_graph:
+            gn = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(stream):
+                token_step_per_node()
+                stream.synchronize()
+                with torch.cuda.graph(gn, stream=stream):
+                    token_step_per_node()
+            run_n = gn.replay
+        ms_node = timed(run_n, max(8, args.steps // 4), 3)
+        per_node = {"value": 1e3 / ms_node, "unit": "tok/s", "ms_per_step": ms_node, "launches_per_step": l_node,
+                    "hbm_gbs": step_bytes / ms_node / 1e6}
+        del run_n
 
     # ---- N > 1: the fused path -- each GEMV stores its rows into every rank's dst over NVLink, a stream wait-value
     #      replaces the collective (b200_mul_mat_rowsplit_fused + b200_rowsplit_wait).  When it runs, it is the headline
@@ -610,7 +663,7 @@ def main():
                                             else " decode"),
                        "matmuls_per_step": len(mms), "batch": n, "l2": "inputs_exceed_l2 (%.2f GB of weights streamed "
                        "per step per GPU)" % (weight_bytes_local / 1e9),
-                       "launch": "cuda_graph_replay" if use_graph else "eager"},
+                       "launch": "cuda_graph_replay" if use_graph else "eager", "calls": grouping},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": how, "kernel": "k_gemv (all GEMV launches of the step)",
                          "algorithmic_bytes_per_step": step_bytes, "launches_per_step": launches_per_step},
@@ -619,6 +672,7 @@ def main():
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
             "ms_per_step_eager": ms_eager,
+            "per_node_calls": per_node,
             "pp512": pp,
             "single_gpu_same_workload": single,
             "nccl_all_gather_baseline": nccl_leg,

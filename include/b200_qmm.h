@@ -120,6 +120,20 @@ B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, con
                              float * dst, int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                              size_t workspace_bytes, b200_stream_t stream);
 
+/*
+ * nmat MUL_MATs that read the SAME activations x (q/k/v of one attention block, gate/up of one FFN): dst[i] = W[i] x^T.
+ * x is quantized once instead of nmat times, and consecutive matrices of one type whose row counts are multiples of 8
+ * are multiplied by ONE kernel launch over their concatenated rows (up to 4 per launch) -- fewer, longer launches is
+ * what batch-1 decode is short of.  The reference issues quantize_row_q8_1_cuda + mul_mat_vec_q per node
+ * (ggml/src/ggml-cuda/ggml-cuda.cu:1877-1938); results equal nmat separate b200_mul_mat calls up to fp32 summation order.
+ * All W[i] are packed (row stride = b200_row_size); types[i] may differ; n >= 9 falls back to one b200_mul_mat per matrix.
+ */
+B200_API size_t b200_mul_mat_multi_workspace_size(int nmat, const int * types, const int64_t * m, int64_t n, int64_t k);
+B200_API int    b200_mul_mat_multi(int nmat, const int * types, const void * const * W, const float * x,
+                                   int64_t x_row_stride, float * const * dst, const int64_t * dst_row_stride,
+                                   const int64_t * m, int64_t n, int64_t k, void * workspace, size_t workspace_bytes,
+                                   b200_stream_t stream);
+
 /* ---- batched MUL_MAT on the tensor cores (n > 8) ---------------------------------------------------------------- */
 
 /*

@@ -242,6 +242,86 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
     return B200_OK;
 }
 
+// Several MUL_MATs that read the SAME activations (q/k/v; gate/up): x is quantized once, and consecutive matrices of one
+// type go out as ONE GEMV launch over their concatenated rows.
+size_t b200_mul_mat_multi_workspace_size(int nmat, const int * types, const int64_t * m, int64_t n, int64_t k) {
+    size_t need = 0;
+    for (int i = 0; i < nmat; i++) {
+        const size_t w = b200_mul_mat_workspace_size(types[i], m[i], n, k);
+        if (w > need) need = w;
+    }
+    // both activation layouts may be live at once (IQ4_XS wants its own)
+    if (k > 0 && n > 0 && n < mmq_min_batch()) need = 2 * ws_align((size_t) n * q8_soa_layout(k).bytes);
+    return need;
+}
+
+int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, const float * x, int64_t x_row_stride,
+                       float * const * dst, const int64_t * dst_row_stride, const int64_t * m, int64_t n, int64_t k,
+                       void * workspace, size_t workspace_bytes, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (nmat < 0 || (nmat > 0 && (!types || !W || !dst || !dst_row_stride || !m))) return B200_ERR_SHAPE;
+    if (nmat == 0 || n == 0) return B200_OK;
+    bool gemv_ok = n > 0 && k > 0 && x_row_stride >= k && (uintptr_t) x % 4 == 0;
+    for (int i = 0; i < nmat && gemv_ok; i++) gemv_ok = weight_type(types[i]) && !use_mmq(types[i], n, k);
+    if (!gemv_ok) {  // tensor-core sizes, odd arguments: one full b200_mul_mat per matrix (which validates them)
+        for (int i = 0; i < nmat; i++) {
+            int st = b200_mul_mat(types[i], W[i], 0, x, x_row_stride, dst[i], dst_row_stride[i], m[i], n, k, workspace,
+                                  workspace_bytes, stream_);
+            if (st != B200_OK) return st;
+        }
+        return B200_OK;
+    }
+    for (int i = 0; i < nmat; i++) {
+        int64_t stride = 0;
+        int st = check_weights(types[i], W[i], stride, k);
+        if (st != B200_OK) return st;
+        if (m[i] < 0 || m[i] > INT32_MAX || dst_row_stride[i] < m[i] || (uintptr_t) dst[i] % 4 != 0) return B200_ERR_SHAPE;
+    }
+    const q8_layout L    = q8_soa_layout(k);
+    const size_t    half = ws_align((size_t) n * L.bytes);
+    if (!workspace || workspace_bytes < 2 * half) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 16 != 0) return B200_ERR_ALIGNMENT;
+    uint8_t * xq[2]   = {(uint8_t *) workspace, (uint8_t *) workspace + half};   // [0] plain, [1] IQ4_XS-interleaved
+    bool      have[2] = {false, false};
+    int i = 0;
+    while (i < nmat) {
+        const int type = types[i], il = type == B200_TYPE_IQ4_XS ? 1 : 0;
+        if (!have[il]) {
+            int st = launch_quantize_q8_soa(x, x_row_stride, xq[il], k, n, il == 1, stream);
+            if (st != B200_OK) return st;
+            have[il] = true;
+        }
+        // the run of matrices that can share a launch: same type, rows a multiple of 8, total rows fit an int
+        int     j     = i + 1;
+        int64_t total = m[i];
+        if (m[i] % 8 == 0 && m[i] > 0)
+            while (j < nmat && j - i < 4 && types[j] == type && m[j] % 8 == 0 && m[j] > 0 && total + m[j] <= INT32_MAX)
+                total += m[j++];
+        const int maxc = gemv_max_cols(type, k);
+        for (int64_t c0 = 0; c0 < n; c0 += maxc) {
+            gemv_args g = {};
+            g.type = type, g.k = k, g.world = 1;
+            g.w_row_stride = (k / blck_of(type)) * (int64_t) tsize_of(type);
+            g.ncols = (int) (n - c0 < maxc ? n - c0 : maxc);
+            g.xq    = xq[il] + (size_t) c0 * L.bytes;
+            g.W = (const uint8_t *) W[i], g.dst = dst[i] + c0 * dst_row_stride[i], g.dst_col_stride = dst_row_stride[i];
+            g.m = total, g.nmat = j - i;
+            int64_t at = m[i];
+            for (int q = i + 1; q < j; q++) {
+                g.mstart[q - i - 1] = at, g.Wm[q - i - 1] = (const uint8_t *) W[q];
+                g.dstm[q - i - 1] = dst[q] + c0 * dst_row_stride[q], g.dcsm[q - i - 1] = dst_row_stride[q];
+                at += m[q];
+            }
+            if (g.m > 0) {
+                int st = launch_gemv(g, stream);
+                if (st != B200_OK) return st;
+            }
+        }
+        i = j;
+    }
+    return B200_OK;
+}
+
 static size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
 size_t b200_mul_mat_host_workspace_size(int type, int64_t m, int64_t n, int64_t k) {

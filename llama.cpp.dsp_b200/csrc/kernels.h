@@ -42,6 +42,13 @@ struct gemv_args {
     int            n_used, ne11;
     int64_t        npairs;
     int64_t        x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
+    // several matrices sharing x in one launch (nmat > 1): m = total rows; matrix 0 is (W, dst, dst_col_stride),
+    // matrix i >= 1 starts at virtual row mstart[i-1]; all contiguous, same type and k, every m_i % 8 == 0
+    int             nmat;
+    int64_t         mstart[3];
+    const uint8_t * Wm[3];
+    float *         dstm[3];
+    int64_t         dcsm[3];
     // fused row-split all-gather (world > 1): dst rows are offset by row_offset and mirrored into every peer
     int            world, rank;
     int64_t        row_offset;

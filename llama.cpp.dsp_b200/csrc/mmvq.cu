@@ -408,6 +408,26 @@ struct gemv_peers {
     int32_t * rearm;
 };
 
+// Several weight matrices of one type and row length multiplied with the SAME activations in one launch (q/k/v, gate/up):
+// the launch treats them as one matrix of a.m = sum(m_i) rows; matrices 1.. are described here, matrix 0 by gemv_kargs.
+struct gemv_multi {
+    int             nmat;         // 1 = plain launch
+    int             mstart[3];    // first virtual row of matrix 1, 2, 3
+    const uint8_t * W[3];
+    float *         dst[3];
+    int64_t         dst_col_stride[3];
+};
+__device__ __forceinline__ void gemv_locate(const gemv_multi & mm, int & r, const uint8_t *& W, float *& dst,
+                                            int64_t & dcs) {
+    if (mm.nmat > 1) {
+        int sub = 0;
+#pragma unroll
+        for (int i = 0; i < 3; i++)                             // compile-time indices: the arrays stay in param space
+            if (i + 1 < mm.nmat && r >= mm.mstart[i]) W = mm.W[i], dst = mm.dst[i], dcs = mm.dst_col_stride[i], sub = mm.mstart[i];
+        r -= sub;
+    }
+}
+
 // Sum V per-lane values over the 32 lanes of a warp with log2(V) exchange steps + the remaining plain steps.
 // On return p[0] holds the warp-wide sum of row `butterfly_row<V>(lane)`; lanes with (lane & (32/V - 1)) == 0 write it.
 template <int V>
@@ -449,7 +469,7 @@ template <int NCOLS, int MINB> struct gemv_shape {
 
 template <int TYPE, int NCOLS, int V, int MINB>
 __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<NCOLS, MINB>::RESIDENT)
-    k_gemv(const gemv_kargs a, const gemv_peers peers) {
+    k_gemv(const gemv_kargs a, const gemv_peers peers, const gemv_multi mm) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int BYTES = qtraits<TYPE>::bytes;
     constexpr int BLCK  = qtraits<TYPE>::blck;
@@ -480,8 +500,10 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     }
 
     // this CTA's rows and stages
-    const int  r_begin   = (int) ((int64_t) blockIdx.x * a.m / gridDim.x);
-    const int  r_end     = (int) ((int64_t) (blockIdx.x + 1) * a.m / gridDim.x);
+    // (several matrices: whole stages only, so that no stage straddles two matrices -- the host guarantees m_i % V == 0)
+    const int  gran      = mm.nmat > 1 ? V : 1;
+    const int  r_begin   = (int) ((int64_t) blockIdx.x * (a.m / gran) / gridDim.x) * gran;
+    const int  r_end     = (int) ((int64_t) (blockIdx.x + 1) * (a.m / gran) / gridDim.x) * gran;
     const int  nstages   = (r_end - r_begin + V - 1) / V;
     const int  row_bytes = a.k / BLCK * BYTES;
     const bool contiguous = a.w_row_stride == row_bytes;
@@ -508,7 +530,12 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 if (lane == 0) mbar_arrive(bar);
             } else if (contiguous) {
                 if (lane == 0) {
-                    const uint64_t g    = (uint64_t) (W + (int64_t) r0 * row_bytes);
+                    const uint8_t * Wl = W;
+                    float *         dl = nullptr;
+                    int64_t         sl = 0;
+                    int             rl = r0;
+                    gemv_locate(mm, rl, Wl, dl, sl);
+                    const uint64_t g    = (uint64_t) (Wl + (int64_t) rl * row_bytes);
                     const uint64_t g0   = g & ~(uint64_t) 15;
                     const uint32_t span = (uint32_t) (((g + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
                     mbar_expect_tx(bar, span);
@@ -606,7 +633,12 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         // row v starts at base + v * row_step + (its global address & 15): every bulk copy began at the 16-byte
         // boundary below its first byte (one copy per stage when rows are contiguous, one per row otherwise)
         const uint32_t base = sm_stage + slot * a.stage_bytes;
-        const uint32_t c0   = (uint32_t) ((uint64_t) (W + (int64_t) r0 * a.w_row_stride) & 15);
+        const uint8_t * Wl  = W;
+        float *         dl  = dst;
+        int64_t         dcs = a.dst_col_stride;
+        int             rl  = r0;
+        gemv_locate(mm, rl, Wl, dl, dcs);
+        const uint32_t c0   = (uint32_t) ((uint64_t) (Wl + (int64_t) rl * a.w_row_stride) & 15);
         float acc[NCOLS][V];
 #pragma unroll
         for (int v = 0; v < V; v++) {
@@ -650,7 +682,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                     for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
                     if (a.dbg & 4) __threadfence_system();      // experiment: fence per stage
                 } else {
-                    dst[fc * a.dst_col_stride + r0 + fv] = v;
+                    dl[fc * dcs + rl + fv] = v;
                 }
             }
             __syncwarp();
@@ -798,7 +830,13 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = env_int("B200_PDL", 1);
     cfg.attrs = attr, cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, a, peers));
+    gemv_multi mm = {};
+    mm.nmat = g.nmat > 1 ? g.nmat : 1;
+    for (int i = 1; i < mm.nmat; i++) {
+        mm.mstart[i - 1] = (int) g.mstart[i - 1], mm.W[i - 1] = g.Wm[i - 1], mm.dst[i - 1] = g.dstm[i - 1];
+        mm.dst_col_stride[i - 1] = g.dcsm[i - 1];
+    }
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, a, peers, mm));
     note_launch();
     return B200_OK;
 }
@@ -819,6 +857,7 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     if (pairs > 1) gx0 = (gx0 + pairs - 1) / pairs;             // MUL_MAT_ID: the pairs share the machine
     const bool fused = g.xq == nullptr;                         // f32 activations: quantize inside the kernel
     if (fused && NCOLS != 1) return B200_ERR_UNSUPPORTED;
+    if (g.nmat > 1 && (!contiguous || fused || g.ids || g.world > 1)) return B200_ERR_UNSUPPORTED;
     if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, fused, P)) return B200_ERR_UNSUPPORTED;
     int64_t gx = (int64_t) g_sm_count * P.minb * env_int("B200_GEMV_WAVES", 1);
     if (pairs > 1) gx = (gx + pairs - 1) / pairs;

@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libb200qmm.so")
+LIB_PATH = os.environ.get("B200_QMM_LIB") or os.path.join(HERE, "lib", "libb200qmm.so")   # override: A/B builds
 
 GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_Q8_1, GGML_TYPE_Q4_K, GGML_TYPE_Q6_K, GGML_TYPE_IQ4_XS = 2, 8, 9, 12, 14, 23
 TYPE_BY_NAME = {"q4_0": 2, "q8_0": 8, "q4_K": 12, "q6_K": 14, "iq4_xs": 23}
@@ -22,7 +22,7 @@ EXPORTS = [
     "b200_qmm_abi_version", "b200_status_string", "b200_last_cuda_error", "b200_device_ok", "b200_sm_count",
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
-    "b200_mul_mat", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
+    "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
     "b200_mul_mat_mmq", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
@@ -79,6 +79,9 @@ def lib():
     L.b200_mul_mat_id_workspace_size.argtypes = [i32, i64, i64, i64, i64, i64]
     L.b200_mul_mat_id.argtypes = [i32, vp, i64, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp,
                                   sz, vp]
+    L.b200_mul_mat_multi_workspace_size.restype = sz
+    L.b200_mul_mat_multi_workspace_size.argtypes = [i32, vp, vp, i64, i64]
+    L.b200_mul_mat_multi.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, vp, sz, vp]
     L.b200_row_split.argtypes = [i64, i32, i32, vp, C.POINTER(i64), C.POINTER(i64)]
     L.b200_mul_mat_rowsplit_workspace_size.restype = sz
     L.b200_mul_mat_rowsplit_workspace_size.argtypes = [i32, i64, i64]
@@ -193,6 +196,43 @@ def mul_mat(t, w, x, m, k, out=None, stream=None):
     check(lib().b200_mul_mat(t, w.data_ptr(), 0, x.data_ptr(), x.stride(0) if n > 1 else k, dst.data_ptr(),
                              dst.stride(0) if n > 1 else m, m, n, k, ws, wsz, _stream_ptr(stream)))
     return dst
+
+
+class MultiMatMul:
+    """Prepared argument block for b200_mul_mat_multi: several weight matrices multiplied with the same activations.
+    Built once per group (pointer arrays are ctypes arrays), called every token."""
+
+    def __init__(self, types, ws, ms, k, outs, n=1):
+        import torch
+        nmat = len(types)
+        _require_cuda(*ws, *outs)
+        self.nmat, self.k, self.n = nmat, k, n
+        self.keep = (list(ws), list(outs))
+        self.types = (C.c_int * nmat)(*types)
+        self.W = (C.c_void_p * nmat)(*[w.data_ptr() for w in ws])
+        self.dst = (C.c_void_p * nmat)(*[o.data_ptr() for o in outs])
+        self.dstride = (C.c_int64 * nmat)(*[(o.stride(0) if n > 1 else m) for o, m in zip(outs, ms)])
+        self.m = (C.c_int64 * nmat)(*ms)
+        self.ws_bytes = lib().b200_mul_mat_multi_workspace_size(nmat, self.types, self.m, n, k)
+        self.device = outs[0].device
+        assert all(o.dtype == torch.float32 for o in outs)
+
+    def __call__(self, x, stream=None):
+        n = x.shape[0]
+        assert n == self.n and x.shape[1] == self.k and x.stride(1) == 1
+        ws, wsz = _workspace(self.device, self.ws_bytes)
+        check(lib().b200_mul_mat_multi(self.nmat, self.types, self.W, x.data_ptr(), x.stride(0) if n > 1 else self.k,
+                                       self.dst, self.dstride, self.m, n, self.k, ws, wsz, _stream_ptr(stream)))
+
+
+def mul_mat_multi(types, ws, x, ms, k, outs=None, stream=None):
+    """[W_i x^T for i] with x quantized once and same-type matrices sharing launches; returns the list of dst [n, m_i]"""
+    import torch
+    n = x.shape[0]
+    if outs is None:
+        outs = [torch.empty((n, m), dtype=torch.float32, device=x.device) for m in ms]
+    MultiMatMul(types, ws, ms, k, outs, n)(x, stream)
+    return outs
 
 
 def build_plane(t, w, m, k, stream=None):

@@ -260,3 +260,46 @@ def test_launch_counter_counts_kernels(qmm):
     qmm.mul_mat(qref.Q4_K, w, torch.ones((1, 256), device="cuda"), 16, 256)
     # one fused launch (quantizer inside the GEMV) or two (separate q8_1 quantizer chained by programmatic launch)
     assert qmm.launch_count() - before in (1, 2)
+
+
+# ------------------------------------------------------------------------------------------------ several matrices, one x
+@pytest.mark.parametrize("n", [1, 2, 4, 5])
+def test_mul_mat_multi_equals_separate_calls(qmm, n):
+    """b200_mul_mat_multi (q/k/v, gate/up sharing activations): x quantized once, same-type matrices in one launch.
+    Mixed types, a row count that is not a multiple of 8 (falls out of the shared launch), IQ4_XS (own activation
+    layout) and more than four matrices of one type are all in the list; every result must equal b200_mul_mat's up to
+    fp32 summation order (rows per stage, hence the in-warp reduction tree, depend on the launch's total row count)."""
+    rng = np.random.default_rng(21)
+    k = 4096
+    spec = [(12, 4096), (12, 1024), (14, 1024), (12, 4096), (12, 1004), (23, 512), (12, 512), (12, 256), (12, 128),
+            (12, 64), (12, 8), (8, 2048), (2, 96)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    x = dev(rng.uniform(-1, 1, (n, k)).astype(np.float32))
+    outs = qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
+    for (t, m), w, got in zip(spec, ws, outs):
+        want = qmm.mul_mat(t, w, x, m, k)
+        assert qref.nmse(want.cpu().numpy(), got.cpu().numpy()) < 1e-11, (t, m)
+        oracle = qref.mul_mat(t, w.cpu().numpy(), x.cpu().numpy(), m, k, "q8_1")
+        assert qref.nmse(oracle, got.cpu().numpy()) < NMSE_TIGHT, (t, m)
+
+
+def test_mul_mat_multi_large_batch_falls_back_to_tensor_cores(qmm):
+    rng = np.random.default_rng(22)
+    k, n = 1024, 33
+    spec = [(12, 256), (12, 384)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    x = dev(rng.uniform(-1, 1, (n, k)).astype(np.float32))
+    outs = qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
+    for (t, m), w, got in zip(spec, ws, outs):
+        assert torch.equal(got, qmm.mul_mat(t, w, x, m, k))
+
+
+def test_mul_mat_multi_launches_fewer_kernels(qmm):
+    rng = np.random.default_rng(23)
+    k = 4096
+    spec = [(12, 4096), (12, 1024), (12, 1024)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    x = dev(rng.uniform(-1, 1, (1, k)).astype(np.float32))
+    before = qmm.launch_count()
+    qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
+    assert qmm.launch_count() - before == 2          # one quantizer + one GEMV for three matrices
