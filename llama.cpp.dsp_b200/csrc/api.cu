@@ -148,6 +148,15 @@ static int fused_quant_max_k() {
     return e && *e ? atoi(e) : 0;
 }
 static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
+// in-lane activation quantizer inside the GEMV (no quantizer kernel): B200_INLANE_QUANT=1
+static bool use_inlane_quant() {
+    static int v = -1;
+    if (v < 0) {
+        const char * e = getenv("B200_INLANE_QUANT");
+        v = e && *e ? atoi(e) : 0;
+    }
+    return v != 0;
+}
 
 static int mmq_min_batch() {
     const char * e = getenv("B200_MMQ_MIN_N");
@@ -227,6 +236,16 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
         g.x = x, g.dst = dst, g.ncols = 1;
         return launch_gemv(g, stream);
     }
+    if (use_inlane_quant()) {
+        for (int64_t c0 = 0; c0 < n; c0 += maxc) {
+            g.ncols = (int) (n - c0 < maxc ? n - c0 : maxc);
+            g.x = x + c0 * x_row_stride, g.xq = nullptr, g.inlane = true;
+            g.dst = dst + c0 * dst_row_stride;
+            st = launch_gemv(g, stream);
+            if (st != B200_OK) return st;
+        }
+        return B200_OK;
+    }
     const q8_layout L = q8_soa_layout(k);
     if (!workspace || workspace_bytes < (size_t) n * L.bytes) return B200_ERR_WORKSPACE;
     if ((uintptr_t) workspace % 16 != 0) return B200_ERR_ALIGNMENT;
@@ -286,7 +305,8 @@ int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, cons
     int i = 0;
     while (i < nmat) {
         const int type = types[i], il = type == B200_TYPE_IQ4_XS ? 1 : 0;
-        if (!have[il]) {
+        const bool inlane = use_inlane_quant();
+        if (!inlane && !have[il]) {
             int st = launch_quantize_q8_soa(x, x_row_stride, xq[il], k, n, il == 1, stream);
             if (st != B200_OK) return st;
             have[il] = true;
@@ -304,6 +324,7 @@ int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, cons
             g.w_row_stride = (k / blck_of(type)) * (int64_t) tsize_of(type);
             g.ncols = (int) (n - c0 < maxc ? n - c0 : maxc);
             g.xq    = xq[il] + (size_t) c0 * L.bytes;
+            if (inlane) g.xq = nullptr, g.x = x + c0 * x_row_stride, g.x_col_stride = x_row_stride, g.inlane = true;
             g.W = (const uint8_t *) W[i], g.dst = dst[i] + c0 * dst_row_stride[i], g.dst_col_stride = dst_row_stride[i];
             g.m = total, g.nmat = j - i;
             int64_t at = m[i];

@@ -36,6 +36,7 @@ struct gemv_args {
     int64_t        dst_col_stride;   // elements
     int64_t        m, k;
     int            ncols;            // 1..8
+    bool           inlane;           // xq == nullptr: every lane quantizes its own 64 activations from x (no scratch)
     // MUL_MAT_ID (ids != nullptr): grid.y = n_tokens * n_used pairs, ncols must be 1
     const int32_t * ids;
     int64_t        ids_row_stride;

@@ -613,6 +613,17 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     q8_unit u[NCOLS];
     if (a.act_bytes) {
         make_unit_q8<TYPE, true>(u[0], smem, L, a.k, ugc);      // the host plans the fused quantizer for one column only
+    } else if (a.xq == nullptr) {
+        // in-lane quantizer: the lane quantizes exactly the 64 activations of its own unit from f32 (two q8_1 blocks;
+        // Q6_K: four 16-element halves shared with the neighbouring lane) -- no quantizer kernel, no scratch, and the
+        // only dependency left on the previous kernel is x itself
+        const float * xc = x;
+        if (a.ids) xc = x;                                       // (x was already offset to this pair's row above)
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            const float * xr = xc + (int64_t) c * a.x_col_stride;
+            make_unit_f32<TYPE>(u[c], xr, a.k, ugc, ((uintptr_t) xr & 15) == 0);
+        }
     } else {
         const uint8_t * xq = a.xq;
         if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
@@ -749,6 +760,7 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
         }
         const size_t budget = total - P.act_bytes;
         P.nteams = nw / T;
+        if (const int cap_t = env_int("B200_GEMV_TEAMS", 0)) P.nteams = P.nteams < cap_t ? P.nteams : cap_t;   // tuning knob
         // rows per stage: every team of the CTA should get a stage, and the ring should hold >= 3 stages
         int vfirst = 8;
         while (vfirst > 2 && (rows_per_cta < (int64_t) P.nteams * vfirst || (size_t) vfirst * P.row_pitch * 3 > budget))
@@ -855,7 +867,9 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     gemv_plan P;
     int64_t gx0 = (int64_t) g_sm_count * 2;
     if (pairs > 1) gx0 = (gx0 + pairs - 1) / pairs;             // MUL_MAT_ID: the pairs share the machine
-    const bool fused = g.xq == nullptr;                         // f32 activations: quantize inside the kernel
+    // f32 activations (xq == nullptr): quantize inside the kernel, cooperatively into shared memory (one column) or
+    // in-lane (g.inlane: any column count, no shared memory)
+    const bool fused = g.xq == nullptr && !g.inlane;
     if (fused && NCOLS != 1) return B200_ERR_UNSUPPORTED;
     if (g.nmat > 1 && (!contiguous || fused || g.ids || g.world > 1)) return B200_ERR_UNSUPPORTED;
     if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, fused, P)) return B200_ERR_UNSUPPORTED;

@@ -15,7 +15,7 @@ import qref  # noqa: E402
 
 qmm = b200pkg.load()
 KNOBS = ["B200_GEMV_STAGES", "B200_GEMV_V", "B200_GEMV_MINB", "B200_PDL", "B200_FUSED_QUANT_MAX_K", "B200_GEMV_WAVES",
-         "B200_GEMV_RESIDENT"]
+         "B200_GEMV_RESIDENT", "B200_GEMV_TEAMS"]
 
 
 def make_weights(t, m, k, copies, rng):
@@ -61,7 +61,16 @@ def main():
     names = [a for a in args if not a.startswith("--")] or ["q4_K"]
     rng = np.random.default_rng(0)
     shapes = [(4096, 14336), (14336, 4096), (4096, 4096), (1024, 4096)]
+    ns = (1, 2, 4, 8)
+    if "--big" in args:      # ring geometry on the shapes that carry the bytes of a decode token
+        shapes = [(28672, 4096), (14336, 4096), (4096, 14336), (6144, 4096), (4096, 4096)]
+        ns = (1,)
     configs = [{}] if quick else [
+        {}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 24}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 32},
+        {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 6}, {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 4},
+        {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 4, "B200_GEMV_STAGES": 12}, {"B200_GEMV_V": 2, "B200_GEMV_STAGES": 32},
+        {"B200_GEMV_V": 2, "B200_GEMV_STAGES": 64}, {"B200_GEMV_V": 4, "B200_GEMV_TEAMS": 4, "B200_GEMV_STAGES": 24},
+    ] if "--big" in args else [
         {}, {"B200_PDL": 0}, {"B200_GEMV_RESIDENT": 2}, {"B200_GEMV_RESIDENT": 2, "B200_FUSED_QUANT_MAX_K": 0},
         {"B200_FUSED_QUANT_MAX_K": 0}, {"B200_GEMV_V": 2}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 8},
         {"B200_GEMV_RESIDENT": 2, "B200_GEMV_V": 4}, {"B200_GEMV_RESIDENT": 2, "B200_GEMV_V": 8},
@@ -73,7 +82,7 @@ def main():
             nbytes = qmm.row_size(t, k) * m
             copies = max(2, int(600e6 // nbytes))          # > 4x L2
             ws = make_weights(t, m, k, copies, rng)
-            for n in (1, 2, 4, 8):
+            for n in ns:
                 for cfg in configs:
                     if n > 1 and cfg:
                         continue
