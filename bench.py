@@ -549,11 +549,41 @@ def main():
         plane_build_s = time.time() - t_pl0
         plane_bytes = sum(p_.numel() for p_ in planes)
 
-        def prefill_step():
+        def prefill_step_per_node():
             for (name, t, m, k), pl in zip(mms[:-1], planes):
                 qmm.mul_mat_mmq(t, pl, xpp[k], m, k, out=opp[m])
             name, t, m, k = mms[-1]
             qmm.mul_mat(t, weights[-1], xs[k], m, k, out=out_local[m])
+
+        # nodes that read the same activations (q/k/v, gate/up) share one b200_mul_mat_mmq_multi call
+        prefill_step = prefill_step_per_node
+        if not args.per_node:
+            def pgroup(name):
+                base = name.split(".")[0]
+                return {"attn_q": "qkv", "attn_k": "qkv", "attn_v": "qkv", "ffn_gate": "gu", "ffn_up": "gu"}.get(base, base)
+            pgroups = []
+            for (name, t, m, k), pl in zip(mms[:-1], planes):
+                key = (pgroup(name), name.split(".")[-1])
+                if not pgroups or pgroups[-1][0] != key:
+                    pgroups.append((key, k, []))
+                pgroups[-1][2].append((name.split(".")[0], t, m, pl))
+            opp_node = {}
+            pcalls = []
+            for _, k, members in pgroups:
+                outs = []
+                for base, t, m, pl in members:
+                    if base not in opp_node:
+                        opp_node[base] = torch.empty((npp, m), device=dev)
+                    outs.append(opp_node[base])
+                pcalls.append((qmm.MultiMatMulMMQ([t for _, t, _, _ in members], [pl for _, _, _, pl in members],
+                                                  [m for _, _, m, _ in members], k, outs, npp), xpp[k]))
+
+            def prefill_step_grouped():
+                for call, x in pcalls:
+                    call(x)
+                name, t, m, k = mms[-1]
+                qmm.mul_mat(t, weights[-1], xs[k], m, k, out=out_local[m])
+            prefill_step = prefill_step_grouped
 
         def prefill_step_transient():   # no cached planes: b200_mul_mat rebuilds each plane in its workspace
             for (name, t, m, k), w in zip(mms[:-1], weights[:-1]):
@@ -565,6 +595,7 @@ def main():
         pp_launches = qmm.launch_count() - b0
         ms_pp = timed(prefill_step, 5, 2)
         ms_pp_transient = timed(prefill_step_transient, 2, 1)
+        ms_pp_node = timed(prefill_step_per_node, 3, 1) if prefill_step is not prefill_step_per_node else ms_pp
         flops = sum(2.0 * m * k * npp for _, _, m, k in mms[:-1])
         # int8 tensor-core denominator: measured live with a cuBLASLt int8 GEMM (torch._int_mm), else 2 x measured bf16
         int8_peak, int8_how = None, None
@@ -594,6 +625,7 @@ def main():
               "roofline": {"bound": "tensor", "achieved": tops, "peak": int8_peak, "unit": "TOP/s (int8)",
                            "frac": tops / int8_peak, "peak_source": int8_how, "nominal_int8_tops": 4500.0,
                            "frac_of_nominal": tops / 4500.0, "kernel": "k_mmq (tcgen05.mma kind::i8, TMEM accumulators)"},
+              "per_node_calls": {"value": npp * 1e3 / ms_pp_node, "unit": "tok/s", "ms_per_step": ms_pp_node},
               "planes": {"cached": True, "bytes": plane_bytes, "build_seconds_once": plane_build_s},
               "transient_planes": {"value": npp * 1e3 / ms_pp_transient, "unit": "tok/s", "ms_per_step": ms_pp_transient}}
         del planes

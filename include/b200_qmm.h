@@ -156,6 +156,13 @@ B200_API size_t b200_mul_mat_mmq_workspace_size(int64_t m, int64_t n, int64_t k)
 B200_API int    b200_mul_mat_mmq(int type, const void * plane, const float * x, int64_t x_row_stride, float * dst,
                                  int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                                  size_t workspace_bytes, b200_stream_t stream);
+/* Several prepared planes of one k against the SAME activations (q/k/v, gate/up): x is quantized to int8 once and the
+ * m-tiles of up to four single-plane matrices share one GEMM grid, so a k/v projection's eight tiles do not hold a launch
+ * of their own.  Same results as one b200_mul_mat_mmq per matrix (bit-identical: tiles are independent). */
+B200_API int    b200_mul_mat_mmq_multi(int nmat, const int * types, const void * const * planes, const float * x,
+                                       int64_t x_row_stride, float * const * dst, const int64_t * dst_row_stride,
+                                       const int64_t * m, int64_t n, int64_t k, void * workspace,
+                                       size_t workspace_bytes, b200_stream_t stream);
 /* smallest n that b200_mul_mat sends to the tensor-core path (MMVQ_MAX_BATCH_SIZE + 1, ggml-cuda/mmvq.cuh:3) */
 B200_API int    b200_mmq_min_batch(void);
 

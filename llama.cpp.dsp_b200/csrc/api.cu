@@ -203,6 +203,47 @@ int b200_mul_mat_mmq(int type, const void * plane, const float * x, int64_t x_ro
     return launch_mmq(type, plane, x, x_row_stride, dst, dst_row_stride, m, n, k, workspace, (cudaStream_t) stream);
 }
 
+int b200_mul_mat_mmq_multi(int nmat, const int * types, const void * const * planes, const float * x, int64_t x_row_stride,
+                           float * const * dst, const int64_t * dst_row_stride, const int64_t * m, int64_t n, int64_t k,
+                           void * workspace, size_t workspace_bytes, b200_stream_t stream) {
+    if (nmat < 0 || (nmat > 0 && (!types || !planes || !dst || !dst_row_stride || !m))) return B200_ERR_SHAPE;
+    if (nmat == 0 || n == 0) return B200_OK;
+    if (n < 0 || k <= 0 || x_row_stride < k || n > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
+    if (!workspace || workspace_bytes < mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
+    // single-plane matrices share launches; two-plane types (Q8_0) take the two-pass path one by one
+    const void * pl[64];
+    float *      ds[64];
+    int64_t      st_[64], ms[64];
+    int cnt = 0;
+    auto flush = [&]() -> int {
+        if (!cnt) return B200_OK;
+        const int st = launch_mmq_multi(cnt, pl, x, x_row_stride, ds, st_, ms, n, k, workspace, (cudaStream_t) stream);
+        cnt = 0;
+        return st;
+    };
+    for (int i = 0; i < nmat; i++) {
+        if (!weight_type(types[i])) return B200_ERR_TYPE;
+        if (m[i] < 0 || m[i] > INT32_MAX || dst_row_stride[i] < m[i]) return B200_ERR_SHAPE;
+        if (m[i] == 0) continue;
+        if (!planes[i] || (uintptr_t) planes[i] % 256 != 0 || !dst[i]) return B200_ERR_ALIGNMENT;
+        if (mmq_nplanes(types[i]) != 1) {
+            int st = flush();
+            if (st != B200_OK) return st;
+            st = launch_mmq(types[i], planes[i], x, x_row_stride, dst[i], dst_row_stride[i], m[i], n, k, workspace,
+                            (cudaStream_t) stream);
+            if (st != B200_OK) return st;
+            continue;
+        }
+        pl[cnt] = planes[i], ds[cnt] = dst[i], st_[cnt] = dst_row_stride[i], ms[cnt] = m[i];
+        if (++cnt == 64) {
+            const int st = flush();
+            if (st != B200_OK) return st;
+        }
+    }
+    return flush();
+}
+
 int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x, int64_t x_row_stride, float * dst,
                  int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace, size_t workspace_bytes,
                  b200_stream_t stream_) {

@@ -65,6 +65,10 @@ int    launch_gemv(const gemv_args & a, cudaStream_t stream);
 // ---- batched matmul on tcgen05 (mmq.cu): int8 "prefill plane" of a weight tensor + the GEMM that consumes it
 size_t mmq_plane_bytes(int64_t m, int64_t k);
 size_t mmq_workspace_bytes(int64_t n, int64_t k);
+// several single-plane matrices of one k against the same activations: one activation quantizer, shared GEMM launches
+int    launch_mmq_multi(int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
+                        const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
+                        cudaStream_t stream);
 int    launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
                           cudaStream_t stream);
 int    mmq_nplanes(int type);   // int8 planes per weight tensor (2 for Q8_0: value + residual)

@@ -146,6 +146,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
         "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap * map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -209,6 +217,17 @@ struct mmq_kargs {
     int64_t       dst_stride;
     int           m, n, nch, npad, mpad;
     int           accumulate;   // dst += result (second plane of a two-plane weight)
+    // several weight matrices against the same activations in one launch (q/k/v, gate/up): the grid's x dimension runs
+    // over the m-tiles of all of them; matrix i >= 1 starts at tile tile0[i-1] and is described by the x-fields
+    int           nmat;
+    int           tile0[3];
+    const float * Sx[3];
+    float *       dstx[3];
+    int64_t       dst_stridex[3];
+    int           mx[3], mpadx[3];
+};
+struct mmq_maps3 {
+    CUtensorMap m[3];
 };
 
 template <int BN> struct mmq_shape {
@@ -219,35 +238,58 @@ template <int BN> struct mmq_shape {
     static constexpr int NSC     = 4;                                 // ring of per-chunk scale vectors
     static constexpr int SC_FLTS = MMQ_BM + BN;                       // [128 row scales][BN column scales]
     static constexpr int SMEM    = NS * STAGE + NSC * SC_FLTS * 4 + 1024;   // + alignment slack (128-byte swizzle: 1024)
-    static constexpr int THREADS = 320;
+    // Epilogue warps.  The epilogue is what paces this kernel: the accumulator is read out of TMEM once per 256-chunk at
+    // ~64 B/clk per SM, and a warp cannot overlap its own tcgen05.ld with its own scale-accumulate math.  16 warps of 32
+    // columns each (BN = 128) let one warp's math run under another's load; at BN = 256 that would need 64 accumulator
+    // registers per thread in a 576-thread CTA (96-register cap: it spills), so BN = 256 keeps 8 warps x 128 columns.
+    static constexpr int EW      = BN == 128 ? 16 : 8;
+    static constexpr int THREADS = (2 + EW) * 32;
+    static constexpr int NB      = 512 / BN;                          // TMEM accumulator buffers (all 512 columns in use)
 };
 
 template <int BN>
-__global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensorMap mapA,
-                                                const __grid_constant__ CUtensorMap mapB, const mmq_kargs a) {
+__global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_constant__ CUtensorMap mapA,
+                                                const __grid_constant__ CUtensorMap mapB, const mmq_kargs a,
+                                                const __grid_constant__ mmq_maps3 mapAx) {
     using SH = mmq_shape<BN>;
     constexpr int NS = SH::NS;
     extern __shared__ uint8_t mmq_smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * NS + 4 + 2 * SH::NSC];
+    constexpr int NB = SH::NB;
+    __shared__ __align__(8) uint64_t bars[2 * NS + 2 * NB + 2 * SH::NSC];
     __shared__ uint32_t tmem_slot;
 
     const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
-                   bar_tempty = bar_tfull + 16, bar_sfull = bar_tempty + 16, bar_sempty = bar_sfull + 8 * SH::NSC;
+                   bar_tempty = bar_tfull + 8 * NB, bar_sfull = bar_tempty + 8 * NB, bar_sempty = bar_sfull + 8 * SH::NSC;
     const uint32_t scales = tiles + NS * SH::STAGE;             // shared address of the scale ring
-    const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;
+    // which weight matrix this CTA works on (compile-time indices only: the parameter arrays stay in param space)
+    const CUtensorMap * pA = &mapA;
+    const float *       S  = a.S;
+    float *             dstp = a.dst;
+    int64_t             dstride = a.dst_stride;
+    int                 mrows = a.m, mpad = a.mpad, tile = (int) blockIdx.x;
+    if (a.nmat > 1) {
+        int first = 0;
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+            if (i + 1 < a.nmat && (int) blockIdx.x >= a.tile0[i])
+                pA = &mapAx.m[i], S = a.Sx[i], dstp = a.dstx[i], dstride = a.dst_stridex[i], mrows = a.mx[i], mpad = a.mpadx[i],
+                first = a.tile0[i];
+        tile -= first;
+    }
+    const int m0 = tile * MMQ_BM, n0 = blockIdx.y * BN;
     const int nch = a.nch, nkb = 2 * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
-        for (int b = 0; b < 2; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, 8);
-        for (int b = 0; b < SH::NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, 8);
+        for (int b = 0; b < NB; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, SH::EW);
+        for (int b = 0; b < SH::NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, SH::EW);
         mbar_fence_init();
-        prefetch_tmap(&mapA);
+        prefetch_tmap(pA);
         prefetch_tmap(&mapB);
     }
-    if (warp == 1) tmem_alloc<2 * BN>(smem_u32(&tmem_slot));
+    if (warp == 1) tmem_alloc<NB * BN>(smem_u32(&tmem_slot));
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -264,14 +306,14 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
                     mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
                     const uint32_t sd = scales + b * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
-                    tma_load_1d(sd, a.S + (int64_t) c * a.mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd, S + (int64_t) c * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
                     tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + n0, BN * 4, bar_sfull + 8 * b);
                 }
                 const int s = kb % NS, ph = (kb / NS) & 1;
                 mbar_wait(bar_empty + 8 * s, ph ^ 1);
                 const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
                 mbar_expect_tx(bar_full + 8 * s, SH::STAGE);
-                tma_load_2d(sa, &mapA, kb * MMQ_BK, m0, bar_full + 8 * s);
+                tma_load_2d(sa, pA, kb * MMQ_BK, m0, bar_full + 8 * s);
                 tma_load_2d(sb, &mapB, kb * MMQ_BK, n0, bar_full + 8 * s);
             }
         }
@@ -280,8 +322,8 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
         if (lane == 0) {
             constexpr uint32_t idesc = idesc_i8(MMQ_BM, BN);
             for (int c = 0; c < nch; c++) {
-                const int buf = c & 1;
-                mbar_wait(bar_tempty + 8 * buf, ((c >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+                const int buf = c % NB;
+                mbar_wait(bar_tempty + 8 * buf, ((c / NB) & 1) ^ 1);   // epilogue has drained this accumulator
                 tc_fence_after();
                 for (int h = 0; h < 2; h++) {
                     const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
@@ -299,7 +341,7 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
         }
     } else {
         // ------------------------------------------------------------------------------------------ epilogue warps
-        constexpr int CW = BN / 2;                               // columns per warp
+        constexpr int CW = BN / (SH::EW / 4);                    // columns per warp
         const int q = warp & 3, half = (warp - 2) >> 2;          // TMEM lane quarter (hardware: warp id % 4), column half
         const int row = m0 + q * 32 + lane, col0 = half * CW;
         float acc[CW];
@@ -307,12 +349,12 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
         for (int i = 0; i < CW; i++) acc[i] = 0.f;
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         for (int c = 0; c < nch; c++) {
-            const int buf = c & 1, sb = c % SH::NSC;
+            const int buf = c % NB, sb = c % SH::NSC;
             mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1);
             const float *  sv  = sring + sb * SH::SC_FLTS;
             const float    sic = sv[q * 32 + lane];
             const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);   // warp-uniform: broadcast reads
-            mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
+            mbar_wait(bar_tfull + 8 * buf, (c / NB) & 1);
             tc_fence_after();
 #pragma unroll
             for (int g = 0; g < CW / 32; g++) {
@@ -336,11 +378,207 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);     // scale vectors consumed
         }
-        if (row < a.m) {
+        if (row < mrows) {
 #pragma unroll
             for (int i = 0; i < CW; i++) {
                 const int j = n0 + col0 + i;
                 if (j < a.n) {                                   // lanes = consecutive rows: coalesced
+                    float * d = dstp + (int64_t) j * dstride + row;
+                    *d = a.accumulate ? acc[i] + *d : acc[i];
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<NB * BN>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------ CTA-pair GEMM kernel
+// The same pipeline with tcgen05.mma.cta_group::2: two CTAs on neighbouring SMs (a cluster of 2 along m) execute ONE
+// M256 x N256 x K32 instruction per step.  Each CTA stages its own 128 weight rows and only HALF of the activation tile
+// (128 of the 256 columns); the tensor cores of both SMs read both halves.  Per CTA and 256-chunk that is 64 KB of
+// TMA writes + 64 KB of operand reads instead of 96 + 96 -- the single-CTA kernel above is bound by exactly that
+// shared-memory traffic (ncu: no pipe, L2 or DRAM above 40 %, MMA issue waiting on operands).
+// Roles: both CTAs run a TMA producer and the eight epilogue warps; only the leader (cluster rank 0) issues MMAs.
+//   full[s]   lives in the leader: 2 arrivals (one per producer) + the bytes of all four TMA boxes
+//   empty[s]  in each CTA, signalled by the leader's tcgen05.commit multicast
+//   tfull[b]  in each CTA, same multicast;  tempty[b] in the leader: 16 arrivals (8 epilogue warps x 2 CTAs)
+__device__ __forceinline__ uint32_t mapa_cluster(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst_smem, const CUtensorMap * map, int c0, int c1,
+                                                 uint32_t bar_cluster_addr) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst_smem), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_result) {  // one warp in EACH CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+__device__ __forceinline__ void mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit_pair(uint32_t bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"(cta_mask)
+                 : "memory");
+}
+
+struct mmq_pair_shape {
+    static constexpr int BN      = 256;                               // columns of the pair's tile
+    static constexpr int NS      = 6;
+    static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // own 128 rows: 16 KB
+    static constexpr int B_BYTES = (BN / 2) * MMQ_BK;                 // own half of the columns: 16 KB
+    static constexpr int STAGE   = A_BYTES + B_BYTES;
+    static constexpr int NSC     = 4;
+    static constexpr int SC_FLTS = MMQ_BM + BN;
+    static constexpr int SMEM    = NS * STAGE + NSC * SC_FLTS * 4 + 1024;
+    static constexpr int THREADS = 320;
+};
+
+__global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUtensorMap mapA,
+                                                     const __grid_constant__ CUtensorMap mapB, const mmq_kargs a) {
+    using SH = mmq_pair_shape;
+    constexpr int NS = SH::NS, BN = SH::BN;
+    extern __shared__ uint8_t mmq_smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * NS + 4 + 2 * SH::NSC];
+    __shared__ uint32_t tmem_slot;
+
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
+                   bar_tempty = bar_tfull + 16, bar_sfull = bar_tempty + 16, bar_sempty = bar_sfull + 8 * SH::NSC;
+    const uint32_t scales = tiles + NS * SH::STAGE;
+    const uint32_t crank  = cluster_ctarank();
+    const bool     leader = crank == 0;
+    const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;   // blockIdx.x = 2 * pair + rank: my own 128 rows
+    const int ms0 = min(m0, a.mpad - MMQ_BM);
+    const int nch = a.nch, nkb = 2 * nch;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 2), mbar_init(bar_empty + 8 * s, 1);
+        for (int b = 0; b < 2; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, 16);
+        for (int b = 0; b < SH::NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, 8);
+        mbar_fence_init();
+        prefetch_tmap(&mapA);
+        prefetch_tmap(&mapB);
+    }
+    if (warp == 1) tmem_alloc_pair<2 * BN>(smem_u32(&tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                         // both CTAs' barriers and TMEM exist
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; kb++) {
+                if ((kb & 1) == 0) {
+                    const int c = kb >> 1, b = c % SH::NSC;
+                    mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
+                    const uint32_t sd = scales + b * SH::SC_FLTS * 4;
+                    mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
+                    tma_load_1d(sd, a.S + (int64_t) c * a.mpad + ms0, MMQ_BM * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + n0, BN * 4, bar_sfull + 8 * b);
+                }
+                const int s = kb % NS, ph = (kb / NS) & 1;
+                mbar_wait(bar_empty + 8 * s, ph ^ 1);            // the pair's MMAs have read my copy of this stage
+                const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
+                const uint32_t lf = mapa_cluster(bar_full + 8 * s, 0);   // completion is counted in the LEADER's barrier
+                tma_load_2d_pair(sa, &mapA, kb * MMQ_BK, m0, lf);
+                tma_load_2d_pair(sb, &mapB, kb * MMQ_BK, n0 + (int) crank * (BN / 2), lf);
+                if (leader) mbar_expect_tx(bar_full + 8 * s, 2 * SH::STAGE);
+                else mbar_arrive_cluster(lf);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------------------------------ MMA issuer (leader only)
+        if (lane == 0 && leader) {
+            constexpr uint32_t idesc = idesc_i8(2 * MMQ_BM, BN);
+            for (int c = 0; c < nch; c++) {
+                const int buf = c & 1;
+                mbar_wait(bar_tempty + 8 * buf, ((c >> 1) & 1) ^ 1);   // both CTAs' epilogues have drained this accumulator
+                tc_fence_after();
+                for (int h = 0; h < 2; h++) {
+                    const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
+                    mbar_wait(bar_full + 8 * s, ph);
+                    tc_fence_after();
+                    const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
+                    const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
+#pragma unroll
+                    for (int kk = 0; kk < MMQ_BK / 32; kk++)
+                        mma_i8_pair(tmem + buf * BN, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) ((h | kk) != 0));
+                    mma_commit_pair(bar_empty + 8 * s, 3);
+                }
+                mma_commit_pair(bar_tfull + 8 * buf, 3);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------------------------------ epilogue warps (both CTAs)
+        constexpr int CW = BN / 2;
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int row = m0 + q * 32 + lane, col0 = half * CW;
+        float acc[CW];
+#pragma unroll
+        for (int i = 0; i < CW; i++) acc[i] = 0.f;
+        const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
+        const uint32_t lte0 = mapa_cluster(bar_tempty, 0);
+        for (int c = 0; c < nch; c++) {
+            const int buf = c & 1, sb = c % SH::NSC;
+            mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1);
+            const float *  sv  = sring + sb * SH::SC_FLTS;
+            const float    sic = sv[q * 32 + lane];
+            const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
+            mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int g = 0; g < CW / 32; g++) {
+                uint32_t r[32];
+                tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0 + g * 32, r);
+                tmem_ld_wait();
+                if (g == CW / 32 - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(lte0 + 8 * buf);
+                }
+#pragma unroll
+                for (int i4 = 0; i4 < 8; i4++) {
+                    const float4 t = tp[g * 8 + i4];
+                    acc[g * 32 + 4 * i4 + 0] = fmaf((float) (int) r[4 * i4 + 0], sic * t.x, acc[g * 32 + 4 * i4 + 0]);
+                    acc[g * 32 + 4 * i4 + 1] = fmaf((float) (int) r[4 * i4 + 1], sic * t.y, acc[g * 32 + 4 * i4 + 1]);
+                    acc[g * 32 + 4 * i4 + 2] = fmaf((float) (int) r[4 * i4 + 2], sic * t.z, acc[g * 32 + 4 * i4 + 2]);
+                    acc[g * 32 + 4 * i4 + 3] = fmaf((float) (int) r[4 * i4 + 3], sic * t.w, acc[g * 32 + 4 * i4 + 3]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);
+        }
+        if (row < a.m) {
+#pragma unroll
+            for (int i = 0; i < CW; i++) {
+                const int j = n0 + col0 + i;
+                if (j < a.n) {
                     float * d = a.dst + (int64_t) j * a.dst_stride + row;
                     *d = a.accumulate ? acc[i] + *d : acc[i];
                 }
@@ -349,7 +587,8 @@ __global__ void __launch_bounds__(320, 1) k_mmq(const __grid_constant__ CUtensor
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<2 * BN>(tmem);
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_pair<2 * BN>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -420,7 +659,8 @@ int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane,
 size_t mmq_workspace_bytes(int64_t n, int64_t k) { return mmq_act_bytes(n, k) + 2048; }
 
 template <int BN>
-static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
+static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
+                         int mtiles, cudaStream_t stream) {
     static bool attr_set = false;
     auto kern = k_mmq<BN>;
     if (!attr_set) {
@@ -428,7 +668,7 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) ((a.m + MMQ_BM - 1) / MMQ_BM), (unsigned) ((a.n + BN - 1) / BN), 1);
+    cfg.gridDim          = dim3((unsigned) mtiles, (unsigned) ((a.n + BN - 1) / BN), 1);
     cfg.blockDim         = dim3(mmq_shape<BN>::THREADS, 1, 1);
     cfg.dynamicSmemBytes = mmq_shape<BN>::SMEM;
     cfg.stream           = stream;
@@ -436,7 +676,30 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a, mapAx));
+    note_launch();
+    return B200_OK;
+}
+
+static int launch_mmq_pair(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_mmq_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_pair_shape::SMEM));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    const unsigned mt = (unsigned) ((a.m + MMQ_BM - 1) / MMQ_BM);
+    cfg.gridDim          = dim3((mt + 1) / 2 * 2, (unsigned) ((a.n + mmq_pair_shape::BN - 1) / mmq_pair_shape::BN), 1);
+    cfg.blockDim         = dim3(mmq_pair_shape::THREADS, 1, 1);
+    cfg.dynamicSmemBytes = mmq_pair_shape::SMEM;
+    cfg.stream           = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2, attr[1].val.clusterDim.y = 1, attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr, cfg.numAttrs = 2;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_mmq_pair, mapA, mapB, a));
     note_launch();
     return B200_OK;
 }
@@ -463,8 +726,12 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
     const int64_t mt = (m + MMQ_BM - 1) / MMQ_BM;
     const char *  e  = getenv("B200_MMQ_BN");
     int bn = e && *e ? atoi(e) : ((n <= 128 || mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
+    // CTA pairs (tcgen05 cta_group::2): B200_MMQ_PAIR=1
+    const char * pe = getenv("B200_MMQ_PAIR");
+    const bool   pair = pe && atoi(pe) == 1 && n > 128 && mt >= 2;
+    if (pair) bn = 256;
     CUtensorMap mapA, mapB;
-    int st = make_map(&mapB, Q, n, kp, bn);
+    int st = make_map(&mapB, Q, n, kp, pair ? 128 : bn);
     if (st != B200_OK) return st;
     for (int pl = 0; pl < mmq_nplanes(type); pl++) {
         const uint8_t * pb = (const uint8_t *) plane + (size_t) pl * mmq_plane_bytes(m, k);
@@ -475,7 +742,68 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
         a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
         a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
         a.accumulate = pl > 0;
-        st = bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, stream) : launch_mmq_bn<128>(mapA, mapB, a, stream);
+        a.nmat = 1;
+        static const mmq_maps3 none = {};
+        st = pair ? launch_mmq_pair(mapA, mapB, a, stream)
+                  : bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, none, (int) mt, stream)
+                              : launch_mmq_bn<128>(mapA, mapB, a, none, (int) mt, stream);
+        if (st != B200_OK) return st;
+    }
+    return B200_OK;
+}
+
+// Several prepared planes (single-plane types, same k) against the same activations: x is quantized ONCE and the m-tiles
+// of all matrices share one grid (up to 4 matrices per launch), so that small matrices (k/v projections: 8 m-tiles) do not
+// leave the machine empty and every launch's fixed costs are paid once per group.
+int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
+                     const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
+                     cudaStream_t stream) {
+    if (nmat == 0 || n == 0) return B200_OK;
+    static int sm_count = 0;
+    if (!sm_count) {
+        int dev = 0;
+        B200_CUDA_TRY(cudaGetDevice(&dev));
+        B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
+    int8_t * Q  = (int8_t *) workspace;
+    float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
+    {
+        const int64_t warps = n * nch;
+        k_quantize_x8<<<(unsigned) ((warps + 7) / 8), 256, 0, stream>>>(x, x_stride, Q, Tt, n, k, kp, npad);
+        note_launch();
+        B200_CUDA_TRY(cudaGetLastError());
+    }
+    int64_t total_mt = 0;
+    for (int i = 0; i < nmat; i++) total_mt += (m[i] + MMQ_BM - 1) / MMQ_BM;
+    const char * e  = getenv("B200_MMQ_BN");
+    const int    bn = e && *e ? atoi(e) : ((n <= 128 || total_mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
+    CUtensorMap mapB;
+    int st = make_map(&mapB, Q, n, kp, bn);
+    if (st != B200_OK) return st;
+    for (int i0 = 0; i0 < nmat; i0 += 4) {
+        const int cnt = nmat - i0 < 4 ? nmat - i0 : 4;
+        CUtensorMap mapA;
+        mmq_maps3   mx = {};
+        mmq_kargs   a  = {};
+        a.Tt = Tt, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.accumulate = 0, a.nmat = cnt;
+        int tiles = 0;
+        for (int j = 0; j < cnt; j++) {
+            const int64_t   mj = m[i0 + j];
+            const uint8_t * pb = (const uint8_t *) planes[i0 + j];
+            const float *   Sj = (const float *) (pb + align256((size_t) mj * kp));
+            st = make_map(j == 0 ? &mapA : &mx.m[j - 1], pb, mj, kp, MMQ_BM);
+            if (st != B200_OK) return st;
+            if (j == 0) {
+                a.S = Sj, a.dst = dst[i0], a.dst_stride = dst_stride[i0], a.m = (int) mj, a.mpad = (int) mmq_mpad(mj);
+            } else {
+                a.tile0[j - 1] = tiles, a.Sx[j - 1] = Sj, a.dstx[j - 1] = dst[i0 + j], a.dst_stridex[j - 1] = dst_stride[i0 + j];
+                a.mx[j - 1] = (int) mj, a.mpadx[j - 1] = (int) mmq_mpad(mj);
+            }
+            tiles += (int) ((mj + MMQ_BM - 1) / MMQ_BM);
+        }
+        if (tiles == 0) continue;
+        st = bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, tiles, stream) : launch_mmq_bn<128>(mapA, mapB, a, mx, tiles, stream);
         if (st != B200_OK) return st;
     }
     return B200_OK;

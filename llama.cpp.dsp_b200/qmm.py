@@ -23,7 +23,7 @@ EXPORTS = [
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
     "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
-    "b200_mul_mat_mmq", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
+    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
 ]
@@ -82,6 +82,7 @@ def lib():
     L.b200_mul_mat_multi_workspace_size.restype = sz
     L.b200_mul_mat_multi_workspace_size.argtypes = [i32, vp, vp, i64, i64]
     L.b200_mul_mat_multi.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, vp, sz, vp]
+    L.b200_mul_mat_mmq_multi.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, vp, sz, vp]
     L.b200_row_split.argtypes = [i64, i32, i32, vp, C.POINTER(i64), C.POINTER(i64)]
     L.b200_mul_mat_rowsplit_workspace_size.restype = sz
     L.b200_mul_mat_rowsplit_workspace_size.argtypes = [i32, i64, i64]
@@ -223,6 +224,30 @@ class MultiMatMul:
         ws, wsz = _workspace(self.device, self.ws_bytes)
         check(lib().b200_mul_mat_multi(self.nmat, self.types, self.W, x.data_ptr(), x.stride(0) if n > 1 else self.k,
                                        self.dst, self.dstride, self.m, n, self.k, ws, wsz, _stream_ptr(stream)))
+
+
+class MultiMatMulMMQ:
+    """Prepared argument block for b200_mul_mat_mmq_multi: several weight PLANES multiplied with the same activations
+    on the tensor cores (prefill)."""
+
+    def __init__(self, types, planes, ms, k, outs, n):
+        nmat = len(types)
+        _require_cuda(*planes, *outs)
+        self.nmat, self.k, self.n = nmat, k, n
+        self.keep = (list(planes), list(outs))
+        self.types = (C.c_int * nmat)(*types)
+        self.P = (C.c_void_p * nmat)(*[p.data_ptr() for p in planes])
+        self.dst = (C.c_void_p * nmat)(*[o.data_ptr() for o in outs])
+        self.dstride = (C.c_int64 * nmat)(*[o.stride(0) for o in outs])
+        self.m = (C.c_int64 * nmat)(*ms)
+        self.ws_bytes = lib().b200_mul_mat_mmq_workspace_size(max(ms), n, k)
+        self.device = outs[0].device
+
+    def __call__(self, x, stream=None):
+        assert x.shape == (self.n, self.k) and x.stride(1) == 1
+        ws, wsz = _workspace(self.device, self.ws_bytes)
+        check(lib().b200_mul_mat_mmq_multi(self.nmat, self.types, self.P, x.data_ptr(), x.stride(0), self.dst,
+                                           self.dstride, self.m, self.n, self.k, ws, wsz, _stream_ptr(stream)))
 
 
 def mul_mat_multi(types, ws, x, ms, k, outs=None, stream=None):

@@ -303,3 +303,20 @@ def test_mul_mat_multi_launches_fewer_kernels(qmm):
     before = qmm.launch_count()
     qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
     assert qmm.launch_count() - before == 2          # one quantizer + one GEMV for three matrices
+
+
+def test_mmq_multi_planes_equal_single_calls(qmm):
+    """b200_mul_mat_mmq_multi: several planes, one activation matrix, shared grid.  Tiles are independent, so every
+    result must be BIT-identical to its own b200_mul_mat_mmq call; a Q8_0 member (two planes) takes the two-pass path
+    in the middle of the list, and more than four single-plane members span two launches."""
+    rng = np.random.default_rng(31)
+    k, n = 2048, 200
+    spec = [(12, 512), (12, 136), (14, 128), (8, 256), (23, 384), (2, 64), (12, 1024), (12, 100)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    planes = [qmm.build_plane(t, w, m, k) for (t, m), w in zip(spec, ws)]
+    x = dev(rng.uniform(-1, 1, (n, k)).astype(np.float32))
+    outs = [torch.full((n, m), float("nan"), device="cuda") for _, m in spec]
+    qmm.MultiMatMulMMQ([t for t, _ in spec], planes, [m for _, m in spec], k, outs, n)(x)
+    for (t, m), pl, got in zip(spec, planes, outs):
+        want = qmm.mul_mat_mmq(t, pl, x, m, k)
+        assert torch.equal(got, want), (t, m)
