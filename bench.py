@@ -508,10 +508,50 @@ def main():
 
     e2e = None
     if world == 1:
-        ms_e2e = timed(token_step_host, max(8, args.steps // 4), 3)
+        ms_e2e_eager = timed(token_step_host, max(8, args.steps // 4), 3)
+        ms_e2e, e2e_launch = ms_e2e_eager, "eager"
+        if use_graph:
+            # the same calls captured once and replayed: every replay still does every H2D copy, kernel and D2H copy
+            # (b200_mul_mat_host is stream-ordered, so a caller can capture it like any other stream work)
+            if token_step is token_step_per_node:
+                def host_calls_only():
+                    for (name, t, m, k), w, (lo, hi, _) in zip(mms, weights, slices):
+                        qmm.mul_mat_host(t, w, hx[k], hout[m], hi - lo, k)
+            else:
+                # grouped: one H2D copy of x per group, results of a group adjacent on the host -> one D2H copy per group
+                hcalls, hgroup_out = [], {}
+                for gkey, k, members in node_groups:
+                    total = sum(m for _, _, m, _ in members)
+                    sig = (gkey[0], total)
+                    if sig not in hgroup_out:
+                        hgroup_out[sig] = torch.zeros(n * total).pin_memory()
+                    outs, off = [], 0
+                    for _, _, m, _ in members:
+                        outs.append(hgroup_out[sig][off:off + n * m].view(n, m))
+                        off += n * m
+                    hcalls.append((qmm.MultiMatMulHost([t for _, t, _, _ in members], [w for _, _, _, w in members],
+                                                       [m for _, _, m, _ in members], k, outs, n), hx[k]))
+
+                def host_calls_only():
+                    for call, xh in hcalls:
+                        call(xh)
+                h2d = sum(n * k * 4 for _, k, _ in node_groups)
+            gh = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(stream):
+                host_calls_only()
+                stream.synchronize()
+                with torch.cuda.graph(gh, stream=stream):
+                    host_calls_only()
+
+            def token_step_host_graph():
+                gh.replay()
+                torch.cuda.current_stream().synchronize()   # the caller reads this token's results on the host
+            ms_e2e, e2e_launch = timed(token_step_host_graph, max(8, args.steps // 4), 3), "cuda_graph_replay"
         e2e = {"value": 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": ms_e2e, "api": "b200_mul_mat_host per MUL_MAT (pinned host x -> H2D -> GEMV -> D2H), "
-               "stream sync once per token"}
+               "ms_per_step": ms_e2e, "launch": e2e_launch, "ms_per_step_eager": ms_e2e_eager,
+               "api": ("b200_mul_mat_host per MUL_MAT" if token_step is token_step_per_node or not use_graph else
+                       "b200_mul_mat_multi_host per group of MUL_MATs sharing src1") +
+                      " (pinned host x -> H2D -> quantize + GEMV -> D2H), stream sync once per token"}
     else:
         # row-split: host activations are broadcast to every rank's device, the gathered result is read back on rank 0
         def token_step_host_split():
@@ -686,6 +726,16 @@ def main():
 
     if rank == 0:
         peak, how = peaks()
+        # DRAM bytes of all GEMV launches of one step, from the committed ncu pass over the same workload (None otherwise)
+        traffic, traffic_src = None, None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "decode_step_dram_traffic.json")))
+            if world == 1 and model == "llama3-8b-q4_k_m" and tj["algorithmic_bytes_per_step"] == step_bytes:
+                traffic = tj["gemv_dram_bytes_read"] + tj["gemv_dram_bytes_write"]
+                traffic_src = "ncu dram__bytes_read.sum + dram__bytes_write.sum over the step's GEMV launches " \
+                              "(profiles/r01/decode_step_dram_traffic.json)"
+        except Exception:  # noqa: BLE001
+            pass
         achieved = step_bytes / ms_step / 1e6   # GB/s per GPU (rank 0's slice)
         line = {
             "metric": metric_name(model), "value": 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
@@ -697,7 +747,7 @@ def main():
                        "per step per GPU)" % (weight_bytes_local / 1e9),
                        "launch": "cuda_graph_replay" if use_graph else "eager", "calls": grouping},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": how, "kernel": "k_gemv (all GEMV launches of the step)",
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": how, "kernel": "k_gemv (all GEMV launches of the step)",
                          "algorithmic_bytes_per_step": step_bytes, "launches_per_step": launches_per_step},
             "cpu_baseline": cpu,
             "e2e": e2e,

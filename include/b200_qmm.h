@@ -182,6 +182,15 @@ B200_API int    b200_mul_mat_host(int type, const void * W, int64_t w_row_stride
                                   float * dst_host, int64_t m, int64_t n, int64_t k, void * workspace,
                                   size_t workspace_bytes, b200_stream_t stream);
 
+/* Several matrices against one HOST activation block (b200_mul_mat_multi with the copies of b200_mul_mat_host): x is
+ * copied to the device once, and host results that lie back to back (dst_host[i+1] == dst_host[i] + n * m[i]) come back
+ * in one copy.  nmat <= 64. */
+B200_API size_t b200_mul_mat_multi_host_workspace_size(int nmat, const int * types, const int64_t * m, int64_t n,
+                                                       int64_t k);
+B200_API int    b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W, const float * x_host,
+                                        float * const * dst_host, const int64_t * m, int64_t n, int64_t k,
+                                        void * workspace, size_t workspace_bytes, b200_stream_t stream);
+
 /* ---- MUL_MAT_ID ------------------------------------------------------------------------------------------------ */
 
 /*

@@ -411,6 +411,55 @@ int b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const floa
     return B200_OK;
 }
 
+// Several matrices, one HOST activation block: one H2D copy of x, b200_mul_mat_multi on the device, and one D2H copy per
+// run of host results that lie back to back (a caller that keeps q/k/v or gate/up results adjacent gets a single copy).
+size_t b200_mul_mat_multi_host_workspace_size(int nmat, const int * types, const int64_t * m, int64_t n, int64_t k) {
+    if (nmat <= 0 || !types || !m || n < 0 || k < 0) return 0;
+    size_t rows = 0;
+    for (int i = 0; i < nmat; i++) rows += (size_t) (m[i] > 0 ? m[i] : 0);
+    return align256((size_t) n * k * 4) + align256((size_t) n * rows * 4 + 256 * (size_t) nmat) +
+           align256(b200_mul_mat_multi_workspace_size(nmat, types, m, n, k));
+}
+
+int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W, const float * x_host,
+                            float * const * dst_host, const int64_t * m, int64_t n, int64_t k, void * workspace,
+                            size_t workspace_bytes, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (nmat < 0 || nmat > 64 || (nmat > 0 && (!types || !W || !dst_host || !m))) return B200_ERR_SHAPE;
+    if (nmat == 0 || n == 0) return B200_OK;
+    if (n < 0 || k < 0) return B200_ERR_SHAPE;
+    const size_t need = b200_mul_mat_multi_host_workspace_size(nmat, types, m, n, k);
+    if (!workspace || workspace_bytes < need) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
+    size_t rows = 0;
+    for (int i = 0; i < nmat; i++) {
+        if (m[i] < 0) return B200_ERR_SHAPE;
+        rows += (size_t) m[i];
+    }
+    float * x_dev   = (float *) workspace;
+    float * dst_dev = (float *) ((uint8_t *) workspace + align256((size_t) n * k * 4));
+    void *  ws      = (uint8_t *) dst_dev + align256((size_t) n * rows * 4 + 256 * (size_t) nmat);
+    if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
+    float * dd[64];
+    int64_t ds[64];
+    size_t  off = 0;
+    for (int i = 0; i < nmat; i++) {   // device results packed in list order, exactly like adjacent host results
+        dd[i] = dst_dev + off, ds[i] = m[i];
+        off += (size_t) n * m[i];
+    }
+    const int st = b200_mul_mat_multi(nmat, types, W, x_dev, k, dd, ds, m, n, k, ws,
+                                      b200_mul_mat_multi_workspace_size(nmat, types, m, n, k), stream_);
+    if (st != B200_OK) return st;
+    for (int i = 0; i < nmat;) {
+        int    j     = i + 1;
+        size_t count = (size_t) n * m[i];
+        while (j < nmat && dst_host[j] == dst_host[i] + count) count += (size_t) n * m[j++];
+        if (count) B200_CUDA_TRY(cudaMemcpyAsync(dst_host[i], dd[i], count * 4, cudaMemcpyDeviceToHost, stream));
+        i = j;
+    }
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------------------- MUL_MAT_ID
 // Activations: the n_tokens * ne11 rows of b are quantized once into the workspace (row (t, j) at index t * ne11 + j),
 // then one GEMV grid with blockIdx.y = (token, slot) pair reads row (t, slot % ne11).  B200_FUSED_QUANT_MAX_K > 0

@@ -23,7 +23,8 @@ EXPORTS = [
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
     "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
-    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
+    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
+    "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
 ]
@@ -83,6 +84,9 @@ def lib():
     L.b200_mul_mat_multi_workspace_size.argtypes = [i32, vp, vp, i64, i64]
     L.b200_mul_mat_multi.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, vp, sz, vp]
     L.b200_mul_mat_mmq_multi.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, vp, sz, vp]
+    L.b200_mul_mat_multi_host_workspace_size.restype = sz
+    L.b200_mul_mat_multi_host_workspace_size.argtypes = [i32, vp, vp, i64, i64]
+    L.b200_mul_mat_multi_host.argtypes = [i32, vp, vp, vp, vp, vp, i64, i64, vp, sz, vp]
     L.b200_row_split.argtypes = [i64, i32, i32, vp, C.POINTER(i64), C.POINTER(i64)]
     L.b200_mul_mat_rowsplit_workspace_size.restype = sz
     L.b200_mul_mat_rowsplit_workspace_size.argtypes = [i32, i64, i64]
@@ -224,6 +228,29 @@ class MultiMatMul:
         ws, wsz = _workspace(self.device, self.ws_bytes)
         check(lib().b200_mul_mat_multi(self.nmat, self.types, self.W, x.data_ptr(), x.stride(0) if n > 1 else self.k,
                                        self.dst, self.dstride, self.m, n, self.k, ws, wsz, _stream_ptr(stream)))
+
+
+class MultiMatMulHost:
+    """b200_mul_mat_multi_host: device-resident weights, HOST activations and HOST results (adjacent results return in
+    one copy).  outs_host: list of host tensors [n, m_i]."""
+
+    def __init__(self, types, ws, ms, k, outs_host, n=1):
+        nmat = len(types)
+        _require_cuda(*ws)
+        self.nmat, self.k, self.n = nmat, k, n
+        self.keep = (list(ws), list(outs_host))
+        self.types = (C.c_int * nmat)(*types)
+        self.W = (C.c_void_p * nmat)(*[w.data_ptr() for w in ws])
+        self.dst = (C.c_void_p * nmat)(*[o.data_ptr() for o in outs_host])
+        self.m = (C.c_int64 * nmat)(*ms)
+        self.ws_bytes = lib().b200_mul_mat_multi_host_workspace_size(nmat, self.types, self.m, n, k)
+        self.device = ws[0].device
+
+    def __call__(self, x_host, stream=None):
+        assert not x_host.is_cuda and x_host.is_contiguous() and tuple(x_host.shape) == (self.n, self.k)
+        ws, wsz = _workspace(self.device, self.ws_bytes)
+        check(lib().b200_mul_mat_multi_host(self.nmat, self.types, self.W, x_host.data_ptr(), self.dst, self.m, self.n,
+                                            self.k, ws, wsz, _stream_ptr(stream)))
 
 
 class MultiMatMulMMQ:

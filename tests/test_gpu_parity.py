@@ -320,3 +320,24 @@ def test_mmq_multi_planes_equal_single_calls(qmm):
     for (t, m), pl, got in zip(spec, planes, outs):
         want = qmm.mul_mat_mmq(t, pl, x, m, k)
         assert torch.equal(got, want), (t, m)
+
+
+def test_mul_mat_multi_host_matches_device_path(qmm):
+    """b200_mul_mat_multi_host: host activations in, host results out (adjacent results in one copy, a separate one for
+    the buffer that is not adjacent)."""
+    rng = np.random.default_rng(41)
+    k, n = 4096, 2
+    spec = [(12, 512), (12, 256), (14, 128), (8, 64)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    xh = torch.from_numpy(rng.uniform(-1, 1, (n, k)).astype(np.float32)).pin_memory()
+    block = torch.full((n * (512 + 256 + 128),), float("nan")).pin_memory()
+    outs, off = [], 0
+    for _, m in spec[:3]:
+        outs.append(block[off:off + n * m].view(n, m))
+        off += n * m
+    outs.append(torch.full((n, 64), float("nan")).pin_memory())
+    qmm.MultiMatMulHost([t for t, _ in spec], ws, [m for _, m in spec], k, outs, n)(xh)
+    torch.cuda.synchronize()
+    want = qmm.mul_mat_multi([t for t, _ in spec], ws, xh.cuda(), [m for _, m in spec], k)
+    for got, w_ in zip(outs, want):
+        assert torch.equal(got, w_.cpu())
