@@ -107,9 +107,30 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
 
 // ------------------------------------------------------------------------------------------------ activation quantizer
 // One warp per (column j, chunk c): 8 floats per lane, t = amax / 127, Q = rint(x / t).
+// Also zeroes the results of a split-K GEMM (mmq_zero: up to 4 dst matrices of n rows, m % 4 == 0, 16-byte aligned rows),
+// whose two K halves are then added with red.global.add -- two addends onto zero give the same bits in either order.
+struct mmq_zero {
+    int     cnt;
+    float * p[4];
+    int64_t stride[4];   // elements between rows
+    int64_t m[4];
+};
 __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ x, int64_t x_stride, int8_t * __restrict__ Q,
                                                      float * __restrict__ Tt, int64_t n, int64_t k, int64_t kp,
-                                                     int64_t npad) {
+                                                     int64_t npad, const mmq_zero z) {
+    pdl_launch_dependents();   // the GEMM behind us sets up its barriers / TMEM and prefetches its tensor maps meanwhile
+    pdl_wait();                // x comes from the previous kernel, and dst may still be read by it
+    if (z.cnt) {
+        const int64_t tid = (int64_t) blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t) gridDim.x * blockDim.x;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < z.cnt) {
+                const int64_t m4 = z.m[i] / 4;
+                for (int64_t e = tid; e < n * m4; e += nthr)
+                    reinterpret_cast<float4 *>(z.p[i] + (e / m4) * z.stride[i])[e % m4] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    }
     const int     lane = threadIdx.x & 31;
     const int64_t wid  = (int64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t nch  = kp / MMQ_KC;
@@ -194,7 +215,77 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld32(taddr, r); }
+__device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld16(taddr, r); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// int32 accumulator -> fp32 without the conversion unit.  I2FP issues to the XU pipe (4 lanes/clk per SM sub-partition,
+// 8 clocks per warp instruction): ncu showed it 64 % busy with the tensor pipe at 25 % -- the conversion, not the MMA,
+// paced the kernel.  |D| <= 256 * 127 * 127 < 2^22, so  bits(1.5 * 2^23) + D  is the float 12582912 + D exactly and one
+// FADD removes the bias exactly: same bits as I2FP, on the INT and FMA pipes at full rate.
+constexpr uint32_t MAGIC_BITS = 0x4B400000u;
+constexpr float    MAGIC_F    = 12582912.0f;
+__device__ __forceinline__ float i32_to_f32_magic(uint32_t v) { return __fsub_rn(__uint_as_float(v + MAGIC_BITS), MAGIC_F); }
+// packed fp32 pairs (sm_100 FADD2 / FMUL2 / FFMA2): one issue slot per two elements
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float & lo, float & hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+// acc[0..N) += float(r[0..N)) * (sic * t[0..N)); EPI 0 = I2FP, 1 = magic-number conversion, 2 = magic + packed fp32.
+// All three produce the same bits (every operation is a separately rounded fp32 op on the same operands).
+template <int EPI, int N>
+__device__ __forceinline__ void epi_accumulate(const uint32_t (&r)[N], const float4 * tp, float sic, float * acc) {
+    if (EPI == 2) {
+        const uint64_t s2 = pack2(sic, sic), nm = pack2(-MAGIC_F, -MAGIC_F);
+        uint64_t * acc2 = reinterpret_cast<uint64_t *>(acc);
+#pragma unroll
+        for (int i4 = 0; i4 < N / 4; i4++) {
+            const float4 t = tp[i4];
+            const uint64_t st0 = mul2(s2, pack2(t.x, t.y)), st1 = mul2(s2, pack2(t.z, t.w));
+            const uint64_t f0 = add2(pack2(__uint_as_float(r[4 * i4 + 0] + MAGIC_BITS), __uint_as_float(r[4 * i4 + 1] + MAGIC_BITS)), nm);
+            const uint64_t f1 = add2(pack2(__uint_as_float(r[4 * i4 + 2] + MAGIC_BITS), __uint_as_float(r[4 * i4 + 3] + MAGIC_BITS)), nm);
+            acc2[2 * i4 + 0] = fma2(f0, st0, acc2[2 * i4 + 0]);
+            acc2[2 * i4 + 1] = fma2(f1, st1, acc2[2 * i4 + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int i4 = 0; i4 < N / 4; i4++) {
+            const float4 t = tp[i4];
+            const float  tt[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float f = EPI == 1 ? i32_to_f32_magic(r[4 * i4 + e]) : (float) (int) r[4 * i4 + e];
+                acc[4 * i4 + e] = fmaf(f, sic * tt[e], acc[4 * i4 + e]);
+            }
+        }
+    }
+}
 
 // shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows of 128 bytes, 8-row groups 1024 bytes apart
 // (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30), SBO >> 4 at [32,46), version 1 at [46,48),
@@ -209,6 +300,30 @@ __host__ __device__ constexpr uint32_t idesc_i8(int M, int N) {
     return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24);
 }
 
+// One accumulator chunk of an epilogue warp: CW columns of this warp's 32 TMEM lanes starting at `tbase`, software
+// pipelined over LW-column loads -- the TMEM load of group g+1 is in flight while group g is scaled and accumulated
+// (tcgen05.wait::ld waits for ALL outstanding loads, so load g+1 is issued right after the wait that delivered g).
+// `release()` hands the accumulator buffer back to the tensor core as soon as its last column is in registers.
+template <int EPI, int CW, typename Release>
+__device__ __forceinline__ void epi_chunk(uint32_t tbase, const float4 * tp, float sic, float * acc, Release release) {
+    constexpr int LW = CW > 32 ? 16 : 32;                        // columns per load: two loads' registers must fit
+    constexpr int NG = CW / LW;
+    uint32_t r[2][LW];
+    tmem_ldw(tbase, r[0]);
+#pragma unroll
+    for (int g = 0; g < NG; g++) {
+        tmem_ld_wait();
+        if (g + 1 < NG) {
+            tmem_ldw(tbase + (g + 1) * LW, r[(g + 1) & 1]);
+        } else {
+            tc_fence_before();
+            __syncwarp();
+            release();
+        }
+        epi_accumulate<EPI, LW>(r[g & 1], tp + g * (LW / 4), sic, acc + g * LW);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ the GEMM kernel
 struct mmq_kargs {
     const float * S;      // weight scales  [nch][mpad]
@@ -217,6 +332,9 @@ struct mmq_kargs {
     int64_t       dst_stride;
     int           m, n, nch, npad, mpad;
     int           accumulate;   // dst += result (second plane of a two-plane weight)
+    int           ksplit;       // 1, or 2: grid.z halves of the chunk range, results added with red.global.add onto a
+                                // zeroed dst (few-tile shapes: m = 4096 at n = 512 fills 64 of 148 SMs otherwise)
+    long long *   trace;        // -DB200_MMQ_TRACE builds only: 16 clock counters per CTA (tools/mmq_trace.py), else unused
     // several weight matrices against the same activations in one launch (q/k/v, gate/up): the grid's x dimension runs
     // over the m-tiles of all of them; matrix i >= 1 starts at tile tile0[i-1] and is described by the x-fields
     int           nmat;
@@ -230,6 +348,18 @@ struct mmq_maps3 {
     CUtensorMap m[3];
 };
 
+// Role-level wait accounting (trace builds only): TW(slot, wait) adds the clocks spent in `wait` to counter `slot`.
+#ifdef B200_MMQ_TRACE
+#define TW(slot, stmt)                                   \
+    do {                                                 \
+        const long long t0_ = clock64();                 \
+        stmt;                                            \
+        tw[slot] += clock64() - t0_;                     \
+    } while (0)
+#else
+#define TW(slot, stmt) stmt
+#endif
+
 template <int BN> struct mmq_shape {
     static constexpr int NS      = BN == 256 ? 4 : 6;                 // shared-memory stages
     static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // 16 KB
@@ -242,12 +372,12 @@ template <int BN> struct mmq_shape {
     // ~64 B/clk per SM, and a warp cannot overlap its own tcgen05.ld with its own scale-accumulate math.  16 warps of 32
     // columns each (BN = 128) let one warp's math run under another's load; at BN = 256 that would need 64 accumulator
     // registers per thread in a 576-thread CTA (96-register cap: it spills), so BN = 256 keeps 8 warps x 128 columns.
-    static constexpr int EW      = BN == 128 ? 16 : 8;
+    static constexpr int EW      = 16;
     static constexpr int THREADS = (2 + EW) * 32;
     static constexpr int NB      = 512 / BN;                          // TMEM accumulator buffers (all 512 columns in use)
 };
 
-template <int BN>
+template <int BN, int EPI>
 __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_constant__ CUtensorMap mapA,
                                                 const __grid_constant__ CUtensorMap mapB, const mmq_kargs a,
                                                 const __grid_constant__ mmq_maps3 mapAx) {
@@ -279,7 +409,9 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
         tile -= first;
     }
     const int m0 = tile * MMQ_BM, n0 = blockIdx.y * BN;
-    const int nch = a.nch, nkb = 2 * nch;
+    // this CTA's chunk range [cb, cb + nch): everything below counts chunks and k-blocks locally
+    const int cper = (a.nch + a.ksplit - 1) / a.ksplit, cb = (int) blockIdx.z * cper;
+    const int nch = min(cper, a.nch - cb), nkb = 2 * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
@@ -297,25 +429,35 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
     pdl_launch_dependents();
     pdl_wait();                                                 // activations come from the quantizer kernel before us
 
+#ifdef B200_MMQ_TRACE
+    long long tw[4] = {0, 0, 0, 0};
+    const long long t_start = clock64();
+#endif
     if (warp == 0) {
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             for (int kb = 0; kb < nkb; kb++) {
                 if ((kb & 1) == 0) {                             // this chunk's scale vectors, ahead of its tiles
                     const int c = kb >> 1, b = c % SH::NSC;
-                    mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
+                    TW(0, mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1));
                     const uint32_t sd = scales + b * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
-                    tma_load_1d(sd, S + (int64_t) c * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
-                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + n0, BN * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd, S + (int64_t) (cb + c) * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) (cb + c) * a.npad + n0, BN * 4, bar_sfull + 8 * b);
                 }
                 const int s = kb % NS, ph = (kb / NS) & 1;
-                mbar_wait(bar_empty + 8 * s, ph ^ 1);
+                TW(1, mbar_wait(bar_empty + 8 * s, ph ^ 1));
                 const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
                 mbar_expect_tx(bar_full + 8 * s, SH::STAGE);
-                tma_load_2d(sa, pA, kb * MMQ_BK, m0, bar_full + 8 * s);
-                tma_load_2d(sb, &mapB, kb * MMQ_BK, n0, bar_full + 8 * s);
+                tma_load_2d(sa, pA, (2 * cb + kb) * MMQ_BK, m0, bar_full + 8 * s);
+                tma_load_2d(sb, &mapB, (2 * cb + kb) * MMQ_BK, n0, bar_full + 8 * s);
             }
+#ifdef B200_MMQ_TRACE
+            if (a.trace) {
+                long long * o = a.trace + ((size_t) blockIdx.y * gridDim.x + blockIdx.x) * 16;
+                o[0] = clock64() - t_start, o[1] = tw[0], o[2] = tw[1];
+            }
+#endif
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------------------------------ MMA issuer
@@ -323,11 +465,11 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
             constexpr uint32_t idesc = idesc_i8(MMQ_BM, BN);
             for (int c = 0; c < nch; c++) {
                 const int buf = c % NB;
-                mbar_wait(bar_tempty + 8 * buf, ((c / NB) & 1) ^ 1);   // epilogue has drained this accumulator
+                TW(0, mbar_wait(bar_tempty + 8 * buf, ((c / NB) & 1) ^ 1));   // epilogue has drained this accumulator
                 tc_fence_after();
                 for (int h = 0; h < 2; h++) {
                     const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
-                    mbar_wait(bar_full + 8 * s, ph);
+                    TW(1, mbar_wait(bar_full + 8 * s, ph));
                     tc_fence_after();
                     const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
                     const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
@@ -338,56 +480,58 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
                 }
                 mma_commit(bar_tfull + 8 * buf);                 // chunk accumulated
             }
+#ifdef B200_MMQ_TRACE
+            if (a.trace) {
+                long long * o = a.trace + ((size_t) blockIdx.y * gridDim.x + blockIdx.x) * 16;
+                o[4] = clock64() - t_start, o[5] = tw[0], o[6] = tw[1];
+            }
+#endif
         }
     } else {
         // ------------------------------------------------------------------------------------------ epilogue warps
         constexpr int CW = BN / (SH::EW / 4);                    // columns per warp
         const int q = warp & 3, half = (warp - 2) >> 2;          // TMEM lane quarter (hardware: warp id % 4), column half
         const int row = m0 + q * 32 + lane, col0 = half * CW;
-        float acc[CW];
+        __align__(8) float acc[CW];
 #pragma unroll
         for (int i = 0; i < CW; i++) acc[i] = 0.f;
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         for (int c = 0; c < nch; c++) {
             const int buf = c % NB, sb = c % SH::NSC;
-            mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1);
+            TW(0, mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1));
             const float *  sv  = sring + sb * SH::SC_FLTS;
             const float    sic = sv[q * 32 + lane];
             const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);   // warp-uniform: broadcast reads
-            mbar_wait(bar_tfull + 8 * buf, (c / NB) & 1);
+            TW(1, mbar_wait(bar_tfull + 8 * buf, (c / NB) & 1));
             tc_fence_after();
-#pragma unroll
-            for (int g = 0; g < CW / 32; g++) {
-                uint32_t r[32];
-                tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0 + g * 32, r);
-                tmem_ld_wait();
-                if (g == CW / 32 - 1) {                          // accumulator fully read: hand it back to the tensor core
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
-                }
-#pragma unroll
-                for (int i4 = 0; i4 < 8; i4++) {
-                    const float4 t = tp[g * 8 + i4];
-                    acc[g * 32 + 4 * i4 + 0] = fmaf((float) (int) r[4 * i4 + 0], sic * t.x, acc[g * 32 + 4 * i4 + 0]);
-                    acc[g * 32 + 4 * i4 + 1] = fmaf((float) (int) r[4 * i4 + 1], sic * t.y, acc[g * 32 + 4 * i4 + 1]);
-                    acc[g * 32 + 4 * i4 + 2] = fmaf((float) (int) r[4 * i4 + 2], sic * t.z, acc[g * 32 + 4 * i4 + 2]);
-                    acc[g * 32 + 4 * i4 + 3] = fmaf((float) (int) r[4 * i4 + 3], sic * t.w, acc[g * 32 + 4 * i4 + 3]);
-                }
-            }
+            epi_chunk<EPI, CW>(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0, tp, sic, acc,
+                               [&] { if (lane == 0) mbar_arrive(bar_tempty + 8 * buf); });
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);     // scale vectors consumed
         }
+#ifdef B200_MMQ_TRACE
+        const long long t_loop = clock64();
+#endif
         if (row < mrows) {
 #pragma unroll
             for (int i = 0; i < CW; i++) {
                 const int j = n0 + col0 + i;
                 if (j < a.n) {                                   // lanes = consecutive rows: coalesced
                     float * d = dstp + (int64_t) j * dstride + row;
-                    *d = a.accumulate ? acc[i] + *d : acc[i];
+                    if (a.ksplit > 1) atomicAdd(d, acc[i]);      // RED.ADD.F32: fire and forget
+                    else *d = a.accumulate ? acc[i] + *d : acc[i];
                 }
             }
         }
+#ifdef B200_MMQ_TRACE
+        if (a.trace && warp == 2 && lane == 0) {
+            long long * o = a.trace + ((size_t) blockIdx.y * gridDim.x + blockIdx.x) * 16;
+            o[8] = t_loop - t_start, o[9] = tw[0], o[10] = tw[1], o[11] = clock64() - t_loop;
+            unsigned long long g;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+            o[12] = (long long) g;
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
@@ -539,7 +683,7 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
         constexpr int CW = BN / 2;
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int row = m0 + q * 32 + lane, col0 = half * CW;
-        float acc[CW];
+        __align__(8) float acc[CW];
 #pragma unroll
         for (int i = 0; i < CW; i++) acc[i] = 0.f;
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
@@ -552,25 +696,8 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
             const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
             mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
             tc_fence_after();
-#pragma unroll
-            for (int g = 0; g < CW / 32; g++) {
-                uint32_t r[32];
-                tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0 + g * 32, r);
-                tmem_ld_wait();
-                if (g == CW / 32 - 1) {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_cluster(lte0 + 8 * buf);
-                }
-#pragma unroll
-                for (int i4 = 0; i4 < 8; i4++) {
-                    const float4 t = tp[g * 8 + i4];
-                    acc[g * 32 + 4 * i4 + 0] = fmaf((float) (int) r[4 * i4 + 0], sic * t.x, acc[g * 32 + 4 * i4 + 0]);
-                    acc[g * 32 + 4 * i4 + 1] = fmaf((float) (int) r[4 * i4 + 1], sic * t.y, acc[g * 32 + 4 * i4 + 1]);
-                    acc[g * 32 + 4 * i4 + 2] = fmaf((float) (int) r[4 * i4 + 2], sic * t.z, acc[g * 32 + 4 * i4 + 2]);
-                    acc[g * 32 + 4 * i4 + 3] = fmaf((float) (int) r[4 * i4 + 3], sic * t.w, acc[g * 32 + 4 * i4 + 3]);
-                }
-            }
+            epi_chunk<2, CW>(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0, tp, sic, acc,
+                             [&] { if (lane == 0) mbar_arrive_cluster(lte0 + 8 * buf); });
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);
         }
@@ -658,17 +785,32 @@ int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane,
 // workspace of the GEMM proper: quantized activations + their scales (+ slack for overhanging tiles)
 size_t mmq_workspace_bytes(int64_t n, int64_t k) { return mmq_act_bytes(n, k) + 2048; }
 
+template <int BN, int EPI>
+static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
+                             int mtiles, cudaStream_t stream);
+// epilogue flavour: B200_MMQ_EPI = 0 (I2FP), 1 (magic-number conversion), 2 (magic + packed fp32; default)
 template <int BN>
 static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
                          int mtiles, cudaStream_t stream) {
+    const char * e   = getenv("B200_MMQ_EPI");
+    const int    epi = e && *e ? atoi(e) : 2;
+    switch (epi) {
+        case 0: return launch_mmq_bn_epi<BN, 0>(mapA, mapB, a, mapAx, mtiles, stream);
+        case 1: return launch_mmq_bn_epi<BN, 1>(mapA, mapB, a, mapAx, mtiles, stream);
+        default: return launch_mmq_bn_epi<BN, 2>(mapA, mapB, a, mapAx, mtiles, stream);
+    }
+}
+template <int BN, int EPI>
+static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
+                             int mtiles, cudaStream_t stream) {
     static bool attr_set = false;
-    auto kern = k_mmq<BN>;
+    auto kern = k_mmq<BN, EPI>;
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_shape<BN>::SMEM));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) mtiles, (unsigned) ((a.n + BN - 1) / BN), 1);
+    cfg.gridDim          = dim3((unsigned) mtiles, (unsigned) ((a.n + BN - 1) / BN), (unsigned) (a.ksplit > 1 ? a.ksplit : 1));
     cfg.blockDim         = dim3(mmq_shape<BN>::THREADS, 1, 1);
     cfg.dynamicSmemBytes = mmq_shape<BN>::SMEM;
     cfg.stream           = stream;
@@ -676,7 +818,13 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a, mapAx));
+    mmq_kargs a2 = a;
+    a2.trace = nullptr;
+    if (a2.ksplit < 1) a2.ksplit = 1;
+#ifdef B200_MMQ_TRACE
+    if (const char * tp = getenv("B200_MMQ_TRACE_PTR")) a2.trace = (long long *) strtoull(tp, nullptr, 0);
+#endif
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a2, mapAx));
     note_launch();
     return B200_OK;
 }
@@ -704,6 +852,30 @@ static int launch_mmq_pair(const CUtensorMap & mapA, const CUtensorMap & mapB, c
     return B200_OK;
 }
 
+static int launch_quantize_x8(const float * x, int64_t x_stride, int8_t * Q, float * Tt, int64_t n, int64_t k, int64_t kp,
+                              int64_t npad, const mmq_zero & z, cudaStream_t stream) {
+    const int64_t warps = n * (kp / MMQ_KC);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim  = dim3((unsigned) ((warps + 7) / 8), 1, 1);
+    cfg.blockDim = dim3(256, 1, 1);
+    cfg.stream   = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8, x, x_stride, Q, Tt, n, k, kp, npad, z));
+    note_launch();
+    return B200_OK;
+}
+
+// split-K decision: two K halves when one would leave more than half of the SMs without a tile (B200_MMQ_KSPLIT=1/2 forces)
+static int mmq_ksplit(int64_t tiles, int64_t nch, int sm_count, bool allowed) {
+    const char * e = getenv("B200_MMQ_KSPLIT");
+    if (!allowed || nch < 4) return 1;
+    if (e && *e) return atoi(e) == 2 ? 2 : 1;
+    return tiles * 2 <= sm_count ? 2 : 1;
+}
+
 int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
     if (m == 0 || n == 0) return B200_OK;
@@ -716,20 +888,23 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
     const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
     int8_t * Q  = (int8_t *) workspace;
     float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
-    {
-        const int64_t warps = n * nch;
-        k_quantize_x8<<<(unsigned) ((warps + 7) / 8), 256, 0, stream>>>(x, x_stride, Q, Tt, n, k, kp, npad);
-        note_launch();
-        B200_CUDA_TRY(cudaGetLastError());
-    }
-    // tile width: 256 columns unless that leaves most SMs idle
+    // tile width: 256 columns (the tensor core takes ~120 clocks per instruction whether N is 128 or 256, see
+    // profiles/r01/mmq_trace_v1.log) unless n is small; shapes with few tiles split K in two instead of narrowing tiles
     const int64_t mt = (m + MMQ_BM - 1) / MMQ_BM;
     const char *  e  = getenv("B200_MMQ_BN");
-    int bn = e && *e ? atoi(e) : ((n <= 128 || mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
+    int bn = e && atoi(e) > 0 ? atoi(e) : (n <= 128 ? 128 : 256);
     // CTA pairs (tcgen05 cta_group::2): B200_MMQ_PAIR=1
     const char * pe = getenv("B200_MMQ_PAIR");
     const bool   pair = pe && atoi(pe) == 1 && n > 128 && mt >= 2;
     if (pair) bn = 256;
+    const bool can_split = !pair && mmq_nplanes(type) == 1 && m % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t) dst % 16 == 0;
+    const int  ksplit = mmq_ksplit(mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
+    {
+        mmq_zero z = {};
+        if (ksplit > 1) z.cnt = 1, z.p[0] = dst, z.stride[0] = dst_stride, z.m[0] = m;
+        const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
+        if (st != B200_OK) return st;
+    }
     CUtensorMap mapA, mapB;
     int st = make_map(&mapB, Q, n, kp, pair ? 128 : bn);
     if (st != B200_OK) return st;
@@ -742,6 +917,7 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
         a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
         a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
         a.accumulate = pl > 0;
+        a.ksplit = ksplit;
         a.nmat = 1;
         static const mmq_maps3 none = {};
         st = pair ? launch_mmq_pair(mapA, mapB, a, stream)
@@ -768,16 +944,22 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
     const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
     int8_t * Q  = (int8_t *) workspace;
     float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
-    {
-        const int64_t warps = n * nch;
-        k_quantize_x8<<<(unsigned) ((warps + 7) / 8), 256, 0, stream>>>(x, x_stride, Q, Tt, n, k, kp, npad);
-        note_launch();
-        B200_CUDA_TRY(cudaGetLastError());
-    }
     int64_t total_mt = 0;
-    for (int i = 0; i < nmat; i++) total_mt += (m[i] + MMQ_BM - 1) / MMQ_BM;
+    bool    can_split = nmat <= 4;
+    for (int i = 0; i < nmat; i++) {
+        total_mt += (m[i] + MMQ_BM - 1) / MMQ_BM;
+        can_split = can_split && m[i] % 4 == 0 && dst_stride[i] % 4 == 0 && (uintptr_t) dst[i] % 16 == 0;
+    }
     const char * e  = getenv("B200_MMQ_BN");
-    const int    bn = e && *e ? atoi(e) : ((n <= 128 || total_mt * ((n + 255) / 256) < sm_count) ? 128 : 256);
+    const int    bn = e && atoi(e) > 0 ? atoi(e) : (n <= 128 ? 128 : 256);
+    const int    ksplit = mmq_ksplit(total_mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
+    {
+        mmq_zero z = {};
+        if (ksplit > 1)
+            for (int i = 0; i < nmat; i++) z.p[z.cnt] = dst[i], z.stride[z.cnt] = dst_stride[i], z.m[z.cnt] = m[i], z.cnt++;
+        const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
+        if (st != B200_OK) return st;
+    }
     CUtensorMap mapB;
     int st = make_map(&mapB, Q, n, kp, bn);
     if (st != B200_OK) return st;
@@ -786,7 +968,7 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
         CUtensorMap mapA;
         mmq_maps3   mx = {};
         mmq_kargs   a  = {};
-        a.Tt = Tt, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.accumulate = 0, a.nmat = cnt;
+        a.Tt = Tt, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.accumulate = 0, a.nmat = cnt, a.ksplit = ksplit;
         int tiles = 0;
         for (int j = 0; j < cnt; j++) {
             const int64_t   mj = m[i0 + j];

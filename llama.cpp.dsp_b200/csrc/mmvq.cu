@@ -391,7 +391,8 @@ struct gemv_kargs {
     int64_t         x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
     int             world, rank;
     int64_t         row_offset;
-    int             dbg;          // profiling aid: 2 = skip the TMA loads
+    int             dbg;          // profiling aid: 2 = skip the TMA loads, 8 = skip the dot products,
+                                  // 32 = weight loads carry the L2 evict_first policy (experiment)
     unsigned long long * trace;   // profiling aid: 8 globaltimer stamps per CTA (tools/gemv_trace.py), else nullptr
 };
 __device__ __forceinline__ void trace_stamp(const gemv_kargs & a, int i) {
@@ -522,6 +523,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 
     if (warp == NW) {
         // ---------------------------------------------------------------------------------------- TMA + epilogue warp
+        const uint64_t policy = (a.dbg & 32) ? l2_policy_evict_first() : 0;
         auto issue = [&](int st, int slot) {  // all lanes call; stage st -> ring slot `slot` (= st % nst)
             const int      r0 = r_begin + st * V, nr = min(V, r_end - r0);
             const uint32_t dstb = sm_stage + slot * a.stage_bytes;
@@ -539,7 +541,8 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                     const uint64_t g0   = g & ~(uint64_t) 15;
                     const uint32_t span = (uint32_t) (((g + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
                     mbar_expect_tx(bar, span);
-                    tma_load_1d(dstb, (const void *) g0, span, bar);
+                    if (a.dbg & 32) tma_load_1d_hint(dstb, (const void *) g0, span, bar, policy);
+                    else tma_load_1d(dstb, (const void *) g0, span, bar);
                 }
             } else {  // strided rows: one bulk copy per row, lane i copies row i
                 uint32_t span = 0;
@@ -656,7 +659,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
             float out[NCOLS];
 #pragma unroll
             for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
-            if (v < nr) {                                       // warp-uniform
+            if (v < nr && !(a.dbg & 8)) {                       // warp-uniform (dbg 8: loads only)
                 const uint32_t ra = base + v * row_step + ((c0 + v * c1) & 15u);
                 unit_dot<TYPE, NCOLS>(ra, ugc, k32, u, out);
             }
@@ -709,6 +712,18 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 static int env_int(const char * name, int dflt) {
     const char * s = getenv(name);
     return s && *s ? atoi(s) : dflt;
+}
+
+// tools/gemv_trace.py, tools/layer_trace.py: B200_GEMV_TRACE_PTR = base pointer, one slab of 4096 x 8 stamps per GEMV
+// launch, in launch order across all kernel variants, B200_GEMV_TRACE_LAUNCHES slabs in all (0 rewinds the counter)
+static unsigned long long * next_trace_slab() {
+    static long long seq = 0;
+    const char * tp = getenv("B200_GEMV_TRACE_PTR");
+    if (!tp) return nullptr;
+    const long long cap = env_int("B200_GEMV_TRACE_LAUNCHES", 0);
+    if (cap == 0) seq = 0;
+    if (seq >= cap) return nullptr;
+    return (unsigned long long *) strtoull(tp, nullptr, 0) + (size_t) (seq++) * 4096 * 8;
 }
 
 struct gemv_plan {
@@ -823,11 +838,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.world = g.world, a.rank = g.rank, a.row_offset = g.row_offset;
     a.dbg = env_int("B200_GEMV_DEBUG", 0);
     a.trace = nullptr;
-    if (const char * tp = getenv("B200_GEMV_TRACE_PTR")) {      // tools/gemv_trace.py: base pointer, one slab per launch
-        static long long seq = 0;
-        const long long  cap = env_int("B200_GEMV_TRACE_LAUNCHES", 0);
-        if (seq < cap) a.trace = (unsigned long long *) strtoull(tp, nullptr, 0) + (size_t) (seq++) * 4096 * 8;
-    }
+    a.trace = next_trace_slab();
     gemv_peers peers = {};
     if (g.world > 1) {
         for (int r = 0; r < g.world && r < 16; r++) peers.dst[r] = g.peer_dst[r], peers.flag[r] = g.peer_flag[r];

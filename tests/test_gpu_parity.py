@@ -175,6 +175,29 @@ def test_mmq_prepared_plane(qmm, name, t, m, k, n):
     assert qref.nmse(qref.mul_mat(t, w, x, m, k, "f64"), got) < NMSE_HARNESS
 
 
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("m,k,n", [(512, 4096, 512), (300, 2048, 200), (128, 1280, 260)])
+def test_mmq_split_k_is_exact_and_deterministic(qmm, monkeypatch, name, t, m, k, n):
+    """few-tile shapes run as two K halves added with red.global.add onto a zeroed dst (B200_MMQ_KSPLIT=2 forces it;
+    m = 300 / an odd chunk count / two-plane Q8_0 exercise the fall-backs).  Same tight bound as the unsplit path vs the
+    plane restatement, and bit-identical from run to run (two addends onto zero commute)."""
+    rng = np.random.default_rng(m + k)
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    plane = qmm.build_plane(t, dev(w), m, k)
+    xd = dev(x)
+    monkeypatch.setenv("B200_MMQ_KSPLIT", "2")
+    out = torch.full((n, m), 7.0, device="cuda")           # stale contents must not leak into the sum
+    got = qmm.mul_mat_mmq(t, plane, xd, m, k, out=out).clone()
+    for _ in range(3):
+        out.fill_(-3.0)
+        assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k, out=out), got)
+    assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
+    monkeypatch.setenv("B200_MMQ_KSPLIT", "1")
+    one = qmm.mul_mat_mmq(t, plane, xd, m, k)
+    assert qref.nmse(one.cpu().numpy(), got.cpu().numpy()) < 1e-11
+
+
 @pytest.mark.parametrize("name,t", [("q4_0", qref.Q4_0), ("q8_0", qref.Q8_0)])
 def test_mmq_k_not_multiple_of_chunk(qmm, name, t):
     rng = np.random.default_rng(3)
