@@ -538,6 +538,215 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
     if (warp == 1) tmem_dealloc<NB * BN>(tmem);
 }
 
+// ------------------------------------------------------------------------------------------------ persistent GEMM kernel
+// One CTA per SM walks a host-made list of work items (item i -> CTA i % gridDim.x).  Items are 128 x 256 tiles in
+// n-fastest order (the CTAs running at one time share a few weight tiles through L2); when the last round would give
+// fewer than half of the CTAs a tile, those tiles are cut into 128 x 128 halves so that the round costs half as much
+// (gate+up of an 8B layer at n = 512: 448 tiles on 148 SMs = 3 rounds + 4 tiles -> 3 rounds + 8 half tiles).
+// Against one CTA per tile this removes, per round, the barrier/TMEM set-up, the pipeline fill and most of the 128 KB
+// result store (~6.5 us of a ~25 us round, profiles/r01/mmq_trace_v1.log): the producer and the MMA warp run ahead into
+// the next item while the epilogue warps still store the previous one.
+// B tiles are always loaded as 128-row boxes (two per k-block for a 256-wide item), so one tensor map serves both widths;
+// the UMMA N comes from a per-item instruction descriptor; TMEM holds two 256-column accumulator buffers.
+struct mmq_pargs {
+    int ntn;       // 256-wide n-tiles per m-tile
+    int mtiles;    // m-tiles of all matrices of the launch
+    int raster;    // 0: consecutive items walk n first, 1: m first (B200_MMQ_RASTER)
+    int n_main;    // 128 x 256 items
+    int n_items;   // n_main + 128 x 128 tail items
+};
+struct mmq_pshape {
+    static constexpr int NS      = 4;
+    static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // 16 KB
+    static constexpr int B_BYTES = 256 * MMQ_BK;                      // 32 KB (two 128-row boxes)
+    static constexpr int STAGE   = A_BYTES + B_BYTES;
+    static constexpr int NSC     = 8;
+    static constexpr int SC_FLTS = MMQ_BM + 256;
+    static constexpr int SMEM    = NS * STAGE + NSC * SC_FLTS * 4 + 1024;
+    static constexpr int EW      = 16;
+    static constexpr int THREADS = (2 + EW) * 32;
+    static constexpr int NB      = 2;
+};
+struct mmq_item {
+    int mt, n0, bn;    // global m-tile (over all matrices of the launch), first column, width
+};
+__device__ __forceinline__ mmq_item mmq_item_of(int it, const mmq_pargs & p) {
+    int t, half = 0, bn = 256;
+    if (it < p.n_main) t = it;
+    else t = p.n_main + ((it - p.n_main) >> 1), half = (it - p.n_main) & 1, bn = 128;
+    mmq_item r;
+    int      nt;
+    if (p.raster) nt = t / p.mtiles, r.mt = t - nt * p.mtiles;
+    else r.mt = t / p.ntn, nt = t - r.mt * p.ntn;
+    r.n0 = nt * 256 + half * 128;
+    r.bn = bn;
+    return r;
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_constant__ CUtensorMap mapA,
+                                                const __grid_constant__ CUtensorMap mapB, const mmq_kargs a,
+                                                const __grid_constant__ mmq_maps3 mapAx, const mmq_pargs p) {
+    using SH = mmq_pshape;
+    constexpr int NS = SH::NS, NB = SH::NB, NSC = SH::NSC;
+    extern __shared__ uint8_t mmq_smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * NS + 2 * NB + 2 * NSC];
+    __shared__ uint32_t tmem_slot;
+
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
+                   bar_tempty = bar_tfull + 8 * NB, bar_sfull = bar_tempty + 8 * NB, bar_sempty = bar_sfull + 8 * NSC;
+    const uint32_t scales = tiles + NS * SH::STAGE;
+    const int      nch = a.nch;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
+        for (int b = 0; b < NB; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, SH::EW);
+        for (int b = 0; b < NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, SH::EW);
+        mbar_fence_init();
+        prefetch_tmap(&mapA);
+        prefetch_tmap(&mapB);
+    }
+    if (warp == 1) tmem_alloc<512>(smem_u32(&tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();                                                 // activations come from the quantizer kernel before us
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            uint32_t st = 0, st_ph = 0, sc = 0, sc_ph = 0;      // stage / scale-slot cursors with their phase bits
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                const mmq_item I = mmq_item_of(it, p);
+                const CUtensorMap * pA = &mapA;
+                const float *       S  = a.S;
+                int                 mpad = a.mpad, tile = I.mt;
+                if (a.nmat > 1) {
+                    int first = 0;
+#pragma unroll
+                    for (int i = 0; i < 3; i++)
+                        if (i + 1 < a.nmat && I.mt >= a.tile0[i]) pA = &mapAx.m[i], S = a.Sx[i], mpad = a.mpadx[i], first = a.tile0[i];
+                    tile -= first;
+                }
+                const int      m0 = tile * MMQ_BM;
+                const uint32_t stage_tx = SH::A_BYTES + (uint32_t) I.bn * MMQ_BK, scale_tx = (MMQ_BM + (uint32_t) I.bn) * 4;
+                for (int c = 0; c < nch; c++) {
+                    mbar_wait(bar_sempty + 8 * sc, sc_ph ^ 1);  // this chunk's scale vectors, ahead of its tiles
+                    const uint32_t sd = scales + sc * SH::SC_FLTS * 4;
+                    mbar_expect_tx(bar_sfull + 8 * sc, scale_tx);
+                    tma_load_1d(sd, S + (int64_t) c * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * sc);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + I.n0, I.bn * 4, bar_sfull + 8 * sc);
+                    if (++sc == NSC) sc = 0, sc_ph ^= 1;
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        mbar_wait(bar_empty + 8 * st, st_ph ^ 1);
+                        const uint32_t sa = tiles + st * SH::STAGE, sb = sa + SH::A_BYTES;
+                        mbar_expect_tx(bar_full + 8 * st, stage_tx);
+                        tma_load_2d(sa, pA, (2 * c + h) * MMQ_BK, m0, bar_full + 8 * st);
+                        tma_load_2d(sb, &mapB, (2 * c + h) * MMQ_BK, I.n0, bar_full + 8 * st);
+                        if (I.bn == 256) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (2 * c + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
+                        if (++st == NS) st = 0, st_ph ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            uint32_t st = 0, st_ph = 0, buf = 0, buf_ph = 0;
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                const uint32_t idesc = it < p.n_main ? idesc_i8(MMQ_BM, 256) : idesc_i8(MMQ_BM, 128);
+                for (int c = 0; c < nch; c++) {
+                    mbar_wait(bar_tempty + 8 * buf, buf_ph ^ 1);   // epilogue has drained this accumulator
+                    tc_fence_after();
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        mbar_wait(bar_full + 8 * st, st_ph);
+                        tc_fence_after();
+                        const uint32_t sa = tiles + st * SH::STAGE, sb = sa + SH::A_BYTES;
+                        const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
+#pragma unroll
+                        for (int kk = 0; kk < MMQ_BK / 32; kk++)
+                            mma_i8(tmem + buf * 256, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) ((h | kk) != 0));
+                        mma_commit(bar_empty + 8 * st);
+                        if (++st == NS) st = 0, st_ph ^= 1;
+                    }
+                    mma_commit(bar_tfull + 8 * buf);
+                    if (++buf == NB) buf = 0, buf_ph ^= 1;
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------------------------------ epilogue warps
+        const int q = warp & 3, part = (warp - 2) >> 2;          // TMEM lane quarter (warp id % 4), column part 0..3
+        const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
+        uint32_t sc = 0, sc_ph = 0, buf = 0, buf_ph = 0;
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+            const mmq_item I = mmq_item_of(it, p);
+            float *  dstp = a.dst;
+            int64_t  dstride = a.dst_stride;
+            int      mrows = a.m, tile = I.mt;
+            if (a.nmat > 1) {
+                int first = 0;
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+                    if (i + 1 < a.nmat && I.mt >= a.tile0[i]) dstp = a.dstx[i], dstride = a.dst_stridex[i], mrows = a.mx[i], first = a.tile0[i];
+                tile -= first;
+            }
+            const int ncw = I.bn >> 2, ng = ncw >> 4;            // columns per warp (64 / 32), 16-column groups (4 / 2)
+            const int row = tile * MMQ_BM + q * 32 + lane, col0 = part * ncw;
+            __align__(8) float acc[64];
+#pragma unroll
+            for (int i = 0; i < 64; i++) acc[i] = 0.f;
+            for (int c = 0; c < nch; c++) {
+                mbar_wait(bar_sfull + 8 * sc, sc_ph);
+                const float *  sv  = sring + sc * SH::SC_FLTS;
+                const float    sic = sv[q * 32 + lane];
+                const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
+                mbar_wait(bar_tfull + 8 * buf, buf_ph);
+                tc_fence_after();
+                const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + buf * 256 + col0;
+                // (one 16-column load in flight per warp: with 64 accumulators a second load buffer does not fit the
+                // 96 registers that 18 warps leave per thread; the other 3-4 warps of the scheduler cover the latency)
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    if (g < ng) {                                // warp-uniform
+                        uint32_t r[16];
+                        tmem_ldw(tbase + g * 16, r);
+                        tmem_ld_wait();
+                        if (g + 1 == ng) {                       // accumulator fully read: hand it back to the tensor core
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                        }
+                        epi_accumulate<EPI, 16>(r, tp + g * 4, sic, acc + g * 16);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_sempty + 8 * sc);
+                if (++sc == NSC) sc = 0, sc_ph ^= 1;
+                if (++buf == NB) buf = 0, buf_ph ^= 1;
+            }
+            if (row < mrows) {
+                const int jn = min(ncw, a.n - (I.n0 + col0));    // columns of this warp inside the matrix
+                float *   d  = dstp + (int64_t) (I.n0 + col0) * dstride + row;
+#pragma unroll
+                for (int i = 0; i < 64; i++) {                   // lanes = consecutive rows: coalesced
+                    if (i < jn) *d = a.accumulate ? acc[i] + *d : acc[i];
+                    d += dstride;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tmem);
+}
+
 // ------------------------------------------------------------------------------------------------ CTA-pair GEMM kernel
 // The same pipeline with tcgen05.mma.cta_group::2: two CTAs on neighbouring SMs (a cluster of 2 along m) execute ONE
 // M256 x N256 x K32 instruction per step.  Each CTA stages its own 128 weight rows and only HALF of the activation tile
@@ -736,6 +945,11 @@ static encode_tiled_fn get_encode_tiled() {
     return fn;
 }
 
+static int env_flag(const char * name, int dflt) {
+    const char * e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+
 // row-major int8 matrix [rows][kp] -> tiles of box_rows x 128 bytes, 128-byte swizzle, zero fill outside
 static int make_map(CUtensorMap * map, const void * base, int64_t rows, int64_t kp, int box_rows) {
     encode_tiled_fn enc = get_encode_tiled();
@@ -829,6 +1043,41 @@ static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB,
     return B200_OK;
 }
 
+// persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
+static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
+                                 const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
+    static bool attr_set = false;
+    auto kern = k_mmq_p<2>;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_pshape::SMEM));
+        attr_set = true;
+    }
+    mmq_pargs p;
+    p.ntn = (a.n + 255) / 256;
+    p.mtiles = mtiles;
+    p.raster = env_flag("B200_MMQ_RASTER", 0);
+    const int tiles = mtiles * p.ntn;
+    const int G     = tiles < sm_count ? tiles : sm_count;
+    const int rem   = tiles % G;
+    const bool halves = tiles > G && rem > 0 && rem * 2 <= G && env_flag("B200_MMQ_TAIL_HALVES", 1);
+    p.n_main  = halves ? tiles - rem : tiles;
+    p.n_items = p.n_main + (halves ? 2 * rem : 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) G, 1, 1);
+    cfg.blockDim         = dim3(mmq_pshape::THREADS, 1, 1);
+    cfg.dynamicSmemBytes = mmq_pshape::SMEM;
+    cfg.stream           = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    mmq_kargs a2 = a;
+    a2.trace = nullptr, a2.ksplit = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB128, a2, mapAx, p));
+    note_launch();
+    return B200_OK;
+}
+
 static int launch_mmq_pair(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
@@ -905,8 +1154,9 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
         const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
         if (st != B200_OK) return st;
     }
+    const bool persist = !pair && ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1);
     CUtensorMap mapA, mapB;
-    int st = make_map(&mapB, Q, n, kp, pair ? 128 : bn);
+    int st = make_map(&mapB, Q, n, kp, (pair || persist) ? 128 : bn);
     if (st != B200_OK) return st;
     for (int pl = 0; pl < mmq_nplanes(type); pl++) {
         const uint8_t * pb = (const uint8_t *) plane + (size_t) pl * mmq_plane_bytes(m, k);
@@ -921,6 +1171,7 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
         a.nmat = 1;
         static const mmq_maps3 none = {};
         st = pair ? launch_mmq_pair(mapA, mapB, a, stream)
+                  : persist ? launch_mmq_persistent(mapA, mapB, a, none, (int) mt, sm_count, stream)
                   : bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, none, (int) mt, stream)
                               : launch_mmq_bn<128>(mapA, mapB, a, none, (int) mt, stream);
         if (st != B200_OK) return st;
@@ -960,8 +1211,9 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
         const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
         if (st != B200_OK) return st;
     }
+    const bool persist = ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1);
     CUtensorMap mapB;
-    int st = make_map(&mapB, Q, n, kp, bn);
+    int st = make_map(&mapB, Q, n, kp, persist ? 128 : bn);
     if (st != B200_OK) return st;
     for (int i0 = 0; i0 < nmat; i0 += 4) {
         const int cnt = nmat - i0 < 4 ? nmat - i0 : 4;
@@ -985,7 +1237,9 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
             tiles += (int) ((mj + MMQ_BM - 1) / MMQ_BM);
         }
         if (tiles == 0) continue;
-        st = bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, tiles, stream) : launch_mmq_bn<128>(mapA, mapB, a, mx, tiles, stream);
+        st = persist ? launch_mmq_persistent(mapA, mapB, a, mx, tiles, sm_count, stream)
+           : bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, tiles, stream)
+                       : launch_mmq_bn<128>(mapA, mapB, a, mx, tiles, stream);
         if (st != B200_OK) return st;
     }
     return B200_OK;

@@ -198,6 +198,25 @@ def test_mmq_split_k_is_exact_and_deterministic(qmm, monkeypatch, name, t, m, k,
     assert qref.nmse(one.cpu().numpy(), got.cpu().numpy()) < 1e-11
 
 
+@pytest.mark.parametrize("name,t", [("q4_K", qref.Q4_K), ("q8_0", qref.Q8_0), ("q6_K", qref.Q6_K)])
+@pytest.mark.parametrize("m,k,n", [(9700, 512, 300), (19000, 256, 512), (2500, 768, 1000)])
+def test_mmq_persistent_schedule(qmm, monkeypatch, name, t, m, k, n):
+    """more tiles than SMs: the persistent kernel walks several items per CTA, the short last round is cut into
+    128 x 128 halves (B200_MMQ_TAIL_HALVES=0 keeps whole tiles), n and m are ragged, Q8_0 takes the accumulate pass.
+    Both schedules and the one-CTA-per-tile kernel (B200_MMQ_PERSIST=0) must give the same bits."""
+    rng = np.random.default_rng(m + n)
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    plane = qmm.build_plane(t, dev(w), m, k)
+    xd = dev(x)
+    got = qmm.mul_mat_mmq(t, plane, xd, m, k).clone()
+    assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
+    monkeypatch.setenv("B200_MMQ_TAIL_HALVES", "0")
+    assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
+    monkeypatch.setenv("B200_MMQ_PERSIST", "0")
+    assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
+
+
 @pytest.mark.parametrize("name,t", [("q4_0", qref.Q4_0), ("q8_0", qref.Q8_0)])
 def test_mmq_k_not_multiple_of_chunk(qmm, name, t):
     rng = np.random.default_rng(3)

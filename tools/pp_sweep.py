@@ -70,17 +70,25 @@ def main():
             for _ in range(2):
                 g.replay()
             torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            for _ in range(8):
-                g.replay()
-            e1.record(stream)
-            torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 8
+            reps = int(os.environ.get("REPS", "8"))
+            with bench.ClockSampler(0) as clk:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(reps):
+                    g.replay()
+                e1.record(stream)
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            try:
+                watts = clk.nv.nvmlDeviceGetPowerUsage(clk.h) / 1e3
+            except Exception:  # noqa: BLE001
+                watts = float("nan")
+            cs = clk.summary()
+            clocks = "sm %s MHz (min %s) %s %.0f W" % (cs["sm_mhz"], min(clk.samples) if clk.samples else None, cs["reasons"], watts)
         same = "ref" if ref is None else ("bit-identical" if torch.equal(res, ref) else "DIFFERS max %g" % float((res - ref).abs().max()))
         if ref is None:
             ref = res
-        print("%-50s %7.3f ms  %8.0f tok/s  %7.1f TOP/s  [%s]" % (cfg, ms, npp * 1e3 / ms, flops / ms / 1e9, same), flush=True)
+        print("%-50s %7.3f ms  %8.0f tok/s  %7.1f TOP/s  [%s]  %s" % (cfg, ms, npp * 1e3 / ms, flops / ms / 1e9, same, clocks), flush=True)
         del g
 
 
