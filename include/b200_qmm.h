@@ -165,6 +165,9 @@ B200_API int    b200_mul_mat_mmq_multi(int nmat, const int * types, const void *
                                        size_t workspace_bytes, b200_stream_t stream);
 /* smallest n that b200_mul_mat sends to the tensor-core path (MMVQ_MAX_BATCH_SIZE + 1, ggml-cuda/mmvq.cuh:3) */
 B200_API int    b200_mmq_min_batch(void);
+/* elements of k that share one scale on the tensor-core path (plane and activation quantization granularity; a
+ * build-time constant, 256 or 512): what a restatement of the path's arithmetic has to use (tests/qref.py:mul_mat_plane) */
+B200_API int    b200_mmq_chunk(void);
 
 /*
  * Same product with HOST activations and a HOST result: the activations are copied host->device, the matmul runs, and

@@ -174,6 +174,7 @@ size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
 }
 
 int    b200_mmq_min_batch(void) { return mmq_min_batch(); }
+int    b200_mmq_chunk(void) { return mmq_chunk(); }
 size_t b200_mmq_plane_size(int type, int64_t m, int64_t k) {
     if (!weight_type(type) || m < 0 || k < 0 || k % blck_of(type) != 0) return 0;
     return mmq_nplanes(type) * mmq_plane_bytes(m, k);

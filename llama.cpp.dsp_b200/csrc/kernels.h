@@ -64,6 +64,7 @@ int    launch_gemv(const gemv_args & a, cudaStream_t stream);
 
 // ---- batched matmul on tcgen05 (mmq.cu): int8 "prefill plane" of a weight tensor + the GEMM that consumes it
 size_t mmq_plane_bytes(int64_t m, int64_t k);
+int    mmq_chunk();   // elements of k per scale (build-time: 256 or 512)
 size_t mmq_workspace_bytes(int64_t n, int64_t k);
 // several single-plane matrices of one k against the same activations: one activation quantizer, shared GEMM launches
 int    launch_mmq_multi(int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,

@@ -31,10 +31,20 @@
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ layouts
-constexpr int MMQ_KC = 256;   // scale granularity along k (one TMEM accumulation chunk)
+#ifndef B200_MMQ_KC
+#define B200_MMQ_KC 512
+#endif
+constexpr int MMQ_KC = B200_MMQ_KC;   // scale granularity along k (one TMEM accumulation chunk): 256 or 512
 constexpr int MMQ_BM = 128;   // rows of W per CTA tile (= TMEM lanes)
 constexpr int MMQ_BK = 128;   // int8 elements per shared-memory stage row (= one 128-byte swizzle atom)
+constexpr int MMQ_KBC = MMQ_KC / MMQ_BK;   // k-blocks (shared-memory stages) per chunk
+constexpr int MMQ_G32 = MMQ_KC / 32;       // 32-element groups per chunk
+static_assert(MMQ_KC == 256 || MMQ_KC == 512, "chunk");
+// epilogue flavour the chunk size allows: the magic-number conversion is exact for |D| < 2^22 = 256 * 127 * 127 + ...;
+// a 512-chunk can exceed that, so it converts with I2FP (half as many conversions per weight as at 256 anyway)
+constexpr int MMQ_EPI_DEFAULT = MMQ_KC > 256 ? 0 : 2;
 
+int mmq_chunk() { return MMQ_KC; }
 static inline int64_t mmq_kpad(int64_t k) { return (k + MMQ_KC - 1) / MMQ_KC * MMQ_KC; }
 static inline size_t  align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
@@ -77,7 +87,7 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
         for (int i = 0; i < 32; i++) v[i] = 0.f;
     }
     if (RESID && in) {
-        const float    s0 = S0[(gi / 8) * mpad + row];
+        const float    s0 = S0[(gi / MMQ_G32) * mpad + row];
         const int8_t * p0 = P0 + row * kp + gi * 32;
 #pragma unroll
         for (int i = 0; i < 32; i++) v[i] = __fsub_rn(v[i], __fmul_rn(s0, (float) p0[i]));
@@ -88,6 +98,7 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    if (MMQ_G32 == 16) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 8));
     if (!in) return;
     const float s  = amax / 127.0f;
     const float is = s > 0.f ? 1.0f / s : 0.f;
@@ -102,7 +113,7 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
     uint4 * dst = reinterpret_cast<uint4 *>(P + row * kp + gi * 32);
     dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
     dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
-    if ((gi & 7) == 0) S[(gi / 8) * mpad + row] = s;
+    if ((gi % MMQ_G32) == 0) S[(gi / MMQ_G32) * mpad + row] = s;
 }
 
 // ------------------------------------------------------------------------------------------------ activation quantizer
@@ -117,7 +128,7 @@ struct mmq_zero {
 };
 __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ x, int64_t x_stride, int8_t * __restrict__ Q,
                                                      float * __restrict__ Tt, int64_t n, int64_t k, int64_t kp,
-                                                     int64_t npad, const mmq_zero z) {
+                                                     int64_t npad, const mmq_zero z, bool vec) {
     pdl_launch_dependents();   // the GEMM behind us sets up its barriers / TMEM and prefetches its tensor maps meanwhile
     pdl_wait();                // x comes from the previous kernel, and dst may still be read by it
     if (z.cnt) {
@@ -136,26 +147,37 @@ __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ 
     const int64_t nch  = kp / MMQ_KC;
     if (wid >= n * nch) return;
     const int64_t j = wid / nch, c = wid % nch;
-    const int64_t e0 = c * MMQ_KC + lane * 8;
-    float v[8];
+    constexpr int PL = MMQ_KC / 32;                             // elements per lane: 8 or 16
+    const int64_t e0 = c * MMQ_KC + lane * PL;
+    float v[PL];
+    const float * xr = x + j * x_stride + e0;
+    if (vec && e0 + PL <= k) {                                  // 16-byte loads (x and its row stride 16-byte aligned)
 #pragma unroll
-    for (int i = 0; i < 8; i++) v[i] = e0 + i < k ? x[j * x_stride + e0 + i] : 0.f;
+        for (int i = 0; i < PL / 4; i++) {
+            const float4 f = __ldg(reinterpret_cast<const float4 *>(xr) + i);
+            v[4 * i] = f.x, v[4 * i + 1] = f.y, v[4 * i + 2] = f.z, v[4 * i + 3] = f.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < PL; i++) v[i] = e0 + i < k ? xr[i] : 0.f;
+    }
     float amax = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+    for (int i = 0; i < PL; i++) amax = fmaxf(amax, fabsf(v[i]));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     const float t  = amax / 127.0f;
     const float it = t > 0.f ? 1.0f / t : 0.f;
-    uint32_t o2[2];
+    uint32_t o2[PL / 4];
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
+    for (int h = 0; h < PL / 4; h++) {
         const int a = __float2int_rn(v[4 * h] * it), b = __float2int_rn(v[4 * h + 1] * it);
         const int cc = __float2int_rn(v[4 * h + 2] * it), d = __float2int_rn(v[4 * h + 3] * it);
         o2[h] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (cc & 0xff) << 16) |
                 ((uint32_t) (d & 0xff) << 24);
     }
-    *reinterpret_cast<uint2 *>(Q + j * kp + e0) = make_uint2(o2[0], o2[1]);
+    if (PL == 8) *reinterpret_cast<uint2 *>(Q + j * kp + e0) = make_uint2(o2[0], o2[1]);
+    else *reinterpret_cast<uint4 *>(Q + j * kp + e0) = make_uint4(o2[0], o2[1], o2[PL / 4 - 2], o2[PL / 4 - 1]);
     if (lane == 0) Tt[c * npad + j] = t;
 }
 
@@ -334,6 +356,8 @@ struct mmq_kargs {
     int           accumulate;   // dst += result (second plane of a two-plane weight)
     int           ksplit;       // 1, or 2: grid.z halves of the chunk range, results added with red.global.add onto a
                                 // zeroed dst (few-tile shapes: m = 4096 at n = 512 fills 64 of 148 SMs otherwise)
+    int           dbg;          // experiments (B200_MMQ_DEBUG): 1 = persistent kernel skips the second B box (wrong results,
+                                // 2/3 of the L2->SM traffic), 2 = every item reads the A tile of m-tile 0
     long long *   trace;        // -DB200_MMQ_TRACE builds only: 16 clock counters per CTA (tools/mmq_trace.py), else unused
     // several weight matrices against the same activations in one launch (q/k/v, gate/up): the grid's x dimension runs
     // over the m-tiles of all of them; matrix i >= 1 starts at tile tile0[i-1] and is described by the x-fields
@@ -411,7 +435,7 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
     const int m0 = tile * MMQ_BM, n0 = blockIdx.y * BN;
     // this CTA's chunk range [cb, cb + nch): everything below counts chunks and k-blocks locally
     const int cper = (a.nch + a.ksplit - 1) / a.ksplit, cb = (int) blockIdx.z * cper;
-    const int nch = min(cper, a.nch - cb), nkb = 2 * nch;
+    const int nch = min(cper, a.nch - cb), nkb = MMQ_KBC * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
@@ -437,8 +461,8 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             for (int kb = 0; kb < nkb; kb++) {
-                if ((kb & 1) == 0) {                             // this chunk's scale vectors, ahead of its tiles
-                    const int c = kb >> 1, b = c % SH::NSC;
+                if ((kb % MMQ_KBC) == 0) {                       // this chunk's scale vectors, ahead of its tiles
+                    const int c = kb / MMQ_KBC, b = c % SH::NSC;
                     TW(0, mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1));
                     const uint32_t sd = scales + b * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
@@ -449,8 +473,8 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
                 TW(1, mbar_wait(bar_empty + 8 * s, ph ^ 1));
                 const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
                 mbar_expect_tx(bar_full + 8 * s, SH::STAGE);
-                tma_load_2d(sa, pA, (2 * cb + kb) * MMQ_BK, m0, bar_full + 8 * s);
-                tma_load_2d(sb, &mapB, (2 * cb + kb) * MMQ_BK, n0, bar_full + 8 * s);
+                tma_load_2d(sa, pA, (MMQ_KBC * cb + kb) * MMQ_BK, m0, bar_full + 8 * s);
+                tma_load_2d(sb, &mapB, (MMQ_KBC * cb + kb) * MMQ_BK, n0, bar_full + 8 * s);
             }
 #ifdef B200_MMQ_TRACE
             if (a.trace) {
@@ -467,8 +491,8 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
                 const int buf = c % NB;
                 TW(0, mbar_wait(bar_tempty + 8 * buf, ((c / NB) & 1) ^ 1));   // epilogue has drained this accumulator
                 tc_fence_after();
-                for (int h = 0; h < 2; h++) {
-                    const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
+                for (int h = 0; h < MMQ_KBC; h++) {
+                    const int kb = MMQ_KBC * c + h, s = kb % NS, ph = (kb / NS) & 1;
                     TW(1, mbar_wait(bar_full + 8 * s, ph));
                     tc_fence_after();
                     const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
@@ -616,6 +640,10 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
     pdl_launch_dependents();
     pdl_wait();                                                 // activations come from the quantizer kernel before us
 
+#ifdef B200_MMQ_TRACE
+    long long tw[4] = {0, 0, 0, 0};
+    const long long t_start = clock64();
+#endif
     if (warp == 0) {
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
@@ -632,27 +660,34 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                         if (i + 1 < a.nmat && I.mt >= a.tile0[i]) pA = &mapAx.m[i], S = a.Sx[i], mpad = a.mpadx[i], first = a.tile0[i];
                     tile -= first;
                 }
-                const int      m0 = tile * MMQ_BM;
-                const uint32_t stage_tx = SH::A_BYTES + (uint32_t) I.bn * MMQ_BK, scale_tx = (MMQ_BM + (uint32_t) I.bn) * 4;
+                const int      m0 = (a.dbg & 2) ? 0 : tile * MMQ_BM;
+                const bool     two = I.bn == 256 && !(a.dbg & 1);
+                const uint32_t stage_tx = SH::A_BYTES + (two ? 256u : 128u) * MMQ_BK, scale_tx = (MMQ_BM + (uint32_t) I.bn) * 4;
                 for (int c = 0; c < nch; c++) {
-                    mbar_wait(bar_sempty + 8 * sc, sc_ph ^ 1);  // this chunk's scale vectors, ahead of its tiles
+                    TW(0, mbar_wait(bar_sempty + 8 * sc, sc_ph ^ 1));  // this chunk's scale vectors, ahead of its tiles
                     const uint32_t sd = scales + sc * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * sc, scale_tx);
                     tma_load_1d(sd, S + (int64_t) c * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * sc);
                     tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + I.n0, I.bn * 4, bar_sfull + 8 * sc);
                     if (++sc == NSC) sc = 0, sc_ph ^= 1;
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        mbar_wait(bar_empty + 8 * st, st_ph ^ 1);
+                    for (int h = 0; h < MMQ_KBC; h++) {
+                        TW(1, mbar_wait(bar_empty + 8 * st, st_ph ^ 1));
                         const uint32_t sa = tiles + st * SH::STAGE, sb = sa + SH::A_BYTES;
                         mbar_expect_tx(bar_full + 8 * st, stage_tx);
-                        tma_load_2d(sa, pA, (2 * c + h) * MMQ_BK, m0, bar_full + 8 * st);
-                        tma_load_2d(sb, &mapB, (2 * c + h) * MMQ_BK, I.n0, bar_full + 8 * st);
-                        if (I.bn == 256) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (2 * c + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
+                        tma_load_2d(sa, pA, (MMQ_KBC * c + h) * MMQ_BK, m0, bar_full + 8 * st);
+                        tma_load_2d(sb, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0, bar_full + 8 * st);
+                        if (two) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
                         if (++st == NS) st = 0, st_ph ^= 1;
                     }
                 }
             }
+#ifdef B200_MMQ_TRACE
+            if (a.trace) {
+                long long * o = a.trace + (size_t) blockIdx.x * 16;
+                o[0] = clock64() - t_start, o[1] = tw[0], o[2] = tw[1];
+            }
+#endif
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------------------------------ MMA issuer
@@ -661,11 +696,11 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
             for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
                 const uint32_t idesc = it < p.n_main ? idesc_i8(MMQ_BM, 256) : idesc_i8(MMQ_BM, 128);
                 for (int c = 0; c < nch; c++) {
-                    mbar_wait(bar_tempty + 8 * buf, buf_ph ^ 1);   // epilogue has drained this accumulator
+                    TW(0, mbar_wait(bar_tempty + 8 * buf, buf_ph ^ 1));   // epilogue has drained this accumulator
                     tc_fence_after();
 #pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        mbar_wait(bar_full + 8 * st, st_ph);
+                    for (int h = 0; h < MMQ_KBC; h++) {
+                        TW(1, mbar_wait(bar_full + 8 * st, st_ph));
                         tc_fence_after();
                         const uint32_t sa = tiles + st * SH::STAGE, sb = sa + SH::A_BYTES;
                         const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
@@ -679,6 +714,12 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                     if (++buf == NB) buf = 0, buf_ph ^= 1;
                 }
             }
+#ifdef B200_MMQ_TRACE
+            if (a.trace) {
+                long long * o = a.trace + (size_t) blockIdx.x * 16;
+                o[4] = clock64() - t_start, o[5] = tw[0], o[6] = tw[1];
+            }
+#endif
         }
     } else {
         // ------------------------------------------------------------------------------------------ epilogue warps
@@ -703,11 +744,11 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
 #pragma unroll
             for (int i = 0; i < 64; i++) acc[i] = 0.f;
             for (int c = 0; c < nch; c++) {
-                mbar_wait(bar_sfull + 8 * sc, sc_ph);
+                TW(0, mbar_wait(bar_sfull + 8 * sc, sc_ph));
                 const float *  sv  = sring + sc * SH::SC_FLTS;
                 const float    sic = sv[q * 32 + lane];
                 const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
-                mbar_wait(bar_tfull + 8 * buf, buf_ph);
+                TW(1, mbar_wait(bar_tfull + 8 * buf, buf_ph));
                 tc_fence_after();
                 const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + buf * 256 + col0;
                 // (one 16-column load in flight per warp: with 64 accumulators a second load buffer does not fit the
@@ -731,6 +772,9 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 if (++sc == NSC) sc = 0, sc_ph ^= 1;
                 if (++buf == NB) buf = 0, buf_ph ^= 1;
             }
+#ifdef B200_MMQ_TRACE
+            const long long t_st = clock64();
+#endif
             if (row < mrows) {
                 const int jn = min(ncw, a.n - (I.n0 + col0));    // columns of this warp inside the matrix
                 float *   d  = dstp + (int64_t) (I.n0 + col0) * dstride + row;
@@ -740,7 +784,19 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                     d += dstride;
                 }
             }
+#ifdef B200_MMQ_TRACE
+            tw[2] += clock64() - t_st;
+#endif
         }
+#ifdef B200_MMQ_TRACE
+        if (a.trace && warp == 2 && lane == 0) {
+            long long * o = a.trace + (size_t) blockIdx.x * 16;
+            o[8] = clock64() - t_start - tw[2], o[9] = tw[0], o[10] = tw[1], o[11] = tw[2];
+            unsigned long long g;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+            o[12] = (long long) g;
+        }
+#endif
     }
     tc_fence_before();
     __syncthreads();
@@ -824,7 +880,7 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
     const bool     leader = crank == 0;
     const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;   // blockIdx.x = 2 * pair + rank: my own 128 rows
     const int ms0 = min(m0, a.mpad - MMQ_BM);
-    const int nch = a.nch, nkb = 2 * nch;
+    const int nch = a.nch, nkb = MMQ_KBC * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 2), mbar_init(bar_empty + 8 * s, 1);
@@ -847,8 +903,8 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
         // ------------------------------------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
             for (int kb = 0; kb < nkb; kb++) {
-                if ((kb & 1) == 0) {
-                    const int c = kb >> 1, b = c % SH::NSC;
+                if ((kb % MMQ_KBC) == 0) {
+                    const int c = kb / MMQ_KBC, b = c % SH::NSC;
                     mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
                     const uint32_t sd = scales + b * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
@@ -873,8 +929,8 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
                 const int buf = c & 1;
                 mbar_wait(bar_tempty + 8 * buf, ((c >> 1) & 1) ^ 1);   // both CTAs' epilogues have drained this accumulator
                 tc_fence_after();
-                for (int h = 0; h < 2; h++) {
-                    const int kb = 2 * c + h, s = kb % NS, ph = (kb / NS) & 1;
+                for (int h = 0; h < MMQ_KBC; h++) {
+                    const int kb = MMQ_KBC * c + h, s = kb % NS, ph = (kb / NS) & 1;
                     mbar_wait(bar_full + 8 * s, ph);
                     tc_fence_after();
                     const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
@@ -905,7 +961,7 @@ __global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUt
             const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
             mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
             tc_fence_after();
-            epi_chunk<2, CW>(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0, tp, sic, acc,
+            epi_chunk<MMQ_EPI_DEFAULT, CW>(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0, tp, sic, acc,
                              [&] { if (lane == 0) mbar_arrive_cluster(lte0 + 8 * buf); });
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);
@@ -1007,7 +1063,7 @@ template <int BN>
 static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
                          int mtiles, cudaStream_t stream) {
     const char * e   = getenv("B200_MMQ_EPI");
-    const int    epi = e && *e ? atoi(e) : 2;
+    const int    epi = MMQ_KC > 256 ? 0 : (e && *e ? atoi(e) : MMQ_EPI_DEFAULT);
     switch (epi) {
         case 0: return launch_mmq_bn_epi<BN, 0>(mapA, mapB, a, mapAx, mtiles, stream);
         case 1: return launch_mmq_bn_epi<BN, 1>(mapA, mapB, a, mapAx, mtiles, stream);
@@ -1047,7 +1103,7 @@ static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB,
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
                                  const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
     static bool attr_set = false;
-    auto kern = k_mmq_p<2>;
+    auto kern = k_mmq_p<MMQ_EPI_DEFAULT>;
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_pshape::SMEM));
         attr_set = true;
@@ -1072,7 +1128,10 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
     mmq_kargs a2 = a;
-    a2.trace = nullptr, a2.ksplit = 1;
+    a2.trace = nullptr, a2.ksplit = 1, a2.dbg = env_flag("B200_MMQ_DEBUG", 0);
+#ifdef B200_MMQ_TRACE
+    if (const char * tp = getenv("B200_MMQ_TRACE_PTR")) a2.trace = (long long *) strtoull(tp, nullptr, 0);
+#endif
     B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB128, a2, mapAx, p));
     note_launch();
     return B200_OK;
@@ -1112,7 +1171,8 @@ static int launch_quantize_x8(const float * x, int64_t x_stride, int8_t * Q, flo
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8, x, x_stride, Q, Tt, n, k, kp, npad, z));
+    const bool vec = (uintptr_t) x % 16 == 0 && x_stride % 4 == 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
     note_launch();
     return B200_OK;
 }

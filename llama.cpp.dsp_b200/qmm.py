@@ -23,7 +23,7 @@ EXPORTS = [
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
     "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
-    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
+    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mmq_chunk", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
     "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",

@@ -145,11 +145,15 @@ def random_blocks(t, nrows, k, rng, scale=0.02):
     return raw.reshape(nrows, -1)
 
 
-def mul_mat_plane(t, w, x, m, k, kc=256):
+PLANE_KC = 256   # scale granularity of the tensor-core path; GPU tests set it from b200_mmq_chunk()
+
+
+def mul_mat_plane(t, w, x, m, k, kc=None):
     """numpy restatement of the tensor-core path's arithmetic (llama.cpp.dsp_b200/csrc/mmq.cu): weights dequantized
     bit-exactly, re-expressed as int8 with one f32 scale per (row, 256-chunk); activations int8 with one scale per
     (column, chunk); exact integer chunk dot products; f32 scale-accumulate in chunk order.  -> f32 [n, m]"""
     f32 = np.float32
+    kc = kc or PLANE_KC
     x = np.ascontiguousarray(x, dtype=f32).reshape(-1, k)
     n = x.shape[0]
     kp = (k + kc - 1) // kc * kc

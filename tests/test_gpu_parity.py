@@ -20,6 +20,7 @@ def qmm():
     q = b200pkg.load()
     assert torch.cuda.is_available(), "these tests need the B200"
     assert q.lib().b200_device_ok(torch.cuda.current_device()) == 1
+    qref.PLANE_KC = q.lib().b200_mmq_chunk()
     return q
 
 

@@ -12,6 +12,7 @@ import b200pkg  # noqa: E402
 import qref  # noqa: E402
 
 qmm = b200pkg.load()
+qref.PLANE_KC = qmm.lib().b200_mmq_chunk()
 rng = np.random.default_rng(0)
 quick = len(sys.argv) > 1 and sys.argv[1] == "quick"
 for name, m, k, n in [("q4_K", 128, 256, 16), ("q4_K", 128, 512, 128), ("q4_K", 256, 1024, 256), ("q8_0", 300, 1024, 33),
