@@ -465,11 +465,21 @@ int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W,
 // Activations: the n_tokens * ne11 rows of b are quantized once into the workspace (row (t, j) at index t * ne11 + j),
 // then one GEMV grid with blockIdx.y = (token, slot) pair reads row (t, slot % ne11).  B200_FUSED_QUANT_MAX_K > 0
 // switches rows of k <= that to in-kernel quantization (no workspace).
+// group pairs by expert (one pass over an expert's weights per 4 pairs) when experts are shared: at least two pairs per
+// expert on average, the 4-column GEMV shape exists for this k; B200_MMID_GROUP=0 never, =2 whenever pairs >= 2
+static bool use_mmid_groups(int type, int64_t k, int64_t n_expert, int64_t npairs) {
+    const char * e = getenv("B200_MMID_GROUP");
+    const int    v = e && *e ? atoi(e) : 1;
+    if (v == 0 || k <= fused_quant_max_k() || use_inlane_quant()) return false;
+    if (n_expert > 1024 || npairs > INT32_MAX / 8 || gemv_max_cols(type, k) < 4) return false;
+    return v == 2 ? npairs >= 2 : npairs >= 2 * n_expert;      // measured cross-over (profiles/r01/mmid_bench_v1.log)
+}
 size_t b200_mul_mat_id_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
                                       int64_t n_tokens) {
-    (void) m, (void) n_expert;
+    (void) m;
     if (!weight_type(type) || k <= 0 || n_used <= 0 || n_tokens <= 0 || k <= fused_quant_max_k()) return 0;
-    return (size_t) n_tokens * n_used * q8_soa_layout(k).bytes;   // ne11 <= n_used
+    // q8 activations (ne11 <= n_used rows per token) + the grouping plan
+    return ws_align((size_t) n_tokens * n_used * q8_soa_layout(k).bytes) + mmid_plan_bytes(n_tokens * n_used, n_expert);
 }
 
 int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const float * b, int64_t b_token_stride,
@@ -515,6 +525,26 @@ int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const floa
                                                 n_tokens, type == B200_TYPE_IQ4_XS, stream);
             if (st != B200_OK) return st;
         }
+    }
+    const int64_t npairs_all = n_tokens * n_used;
+    if (!fused && use_mmid_groups(type, k, n_expert, npairs_all) && mmid_max_items(npairs_all, n_expert) <= 65535) {
+        const size_t q8b = ws_align((size_t) n_tokens * ne11 * L.bytes);
+        if (workspace_bytes < q8b + mmid_plan_bytes(npairs_all, n_expert)) return B200_ERR_WORKSPACE;
+        int32_t * plan = (int32_t *) ((uint8_t *) workspace + q8b);
+        st = launch_mmid_plan(ids, ids_row_stride, n_tokens, n_used, n_expert, plan, stream);
+        if (st != B200_OK) return st;
+        const int64_t max_items = mmid_max_items(npairs_all, n_expert);
+        g.ids = nullptr, g.ncols = 4;
+        g.it_hdr = plan, g.it_expert = plan + 4, g.it_pairs = plan + 4 + max_items;
+        g.npairs = max_items;
+        // how many items to expect when sizing grid.x (the count itself is only known on the device): with c pairs on an
+        // expert ceil(c / 4) items, i.e. c / 4 + ~3/8 on average -- rounded up a little, because one item too many
+        // costs a second wave of CTAs and one too few only idles a few SMs
+        const int64_t hit = n_expert < npairs_all ? n_expert : npairs_all;
+        g.items_expected = (npairs_all + 3) / 4 + (hit + 1) / 2;
+        if (g.items_expected > max_items) g.items_expected = max_items;
+        g.xq = (const uint8_t *) workspace;
+        return launch_gemv(g, stream);
     }
     // grid.y is limited to 65535 pairs per launch
     const int64_t tok_per_launch = 65535 / n_used > 0 ? 65535 / n_used : 1;

@@ -43,6 +43,12 @@ struct gemv_args {
     int            n_used, ne11;
     int64_t        npairs;
     int64_t        x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
+    // grouped MUL_MAT_ID (it_hdr != nullptr, ids == nullptr): grid.y = npairs = upper bound of the item count,
+    // items_expected sizes grid.x; the plan arrays are written by launch_mmid_plan
+    const int32_t * it_hdr;
+    const int32_t * it_expert;
+    const int32_t * it_pairs;
+    int64_t         items_expected;
     // several matrices sharing x in one launch (nmat > 1): m = total rows; matrix 0 is (W, dst, dst_col_stride),
     // matrix i >= 1 starts at virtual row mstart[i-1]; all contiguous, same type and k, every m_i % 8 == 0
     int             nmat;
@@ -58,6 +64,11 @@ struct gemv_args {
     int32_t *      local_count;     // this rank's CTA-completion counter (zero between launches)
     int32_t *      rearm;           // arrival counter the quantizer of this launch waited on: reset by the last CTA
 };
+// MUL_MAT_ID plan: group the (token, slot) pairs by the expert they chose, 4 pairs per work item (one GEMV column each)
+size_t  mmid_plan_bytes(int64_t npairs, int64_t n_expert);
+int64_t mmid_max_items(int64_t npairs, int64_t n_expert);
+int     launch_mmid_plan(const int32_t * ids, int64_t ids_row_stride, int64_t n_tokens, int64_t n_used, int64_t n_expert,
+                         void * plan, cudaStream_t stream);
 size_t gemv_q8_smem_bytes(int64_t k, int ncols);
 int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring
 int    launch_gemv(const gemv_args & a, cudaStream_t stream);

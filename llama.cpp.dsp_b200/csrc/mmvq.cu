@@ -389,6 +389,11 @@ struct gemv_kargs {
     int64_t         ids_row_stride;
     int             n_used, ne11;
     int64_t         x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
+    // grouped MUL_MAT_ID (it_hdr != nullptr): blockIdx.y = work item = one expert x up to NCOLS (token, slot) pairs that
+    // chose it (k_mmid_plan); it_hdr[0] = number of items, it_pairs[item][c] = pair index or -1
+    const int32_t * it_hdr;
+    const int32_t * it_expert;
+    const int32_t * it_pairs;
     int             world, rank;
     int64_t         row_offset;
     int             dbg;          // profiling aid: 2 = skip the TMA loads, 8 = skip the dot products,
@@ -491,7 +496,24 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     const uint8_t * W   = a.W;
     const float *   x   = a.x;
     float *         dst = a.dst;
-    if (a.ids) {  // MUL_MAT_ID: pair p = (token, slot); the ids come from the previous kernel (router top-k)
+    __shared__ float * s_dcol[4];                               // grouped MUL_MAT_ID: dst row of each column (or null)
+    int pair_of[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; c++) pair_of[c] = 0;
+    if (a.it_hdr) {  // grouped MUL_MAT_ID: the plan comes from k_mmid_plan, the kernel before us
+        pdl_wait();
+        if ((int) blockIdx.y >= a.it_hdr[0]) return;            // the grid is sized for the worst case
+        W += (int64_t) a.it_expert[blockIdx.y] * a.w_expert_stride;
+#pragma unroll
+        for (int c = 0; c < NCOLS; c++) {
+            const int p = a.it_pairs[blockIdx.y * 4 + c];
+            pair_of[c] = p >= 0 ? p : a.it_pairs[blockIdx.y * 4];   // an empty column repeats column 0 and stores nothing
+            if (threadIdx.x == c) {
+                const int64_t tok = pair_of[c] / a.n_used, slot = pair_of[c] % a.n_used;
+                s_dcol[c] = p >= 0 ? dst + tok * a.dst_token_stride + slot * a.dst_slot_stride : nullptr;
+            }
+        }
+    } else if (a.ids) {  // MUL_MAT_ID: pair p = (token, slot); the ids come from the previous kernel (router top-k)
         pdl_wait();
         const int64_t p = blockIdx.y, tok = p / a.n_used, slot = p % a.n_used;
         const int     e = a.ids[tok * a.ids_row_stride + slot];
@@ -629,9 +651,17 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         }
     } else {
         const uint8_t * xq = a.xq;
-        if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
+        if (a.it_hdr) {
 #pragma unroll
-        for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
+            for (int c = 0; c < NCOLS; c++) {                   // column c = activation row (token, slot % ne11) of its pair
+                const size_t r = (size_t) (pair_of[c] / a.n_used) * a.ne11 + (pair_of[c] % a.n_used) % a.ne11;
+                make_unit_q8<TYPE>(u[c], xq + r * L.bytes, L, a.k, ugc);
+            }
+        } else {
+            if (a.ids) xq += (size_t) ((blockIdx.y / a.n_used) * a.ne11 + (blockIdx.y % a.n_used) % a.ne11) * L.bytes;
+#pragma unroll
+            for (int c = 0; c < NCOLS; c++) make_unit_q8<TYPE>(u[c], xq + (size_t) c * L.bytes, L, a.k, ugc);
+        }
     }
 
     if (threadIdx.x == 0) trace_stamp(a, 2);                    // activations in registers
@@ -695,6 +725,9 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                     // NVLink round trip each: measured 49 us per matmul instead of ~10)
                     for (int r = 0; r < a.world; r++) peers.dst[r][fc * a.dst_col_stride + a.row_offset + r0 + fv] = v;
                     if (a.dbg & 4) __threadfence_system();      // experiment: fence per stage
+                } else if (a.it_hdr) {
+                    float * dp = s_dcol[fc];
+                    if (dp) dp[rl + fv] = v;
                 } else {
                     dl[fc * dcs + rl + fv] = v;
                 }
@@ -832,6 +865,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.nst = P.nst, a.T = P.T, a.nteams = P.nteams, a.row_pitch = P.row_pitch, a.stage_bytes = P.stage_bytes;
     a.act_bytes = P.act_bytes;
     a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used > 0 ? g.n_used : 1;
+    a.it_hdr = g.it_hdr, a.it_expert = g.it_expert, a.it_pairs = g.it_pairs;
     a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
     a.x_token_stride = g.x_token_stride, a.x_slot_stride = g.x_slot_stride;
     a.dst_token_stride = g.dst_token_stride, a.dst_slot_stride = g.dst_slot_stride;
@@ -845,7 +879,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
         peers.local = g.local_count, peers.rearm = g.rearm;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) gx, (unsigned) (g.ids ? g.npairs : 1), 1);
+    cfg.gridDim          = dim3((unsigned) gx, (unsigned) ((g.ids || g.it_hdr) ? g.npairs : 1), 1);
     cfg.blockDim         = dim3((unsigned) gemv_shape<NCOLS, MINB>::THREADS, 1, 1);
     cfg.dynamicSmemBytes = P.smem;
     cfg.stream           = stream;
@@ -873,7 +907,7 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     }
     const int     row_bytes  = (int) (g.k / type_block_elems(TYPE)) * type_block_bytes(TYPE);
     const bool    contiguous = g.w_row_stride == row_bytes;
-    const int64_t pairs      = g.ids ? g.npairs : 1;
+    const int64_t pairs      = g.it_hdr ? g.items_expected : g.ids ? g.npairs : 1;
     // first guess of the grid (two CTAs per SM) to learn the slab length, then the plan fixes CTAs per SM
     gemv_plan P;
     int64_t gx0 = (int64_t) g_sm_count * 2;
@@ -882,10 +916,11 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     // in-lane (g.inlane: any column count, no shared memory)
     const bool fused = g.xq == nullptr && !g.inlane;
     if (fused && NCOLS != 1) return B200_ERR_UNSUPPORTED;
-    if (g.nmat > 1 && (!contiguous || fused || g.ids || g.world > 1)) return B200_ERR_UNSUPPORTED;
+    if (g.nmat > 1 && (!contiguous || fused || g.ids || g.it_hdr || g.world > 1)) return B200_ERR_UNSUPPORTED;
+    if (g.it_hdr && (fused || g.inlane || g.world > 1)) return B200_ERR_UNSUPPORTED;
     if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, fused, P)) return B200_ERR_UNSUPPORTED;
     int64_t gx = (int64_t) g_sm_count * P.minb * env_int("B200_GEMV_WAVES", 1);
-    if (pairs > 1) gx = (gx + pairs - 1) / pairs;
+    if (pairs > 1) gx = g.it_hdr ? gx / pairs : (gx + pairs - 1) / pairs;   // grouped: stay inside one wave of CTAs
     const int64_t max_ctas = (g.m + P.V - 1) / P.V;             // at least one stage each
     if (gx > max_ctas) gx = max_ctas;
     if (gx < 1) gx = 1;
@@ -915,6 +950,70 @@ static int launch_gemv_n(const gemv_args & g, cudaStream_t stream) {
         case 4: return launch_gemv_t<TYPE, 4>(g, stream);
     }
     return B200_ERR_SHAPE;
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT_ID plan
+// Groups the (token, slot) pairs of one MUL_MAT_ID by the expert they chose: item = one expert x up to 4 pairs, so an
+// expert's weights are streamed once per 4 pairs instead of once per pair (the reference gathers rows per expert on the
+// host after a D2H copy of ids, ggml-cuda.cu:2008-2011,2059-2118; here ids never leave the device).
+// plan = [n_items, 0, 0, 0][item_expert: max_items][item_pairs: max_items x 4].  Which pairs share an item depends on
+// atomic order, results do not: every column of the GEMV is computed on its own.
+constexpr int MMID_MAX_EXPERTS = 1024;
+int64_t mmid_max_items(int64_t npairs, int64_t n_expert) {
+    const int64_t a = npairs / 4 + (n_expert < npairs ? n_expert : npairs);
+    return a < npairs ? a : npairs;
+}
+size_t mmid_plan_bytes(int64_t npairs, int64_t n_expert) {
+    if (n_expert > MMID_MAX_EXPERTS || npairs <= 0) return 0;
+    return 16 + (size_t) mmid_max_items(npairs, n_expert) * 20;
+}
+__global__ void __launch_bounds__(1024) k_mmid_plan(const int32_t * __restrict__ ids, int64_t ids_row_stride, int npairs,
+                                                    int n_used, int n_expert, int max_items, int32_t * __restrict__ hdr,
+                                                    int32_t * __restrict__ item_expert, int32_t * __restrict__ item_pairs) {
+    __shared__ int cnt[MMID_MAX_EXPERTS], off[MMID_MAX_EXPERTS], cur[MMID_MAX_EXPERTS];
+    pdl_launch_dependents();
+    pdl_wait();                                                 // ids come from the router kernels before us
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) cnt[e] = 0, cur[e] = 0;
+    for (int i = threadIdx.x; i < max_items; i += blockDim.x) {
+        item_expert[i] = 0;
+        item_pairs[4 * i] = item_pairs[4 * i + 1] = item_pairs[4 * i + 2] = item_pairs[4 * i + 3] = -1;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
+        const int e = ids[(int64_t) (p / n_used) * ids_row_stride + p % n_used];
+        if (e >= 0 && e < n_expert) atomicAdd(&cnt[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int e = 0; e < n_expert; e++) off[e] = run, run += (cnt[e] + 3) / 4;
+        hdr[0] = run, hdr[1] = hdr[2] = hdr[3] = 0;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
+        const int e = ids[(int64_t) (p / n_used) * ids_row_stride + p % n_used];
+        if (e < 0 || e >= n_expert) continue;                   // (an invalid id leaves its dst row untouched)
+        const int pos = atomicAdd(&cur[e], 1), item = off[e] + pos / 4;
+        item_pairs[4 * item + (pos & 3)] = p;
+        item_expert[item] = e;
+    }
+}
+int launch_mmid_plan(const int32_t * ids, int64_t ids_row_stride, int64_t n_tokens, int64_t n_used, int64_t n_expert,
+                     void * plan, cudaStream_t stream) {
+    const int64_t npairs = n_tokens * n_used, max_items = mmid_max_items(npairs, n_expert);
+    int32_t * hdr = (int32_t *) plan;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim  = dim3(1, 1, 1);
+    cfg.blockDim = dim3(1024, 1, 1);
+    cfg.stream   = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_mmid_plan, ids, ids_row_stride, (int) npairs, (int) n_used, (int) n_expert,
+                                     (int) max_items, hdr, hdr + 4, hdr + 4 + max_items));
+    note_launch();
+    return B200_OK;
 }
 
 int launch_gemv(const gemv_args & g, cudaStream_t stream) {

@@ -297,6 +297,40 @@ def test_mul_mat_id(qmm, name, t, n_expert, n_used, n_tokens, bcast):
     assert qref.nmse(cpu, got) < NMSE_HARNESS
 
 
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("n_expert,n_used,n_tokens,bcast", [(8, 2, 8, True), (8, 2, 33, False), (4, 4, 7, False),
+                                                            (16, 1, 5, True), (8, 2, 1, True)])
+def test_mul_mat_id_grouped_by_expert(qmm, monkeypatch, name, t, n_expert, n_used, n_tokens, bcast):
+    """batched decode: pairs that chose the same expert share one pass over its weights (4 per work item, planned on the
+    device).  Forced on (B200_MMID_GROUP=2) and off (=0): both must meet the oracle bounds, agree with each other to fp32
+    summation order, and the grouped result must not depend on the atomic order of the plan (bit-identical re-runs).
+    ids contain repeated experts across tokens and, with a skewed router, one hot expert."""
+    rng = np.random.default_rng(n_expert * 1000 + n_used * 10 + n_tokens)
+    m, k = 72, 512
+    ne11 = 1 if bcast else n_used
+    w = qref.random_blocks(t, n_expert * m, k, rng)
+    b = rng.uniform(-1, 1, (n_tokens, ne11, k)).astype(np.float32)
+    ids_full = np.stack([rng.permutation(n_expert) for _ in range(n_tokens)]).astype(np.int32)
+    ids_full[: n_tokens // 2, 0] = 1                              # a hot expert (rows stay permutations where it matters not)
+    for r in range(n_tokens // 2):                                # keep each row's first n_used ids distinct
+        row = [1] + [e for e in ids_full[r, 1:] if e != 1]
+        ids_full[r, :len(row)] = row
+    ids_dev = dev(ids_full)[:, :n_used]
+    ids = ids_full[:, :n_used]
+    wd, bd = dev(w), dev(b)
+    monkeypatch.setenv("B200_MMID_GROUP", "2")
+    out = torch.full((n_tokens, n_used, m), 5.0, device="cuda")
+    got = qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert, out=out).clone()
+    for _ in range(3):
+        assert torch.equal(qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert), got)
+    monkeypatch.setenv("B200_MMID_GROUP", "0")
+    plain = qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert)
+    g = got.cpu().numpy()
+    assert qref.nmse(qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "q8_1"), g) < NMSE_TIGHT
+    assert qref.nmse(qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "cpu"), g) < NMSE_HARNESS
+    assert qref.nmse(plain.cpu().numpy(), g) < 1e-11
+
+
 def test_launch_counter_counts_kernels(qmm):
     before = qmm.launch_count()
     w = torch.zeros(144 * 16, dtype=torch.uint8, device="cuda")
