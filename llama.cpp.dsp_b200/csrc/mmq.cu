@@ -189,6 +189,10 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
         "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// pull a tensor-map box into L2 only (no shared memory, nothing to wait for)
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap * map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -354,6 +358,9 @@ struct mmq_kargs {
     int64_t       dst_stride;
     int           m, n, nch, npad, mpad;
     int           accumulate;   // dst += result (second plane of a two-plane weight)
+    int           plane_split;  // with ksplit = 2: grid.z selects the PLANE of a two-plane weight (Q8_0: value, residual;
+                                // second plane in mapAx.m[0] / Sx[0]) instead of a K half -- the same two addends as the
+                                // sequential accumulate pass, on twice as many SMs
     int           ksplit;       // 1, or 2: grid.z halves of the chunk range, results added with red.global.add onto a
                                 // zeroed dst (few-tile shapes: m = 4096 at n = 512 fills 64 of 148 SMs otherwise)
     int           dbg;          // experiments (B200_MMQ_DEBUG): 1 = persistent kernel skips the second B box (wrong results,
@@ -434,7 +441,8 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
     }
     const int m0 = tile * MMQ_BM, n0 = blockIdx.y * BN;
     // this CTA's chunk range [cb, cb + nch): everything below counts chunks and k-blocks locally
-    const int cper = (a.nch + a.ksplit - 1) / a.ksplit, cb = (int) blockIdx.z * cper;
+    if (a.plane_split && blockIdx.z == 1) pA = &mapAx.m[0], S = a.Sx[0];
+    const int cper = a.plane_split ? a.nch : (a.nch + a.ksplit - 1) / a.ksplit, cb = a.plane_split ? 0 : (int) blockIdx.z * cper;
     const int nch = min(cper, a.nch - cb), nkb = MMQ_KBC * nch;
 
     if (threadIdx.x == 0) {
@@ -573,6 +581,7 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
 // B tiles are always loaded as 128-row boxes (two per k-block for a 256-wide item), so one tensor map serves both widths;
 // the UMMA N comes from a per-item instruction descriptor; TMEM holds two 256-column accumulator buffers.
 struct mmq_pargs {
+    int pf;        // weight tiles are prefetched into L2 this many k-blocks ahead of their load (0 = off)
     int ntn;       // 256-wide n-tiles per m-tile
     int mtiles;    // m-tiles of all matrices of the launch
     int raster;    // 0: consecutive items walk n first, 1: m first (B200_MMQ_RASTER)
@@ -677,6 +686,10 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                         mbar_expect_tx(bar_full + 8 * st, stage_tx);
                         tma_load_2d(sa, pA, (MMQ_KBC * c + h) * MMQ_BK, m0, bar_full + 8 * st);
                         tma_load_2d(sb, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0, bar_full + 8 * st);
+                        // the weight plane is streamed from HBM once per n-tile: ask L2 for the tile `pf` k-blocks ahead
+                        // now, so that its load finds it there (activation tiles are L2-resident anyway)
+                        if (p.pf && MMQ_KBC * c + h + p.pf < MMQ_KBC * nch)
+                            tma_prefetch_2d(pA, (MMQ_KBC * c + h + p.pf) * MMQ_BK, m0);
                         if (two) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
                         if (++st == NS) st = 0, st_ph ^= 1;
                     }
@@ -1110,6 +1123,7 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     }
     mmq_pargs p;
     p.ntn = (a.n + 255) / 256;
+    p.pf  = env_flag("B200_MMQ_PF", 8);
     p.mtiles = mtiles;
     p.raster = env_flag("B200_MMQ_RASTER", 0);
     const int tiles = mtiles * p.ntn;
@@ -1206,8 +1220,12 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
     const char * pe = getenv("B200_MMQ_PAIR");
     const bool   pair = pe && atoi(pe) == 1 && n > 128 && mt >= 2;
     if (pair) bn = 256;
-    const bool can_split = !pair && mmq_nplanes(type) == 1 && m % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t) dst % 16 == 0;
-    const int  ksplit = mmq_ksplit(mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
+    const bool aligned   = m % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t) dst % 16 == 0;
+    const bool can_split = !pair && mmq_nplanes(type) == 1 && aligned;
+    // two-plane weights with few tiles: both planes in one launch, grid.z = plane (same addends as the accumulate pass)
+    const bool plane_split = !pair && mmq_nplanes(type) == 2 && aligned && mt * ((n + bn - 1) / bn) * 2 <= sm_count &&
+                             env_flag("B200_MMQ_PLANE_SPLIT", 1);
+    const int  ksplit = plane_split ? 2 : mmq_ksplit(mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
     {
         mmq_zero z = {};
         if (ksplit > 1) z.cnt = 1, z.p[0] = dst, z.stride[0] = dst_stride, z.m[0] = m;
@@ -1218,11 +1236,26 @@ int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, 
     CUtensorMap mapA, mapB;
     int st = make_map(&mapB, Q, n, kp, (pair || persist) ? 128 : bn);
     if (st != B200_OK) return st;
+    if (plane_split) {
+        const uint8_t * p0 = (const uint8_t *) plane, * p1 = p0 + mmq_plane_bytes(m, k);
+        mmq_maps3 mx = {};
+        st = make_map(&mapA, p0, m, kp, MMQ_BM);
+        if (st != B200_OK) return st;
+        st = make_map(&mx.m[0], p1, m, kp, MMQ_BM);
+        if (st != B200_OK) return st;
+        mmq_kargs a = {};
+        a.S = (const float *) (p0 + align256((size_t) m * kp)), a.Sx[0] = (const float *) (p1 + align256((size_t) m * kp));
+        a.Tt = Tt, a.dst = dst, a.dst_stride = dst_stride;
+        a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
+        a.ksplit = 2, a.plane_split = 1, a.nmat = 1;
+        return bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, (int) mt, stream)
+                         : launch_mmq_bn<128>(mapA, mapB, a, mx, (int) mt, stream);
+    }
     for (int pl = 0; pl < mmq_nplanes(type); pl++) {
         const uint8_t * pb = (const uint8_t *) plane + (size_t) pl * mmq_plane_bytes(m, k);
         st = make_map(&mapA, pb, m, kp, MMQ_BM);
         if (st != B200_OK) return st;
-        mmq_kargs a;
+        mmq_kargs a = {};
         a.S   = (const float *) (pb + align256((size_t) m * kp));
         a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
         a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);

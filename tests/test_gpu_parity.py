@@ -199,6 +199,26 @@ def test_mmq_split_k_is_exact_and_deterministic(qmm, monkeypatch, name, t, m, k,
     assert qref.nmse(one.cpu().numpy(), got.cpu().numpy()) < 1e-11
 
 
+@pytest.mark.parametrize("m,k,n", [(512, 4096, 512), (300, 1024, 33), (4096, 1024, 200)])
+def test_mmq_q8_0_plane_split_equals_accumulate_pass(qmm, monkeypatch, m, k, n):
+    """Q8_0 keeps two int8 planes (value + residual).  With few tiles both planes run in ONE launch, grid.z = plane, each
+    added with red.global.add onto a zeroed dst: the same two addends as the sequential accumulate pass, so the bits must
+    be identical to it (B200_MMQ_PLANE_SPLIT=0), from run to run, and stale dst contents must not leak."""
+    rng = np.random.default_rng(m + n)
+    t = qref.Q8_0
+    w = qref.random_blocks(t, m, k, rng)
+    x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+    plane = qmm.build_plane(t, dev(w), m, k)
+    xd = dev(x)
+    out = torch.full((n, m), 9.0, device="cuda")
+    got = qmm.mul_mat_mmq(t, plane, xd, m, k, out=out).clone()
+    out.fill_(-1.0)
+    assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k, out=out), got)
+    monkeypatch.setenv("B200_MMQ_PLANE_SPLIT", "0")
+    assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
+    assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
+
+
 @pytest.mark.parametrize("name,t", [("q4_K", qref.Q4_K), ("q8_0", qref.Q8_0), ("q6_K", qref.Q6_K)])
 @pytest.mark.parametrize("m,k,n", [(9700, 512, 300), (19000, 256, 512), (2500, 768, 1000)])
 def test_mmq_persistent_schedule(qmm, monkeypatch, name, t, m, k, n):
