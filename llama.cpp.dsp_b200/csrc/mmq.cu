@@ -1123,7 +1123,7 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     }
     mmq_pargs p;
     p.ntn = (a.n + 255) / 256;
-    p.pf  = env_flag("B200_MMQ_PF", 8);
+    p.pf  = env_flag("B200_MMQ_PF", 0);   // measured: no gain at 4, 8, 16 (profiles/r01/pp_sweep_l2_lookahead.log)
     p.mtiles = mtiles;
     p.raster = env_flag("B200_MMQ_RASTER", 0);
     const int tiles = mtiles * p.ntn;
