@@ -551,7 +551,11 @@ def main():
                "ms_per_step": ms_e2e, "launch": e2e_launch, "ms_per_step_eager": ms_e2e_eager,
                "api": ("b200_mul_mat_host per MUL_MAT" if token_step is token_step_per_node or not use_graph else
                        "b200_mul_mat_multi_host per group of MUL_MATs sharing src1") +
-                      " (pinned host x -> H2D -> quantize + GEMV -> D2H), stream sync once per token"}
+                      " (pinned host x -> read over PCIe by the quantizer kernel, no staging copy -> GEMV -> results"
+                      " stored into pinned host memory by a copy kernel), stream sync once per token",
+               "h2d": "zero-copy: the activation / result bytes counted here cross the bus as kernel loads from and "
+                      "kernel stores to pinned host memory (B200_HOST_ZEROCOPY=0 restores cudaMemcpyAsync both ways)"
+               if os.environ.get("B200_HOST_ZEROCOPY", "1") != "0" else "cudaMemcpyAsync per call"}
     else:
         # row-split: host activations are broadcast to every rank's device, the gathered result is read back on rank 0
         def token_step_host_split():

@@ -72,6 +72,54 @@ static __global__ void k_rowsplit_signal(const rowsplit_signal_args a) {
     }
 }
 
+// results -> pinned host memory with coalesced 16-byte stores over PCIe: a kernel boundary (~2 us under programmatic
+// dependent launch) instead of a copy node (~10 us each in a stream of 129 per token)
+static __global__ void __launch_bounds__(256) k_copy_out(const float * __restrict__ src, float * __restrict__ dst, size_t count,
+                                                         bool vec) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t) gridDim.x * blockDim.x;
+    if (vec) {
+        for (size_t i = tid; i < count / 4; i += nthr) reinterpret_cast<float4 *>(dst)[i] = reinterpret_cast<const float4 *>(src)[i];
+        for (size_t i = count / 4 * 4 + tid; i < count; i += nthr) dst[i] = src[i];
+    } else {
+        for (size_t i = tid; i < count; i += nthr) dst[i] = src[i];
+    }
+}
+// device results -> host: the copy kernel when dst_host is pinned (UVA-mapped), else cudaMemcpyAsync
+static int results_to_host(float * dst_host, const float * src_dev, size_t count, cudaStream_t stream) {
+    if (!count) return B200_OK;
+    const char * e = getenv("B200_HOST_ZEROCOPY");
+    cudaPointerAttributes at;
+    float * alias = nullptr;
+    if (!(e && *e && atoi(e) == 0)) {
+        if (cudaPointerGetAttributes(&at, dst_host) == cudaSuccess) {
+            if (at.type == cudaMemoryTypeHost && at.devicePointer) alias = (float *) at.devicePointer;
+        } else {
+            cudaGetLastError();
+        }
+    }
+    if (!alias) {
+        B200_CUDA_TRY(cudaMemcpyAsync(dst_host, src_dev, count * 4, cudaMemcpyDeviceToHost, stream));
+        return B200_OK;
+    }
+    const bool vec = (uintptr_t) alias % 16 == 0 && (uintptr_t) src_dev % 16 == 0;
+    size_t blocks = (count / 4 + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 296) blocks = 296;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim  = dim3((unsigned) blocks, 1, 1);
+    cfg.blockDim = dim3(256, 1, 1);
+    cfg.stream   = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_copy_out, src_dev, alias, count, vec));
+    note_launch();
+    return B200_OK;
+}
+
 extern "C" {
 
 int b200_qmm_abi_version(void) { return 1; }
@@ -387,6 +435,21 @@ int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, cons
 
 static size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
+// Host activations that live in pinned (page-locked, UVA-mapped) memory are read by the quantizer kernel straight over
+// PCIe instead of being staged by a copy: one stream operation and one boundary less per call, the same bytes crossing
+// the bus inside the call.  Pageable memory (or B200_HOST_ZEROCOPY=0) takes the staged copy.  n <= 8 only: the
+// tensor-core path reads x more than once.
+static const float * host_x_device_alias(const float * x_host, int64_t n) {
+    const char * e = getenv("B200_HOST_ZEROCOPY");
+    if ((e && *e && atoi(e) == 0) || n >= mmq_min_batch()) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, x_host) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return at.type == cudaMemoryTypeHost && at.devicePointer ? (const float *) at.devicePointer : nullptr;
+}
+
 size_t b200_mul_mat_host_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     if (!weight_type(type) || m < 0 || n < 0 || k < 0) return 0;
     return align256((size_t) n * k * 4) + align256((size_t) n * m * 4) + align256(b200_mul_mat_workspace_size(type, m, n, k));
@@ -404,12 +467,15 @@ int b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const floa
     float * x_dev   = (float *) workspace;
     float * dst_dev = (float *) ((uint8_t *) workspace + align256((size_t) n * k * 4));
     void *  ws      = (uint8_t *) dst_dev + align256((size_t) n * m * 4);
-    if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
-    const int st = b200_mul_mat(type, W, w_row_stride, x_dev, k, dst_dev, m, m, n, k, ws,
+    const float * x_in = k > 0 ? host_x_device_alias(x_host, n) : nullptr;
+    if (!x_in) {
+        if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
+        x_in = x_dev;
+    }
+    const int st = b200_mul_mat(type, W, w_row_stride, x_in, k, dst_dev, m, m, n, k, ws,
                                 b200_mul_mat_workspace_size(type, m, n, k), stream_);
     if (st != B200_OK) return st;
-    B200_CUDA_TRY(cudaMemcpyAsync(dst_host, dst_dev, (size_t) n * m * 4, cudaMemcpyDeviceToHost, stream));
-    return B200_OK;
+    return results_to_host(dst_host, dst_dev, (size_t) n * m, stream);
 }
 
 // Several matrices, one HOST activation block: one H2D copy of x, b200_mul_mat_multi on the device, and one D2H copy per
@@ -440,7 +506,11 @@ int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W,
     float * x_dev   = (float *) workspace;
     float * dst_dev = (float *) ((uint8_t *) workspace + align256((size_t) n * k * 4));
     void *  ws      = (uint8_t *) dst_dev + align256((size_t) n * rows * 4 + 256 * (size_t) nmat);
-    if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
+    const float * x_in = k > 0 ? host_x_device_alias(x_host, n) : nullptr;
+    if (!x_in) {
+        if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
+        x_in = x_dev;
+    }
     float * dd[64];
     int64_t ds[64];
     size_t  off = 0;
@@ -448,14 +518,15 @@ int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W,
         dd[i] = dst_dev + off, ds[i] = m[i];
         off += (size_t) n * m[i];
     }
-    const int st = b200_mul_mat_multi(nmat, types, W, x_dev, k, dd, ds, m, n, k, ws,
+    const int st = b200_mul_mat_multi(nmat, types, W, x_in, k, dd, ds, m, n, k, ws,
                                       b200_mul_mat_multi_workspace_size(nmat, types, m, n, k), stream_);
     if (st != B200_OK) return st;
     for (int i = 0; i < nmat;) {
         int    j     = i + 1;
         size_t count = (size_t) n * m[i];
         while (j < nmat && dst_host[j] == dst_host[i] + count) count += (size_t) n * m[j++];
-        if (count) B200_CUDA_TRY(cudaMemcpyAsync(dst_host[i], dd[i], count * 4, cudaMemcpyDeviceToHost, stream));
+        const int st2 = results_to_host(dst_host[i], dd[i], count, stream);
+        if (st2 != B200_OK) return st2;
         i = j;
     }
     return B200_OK;

@@ -438,3 +438,29 @@ def test_mul_mat_multi_host_matches_device_path(qmm):
     want = qmm.mul_mat_multi([t for t, _ in spec], ws, xh.cuda(), [m for _, m in spec], k)
     for got, w_ in zip(outs, want):
         assert torch.equal(got, w_.cpu())
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_activations_zero_copy_equals_staged_copy(qmm, monkeypatch, pinned):
+    """pinned host activations are read by the quantizer kernel over PCIe (no staging copy) and results go to pinned
+    host memory through a copy kernel; pageable buffers, and B200_HOST_ZEROCOPY=0, take cudaMemcpyAsync.  Same bits either way, for the single and the grouped host entry."""
+    rng = np.random.default_rng(43)
+    k, n = 4096, 3
+    spec = [(12, 512), (14, 128)]
+    ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
+    xh = torch.from_numpy(rng.uniform(-1, 1, (n, k)).astype(np.float32))
+    if pinned:
+        xh = xh.pin_memory()
+    want = qmm.mul_mat_multi([t for t, _ in spec], ws, xh.cuda(), [m for _, m in spec], k)
+    for zc in ("1", "0"):
+        monkeypatch.setenv("B200_HOST_ZEROCOPY", zc)
+        outs = [torch.full((n, m), float("nan")) for _, m in spec]
+        one = torch.full((n, 512), float("nan"))
+        if pinned:                                              # results: copy kernel into pinned memory / cudaMemcpyAsync
+            outs, one = [o.pin_memory() for o in outs], one.pin_memory()
+        qmm.MultiMatMulHost([t for t, _ in spec], ws, [m for _, m in spec], k, outs, n)(xh)
+        qmm.mul_mat_host(12, ws[0], xh, one, 512, k)
+        torch.cuda.synchronize()
+        for got, w_ in zip(outs, want):
+            assert torch.equal(got, w_.cpu())
+        assert torch.equal(one, want[0].cpu())
