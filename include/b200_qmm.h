@@ -177,7 +177,10 @@ B200_API int    b200_mmq_chunk(void);
  * ggml_backend_cuda_set_tensor_async, ggml/src/ggml-cuda/ggml-cuda.cu:2386-2393), graph_compute, then
  * ggml_backend_cuda_get_tensor_async (:2395-2402).  Weights stay device-resident as in a ggml weight buffer
  * (set once through buffer.set_tensor, ggml-cuda.cu:576-582).  bench.py's `e2e` figure is measured through this call.
- *   x_host / dst_host   host memory, packed [n][k] / [n][m]; pinned memory makes the copies truly asynchronous
+ *   x_host / dst_host   host memory, packed [n][k] / [n][m].  PINNED (page-locked, UVA-mapped) buffers are not staged
+ *                       at all for n <= 8: the activation quantizer reads x_host over PCIe and a copy kernel stores the
+ *                       result into dst_host -- a kernel boundary instead of a copy node each way (bench.py e2e:
+ *                       3.90 -> 1.87 ms per token).  Pageable buffers, and B200_HOST_ZEROCOPY=0, use cudaMemcpyAsync.
  *   workspace           device scratch of at least b200_mul_mat_host_workspace_size() bytes, 256-byte aligned
  */
 B200_API size_t b200_mul_mat_host_workspace_size(int type, int64_t m, int64_t n, int64_t k);
