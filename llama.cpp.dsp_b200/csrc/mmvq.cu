@@ -396,8 +396,10 @@ struct gemv_kargs {
     const int32_t * it_pairs;
     int             world, rank;
     int64_t         row_offset;
-    int             dbg;          // profiling aid: 2 = skip the TMA loads, 8 = skip the dot products,
-                                  // 32 = weight loads carry the L2 evict_first policy (experiment)
+    int             evict_first;  // weight loads carry the L2 evict_first policy: weights are streamed once per token, the
+                                  // activations and the q8 scratch they would push out of L2 are re-read by every CTA
+                                  // (+1.5-2 % on the 8B token, profiles/r01/decode_ab_v2.log; B200_GEMV_EVICT_FIRST=0: off)
+    int             dbg;          // profiling aid: 2 = skip the TMA loads, 8 = skip the dot products
     unsigned long long * trace;   // profiling aid: 8 globaltimer stamps per CTA (tools/gemv_trace.py), else nullptr
 };
 __device__ __forceinline__ void trace_stamp(const gemv_kargs & a, int i) {
@@ -545,7 +547,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 
     if (warp == NW) {
         // ---------------------------------------------------------------------------------------- TMA + epilogue warp
-        const uint64_t policy = (a.dbg & 32) ? l2_policy_evict_first() : 0;
+        const uint64_t policy = a.evict_first ? l2_policy_evict_first() : 0;
         auto issue = [&](int st, int slot) {  // all lanes call; stage st -> ring slot `slot` (= st % nst)
             const int      r0 = r_begin + st * V, nr = min(V, r_end - r0);
             const uint32_t dstb = sm_stage + slot * a.stage_bytes;
@@ -563,7 +565,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                     const uint64_t g0   = g & ~(uint64_t) 15;
                     const uint32_t span = (uint32_t) (((g + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
                     mbar_expect_tx(bar, span);
-                    if (a.dbg & 32) tma_load_1d_hint(dstb, (const void *) g0, span, bar, policy);
+                    if (a.evict_first) tma_load_1d_hint(dstb, (const void *) g0, span, bar, policy);
                     else tma_load_1d(dstb, (const void *) g0, span, bar);
                 }
             } else {  // strided rows: one bulk copy per row, lane i copies row i
@@ -871,6 +873,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.dst_token_stride = g.dst_token_stride, a.dst_slot_stride = g.dst_slot_stride;
     a.world = g.world, a.rank = g.rank, a.row_offset = g.row_offset;
     a.dbg = env_int("B200_GEMV_DEBUG", 0);
+    a.evict_first = env_int("B200_GEMV_EVICT_FIRST", 1);
     a.trace = nullptr;
     a.trace = next_trace_slab();
     gemv_peers peers = {};
