@@ -1,5 +1,6 @@
 """Whole-token decode sweep over env knobs, in one process (weights generated once): every quantized matmul of a
-Llama-3-8B-shaped Q4_K_M token through b200_mul_mat_multi per src1 group, CUDA-graph replay, with next-weight hints.
+Llama-3-8B-shaped Q4_K_M token through b200_mul_mat_multi per src1 group, CUDA-graph replay; results are checked bit for bit against the first
+configuration.  B200_QMM_LIB selects an A/B build of the library.
 usage: python tools/decode_sweep.py [model] KNOB=v,KNOB=v ...   (each argument after the model is one configuration)"""
 import os
 import sys
@@ -52,16 +53,11 @@ def main():
     ref = None
     for cfg in configs:
         knobs = dict(cfg)
-        hints = knobs.pop("HINTS", "1") == "1"
         for kn in list(os.environ):
             if kn.startswith("B200_GEMV") or kn in ("B200_PDL",):
                 os.environ.pop(kn)
         for kn, v in knobs.items():
             os.environ[kn] = v
-        for i, (call, _) in enumerate(calls):
-            call.next_weights = calls[(i + 1) % len(calls)][0].keep[0] if hints else None
-        if not hints:
-            getattr(qmm, 'prefetch_hint', lambda *_: None)(None)
 
         def step():
             for call, x in calls:

@@ -29,9 +29,6 @@ for L in range(layers + 8):   # 8 extra layers in front so that the traced ones 
         outs = [torch.zeros((1, m), device=dev) for _, m in spec]
         calls.append((qmm.MultiMatMul([t for t, _ in spec], ws, [m for _, m in spec], k, outs, 1), xs[k]))
         names.append("%s.%d" % (nm, L))
-for i, (c, _) in enumerate(calls):
-    if os.environ.get("HINTS", "0") == "1":
-        c.next_weights = calls[(i + 1) % len(calls)][0].keep[0]
 
 
 def run(first, last):
