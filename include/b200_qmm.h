@@ -59,6 +59,11 @@ B200_API int          b200_device_ok(int device);          /* 1 if `device` is a
 B200_API int          b200_sm_count(int device);
 /* number of kernels this library has launched since load (all threads); bench.py reports the delta as gpu_launches */
 B200_API int64_t      b200_launch_count(void);
+/* Tuning knobs (B200_* environment variables) are read ONCE per process at first use; a caller that
+ * changes them afterwards (tests, sweep tools) calls this to have them read again. */
+B200_API void         b200_reload_env(void);
+/* profiling aid (tools/gemv_trace.py): the next `launches` GEMV launches write 4096 x 8 globaltimer stamps each to `base` */
+B200_API void         b200_debug_gemv_trace(void * device_base, int64_t launches);
 
 /* is (type) one of Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS?      -- replaces the type switch in ggml_cuda_mul_mat,
  * ggml/src/ggml-cuda/ggml-cuda.cu:1877-1938 and ggml_cuda_should_use_mmq, ggml/src/ggml-cuda/mmq.cu:99-153 */

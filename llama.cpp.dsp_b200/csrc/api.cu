@@ -6,6 +6,7 @@
 #include <cuda.h>
 
 #include <atomic>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -22,6 +23,50 @@ int check_cuda(cudaError_t e, const char * what) {
     snprintf(g_last_cuda_error, sizeof(g_last_cuda_error), "%s: %s (%s)", what, cudaGetErrorName(e),
              cudaGetErrorString(e));
     return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? B200_ERR_NO_DEVICE : B200_ERR_CUDA;
+}
+
+int current_device() {
+    int dev = -1;
+    return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;
+}
+int sm_count_current_device() {
+    static std::atomic<int> cache[MAX_DEVICES];
+    const int dev = current_device();
+    if (dev < 0 || dev >= MAX_DEVICES) return 0;
+    int n = cache[dev].load(std::memory_order_relaxed);
+    if (!n) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        cache[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
+
+// Environment knobs are read once per process (a getenv per knob per launch is ~1 us of host time on the eager path);
+// b200_reload_env() forgets the cached values (tests and sweep tools flip knobs inside one process).
+struct knob_entry {
+    const char * name;
+    int          value;
+};
+static knob_entry           g_knobs[64];
+static std::atomic<int>     g_nknobs{0};
+static std::mutex           g_knob_mtx;
+int env_knob(const char * name, int dflt) {
+    const int n = g_nknobs.load(std::memory_order_acquire);
+    for (int i = 0; i < n; i++)
+        if (g_knobs[i].name == name || strcmp(g_knobs[i].name, name) == 0) return g_knobs[i].value;
+    const char * e = getenv(name);
+    const int    v = e && *e ? atoi(e) : dflt;
+    std::lock_guard<std::mutex> lock(g_knob_mtx);
+    const int m = g_nknobs.load(std::memory_order_relaxed);
+    if (m < 64) {
+        g_knobs[m].name = name, g_knobs[m].value = v;
+        g_nknobs.store(m + 1, std::memory_order_release);
+    }
+    return v;
+}
+static void env_forget() {
+    std::lock_guard<std::mutex> lock(g_knob_mtx);
+    g_nknobs.store(0, std::memory_order_release);
 }
 
 static int blck_of(int type) {
@@ -89,10 +134,9 @@ static __global__ void __launch_bounds__(256) k_copy_out(const float * __restric
 // device results -> host: the copy kernel when dst_host is pinned (UVA-mapped), else cudaMemcpyAsync
 static int results_to_host(float * dst_host, const float * src_dev, size_t count, cudaStream_t stream) {
     if (!count) return B200_OK;
-    const char * e = getenv("B200_HOST_ZEROCOPY");
     cudaPointerAttributes at;
     float * alias = nullptr;
-    if (!(e && *e && atoi(e) == 0)) {
+    if (env_knob("B200_HOST_ZEROCOPY", 1) != 0) {
         if (cudaPointerGetAttributes(&at, dst_host) == cudaSuccess) {
             if (at.type == cudaMemoryTypeHost && at.devicePointer) alias = (float *) at.devicePointer;
         } else {
@@ -123,6 +167,9 @@ static int results_to_host(float * dst_host, const float * src_dev, size_t count
 extern "C" {
 
 int b200_qmm_abi_version(void) { return 1; }
+
+void b200_reload_env(void) { env_forget(); }
+void b200_debug_gemv_trace(void * base, int64_t launches) { gemv_trace_set(base, launches); }
 
 const char * b200_status_string(int s) {
     switch (s) {
@@ -191,25 +238,12 @@ int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * 
 //              CTAs re-reading and re-quantizing the same row cost 2-5 us between the dependency release and the first
 //              dot product (k = 4096: 6.8 us vs 6.0 us per matmul; k = 14336: 18 us vs 12 us).
 // So separate is the default; B200_FUSED_QUANT_MAX_K > 0 opts single-column matmuls with k <= that into the fused path.
-static int fused_quant_max_k() {
-    const char * e = getenv("B200_FUSED_QUANT_MAX_K");
-    return e && *e ? atoi(e) : 0;
-}
+static int fused_quant_max_k() { return env_knob("B200_FUSED_QUANT_MAX_K", 0); }
 static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
 // in-lane activation quantizer inside the GEMV (no quantizer kernel): B200_INLANE_QUANT=1
-static bool use_inlane_quant() {
-    static int v = -1;
-    if (v < 0) {
-        const char * e = getenv("B200_INLANE_QUANT");
-        v = e && *e ? atoi(e) : 0;
-    }
-    return v != 0;
-}
+static bool use_inlane_quant() { return env_knob("B200_INLANE_QUANT", 0) != 0; }
 
-static int mmq_min_batch() {
-    const char * e = getenv("B200_MMQ_MIN_N");
-    return e && *e ? atoi(e) : 9;
-}
+static int mmq_min_batch() { return env_knob("B200_MMQ_MIN_N", 9); }
 static size_t ws_align(size_t v) { return (v + 255) & ~(size_t) 255; }
 // batches above MMVQ_MAX_BATCH_SIZE go to the tensor cores; so do rows too long for one GEMV CTA (k > 32768)
 static bool use_mmq(int type, int64_t n, int64_t k) { return n >= mmq_min_batch() || gemv_max_cols(type, k) < 1; }
@@ -440,8 +474,7 @@ static size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 // the bus inside the call.  Pageable memory (or B200_HOST_ZEROCOPY=0) takes the staged copy.  n <= 8 only: the
 // tensor-core path reads x more than once.
 static const float * host_x_device_alias(const float * x_host, int64_t n) {
-    const char * e = getenv("B200_HOST_ZEROCOPY");
-    if ((e && *e && atoi(e) == 0) || n >= mmq_min_batch()) return nullptr;
+    if (env_knob("B200_HOST_ZEROCOPY", 1) == 0 || n >= mmq_min_batch()) return nullptr;
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, x_host) != cudaSuccess) {
         cudaGetLastError();
@@ -539,8 +572,7 @@ int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W,
 // group pairs by expert (one pass over an expert's weights per 4 pairs) when experts are shared: at least two pairs per
 // expert on average, the 4-column GEMV shape exists for this k; B200_MMID_GROUP=0 never, =2 whenever pairs >= 2
 static bool use_mmid_groups(int type, int64_t k, int64_t n_expert, int64_t npairs) {
-    const char * e = getenv("B200_MMID_GROUP");
-    const int    v = e && *e ? atoi(e) : 1;
+    const int    v = env_knob("B200_MMID_GROUP", 1);
     if (v == 0 || k <= fused_quant_max_k() || use_inlane_quant()) return false;
     if (n_expert > 1024 || npairs > INT32_MAX / 8 || gemv_max_cols(type, k) < 4) return false;
     return v == 2 ? npairs >= 2 : npairs >= 2 * n_expert;      // measured cross-over (profiles/r01/mmid_bench_v1.log)

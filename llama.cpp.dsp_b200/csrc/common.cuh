@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/b200_qmm.h"
 
 namespace b200 {
@@ -38,6 +40,25 @@ constexpr uint32_t IQ4NL_T3 = 0x71594535u;  //   53   69   89  113
 extern thread_local char g_last_cuda_error[256];
 void note_launch();
 int  check_cuda(cudaError_t e, const char * what);
+// per-DEVICE launch state: a kernel's dynamic shared-memory limit is an attribute of the function in one device's
+// context, and one process may drive several B200s (the ggml plug-in registers B200_0..7), so both are keyed by the
+// current device (the reference keeps shmem_limit_raised[GGML_CUDA_MAX_DEVICES] for the same reason, mmq.cuh:2793)
+constexpr int MAX_DEVICES = 64;
+int current_device();                 // cudaGetDevice, -1 on failure
+int sm_count_current_device();        // cached per device; 0 on failure
+int env_knob(const char * name, int dflt);   // integer environment knob, read ONCE per process per name
+
+// raise `kern`'s dynamic shared-memory limit once per device (thread-safe: setting it twice is harmless)
+#define B200_SMEM_ATTR_ONCE(kern, bytes)                                                                          \
+    do {                                                                                                          \
+        static std::atomic<uint64_t> done_{0};                                                                    \
+        const int dev_ = ::b200::current_device();                                                                \
+        if (dev_ < 0 || dev_ >= ::b200::MAX_DEVICES) return B200_ERR_CUDA;                                        \
+        if (!(done_.load(std::memory_order_acquire) >> dev_ & 1)) {                                               \
+            B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (bytes))); \
+            done_.fetch_or(uint64_t(1) << dev_, std::memory_order_release);                                       \
+        }                                                                                                         \
+    } while (0)
 
 #define B200_CUDA_TRY(expr)                                        \
     do {                                                           \

@@ -69,7 +69,7 @@ size_t  mmid_plan_bytes(int64_t npairs, int64_t n_expert);
 int64_t mmid_max_items(int64_t npairs, int64_t n_expert);
 int     launch_mmid_plan(const int32_t * ids, int64_t ids_row_stride, int64_t n_tokens, int64_t n_used, int64_t n_expert,
                          void * plan, cudaStream_t stream);
-size_t gemv_q8_smem_bytes(int64_t k, int ncols);
+void   gemv_trace_set(void * base, long long launches);   // profiling aid (tools/gemv_trace.py)
 int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring
 int    launch_gemv(const gemv_args & a, cudaStream_t stream);
 

@@ -1014,10 +1014,7 @@ static encode_tiled_fn get_encode_tiled() {
     return fn;
 }
 
-static int env_flag(const char * name, int dflt) {
-    const char * e = getenv(name);
-    return e && *e ? atoi(e) : dflt;
-}
+static int env_flag(const char * name, int dflt) { return env_knob(name, dflt); }
 
 // row-major int8 matrix [rows][kp] -> tiles of box_rows x 128 bytes, 128-byte swizzle, zero fill outside
 static int make_map(CUtensorMap * map, const void * base, int64_t rows, int64_t kp, int box_rows) {
@@ -1075,8 +1072,7 @@ static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB,
 template <int BN>
 static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
                          int mtiles, cudaStream_t stream) {
-    const char * e   = getenv("B200_MMQ_EPI");
-    const int    epi = MMQ_KC > 256 ? 0 : (e && *e ? atoi(e) : MMQ_EPI_DEFAULT);
+    const int    epi = MMQ_KC > 256 ? 0 : env_flag("B200_MMQ_EPI", MMQ_EPI_DEFAULT);
     switch (epi) {
         case 0: return launch_mmq_bn_epi<BN, 0>(mapA, mapB, a, mapAx, mtiles, stream);
         case 1: return launch_mmq_bn_epi<BN, 1>(mapA, mapB, a, mapAx, mtiles, stream);
@@ -1086,12 +1082,8 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
 template <int BN, int EPI>
 static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
                              int mtiles, cudaStream_t stream) {
-    static bool attr_set = false;
     auto kern = k_mmq<BN, EPI>;
-    if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_shape<BN>::SMEM));
-        attr_set = true;
-    }
+    B200_SMEM_ATTR_ONCE(kern, mmq_shape<BN>::SMEM);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) mtiles, (unsigned) ((a.n + BN - 1) / BN), (unsigned) (a.ksplit > 1 ? a.ksplit : 1));
     cfg.blockDim         = dim3(mmq_shape<BN>::THREADS, 1, 1);
@@ -1115,12 +1107,8 @@ static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB,
 // persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
                                  const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
-    static bool attr_set = false;
     auto kern = k_mmq_p<MMQ_EPI_DEFAULT>;
-    if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_pshape::SMEM));
-        attr_set = true;
-    }
+    B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
     mmq_pargs p;
     p.ntn = (a.n + 255) / 256;
     p.pf  = env_flag("B200_MMQ_PF", 0);   // measured: no gain at 4, 8, 16 (profiles/r01/pp_sweep_l2_lookahead.log)
@@ -1152,11 +1140,7 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
 }
 
 static int launch_mmq_pair(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_mmq_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, mmq_pair_shape::SMEM));
-        attr_set = true;
-    }
+    B200_SMEM_ATTR_ONCE(k_mmq_pair, mmq_pair_shape::SMEM);
     cudaLaunchConfig_t cfg = {};
     const unsigned mt = (unsigned) ((a.m + MMQ_BM - 1) / MMQ_BM);
     cfg.gridDim          = dim3((mt + 1) / 2 * 2, (unsigned) ((a.n + mmq_pair_shape::BN - 1) / mmq_pair_shape::BN), 1);
@@ -1193,32 +1177,26 @@ static int launch_quantize_x8(const float * x, int64_t x_stride, int8_t * Q, flo
 
 // split-K decision: two K halves when one would leave more than half of the SMs without a tile (B200_MMQ_KSPLIT=1/2 forces)
 static int mmq_ksplit(int64_t tiles, int64_t nch, int sm_count, bool allowed) {
-    const char * e = getenv("B200_MMQ_KSPLIT");
+    const int e = env_flag("B200_MMQ_KSPLIT", 0);
     if (!allowed || nch < 4) return 1;
-    if (e && *e) return atoi(e) == 2 ? 2 : 1;
+    if (e) return e == 2 ? 2 : 1;
     return tiles * 2 <= sm_count ? 2 : 1;
 }
 
 int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
     if (m == 0 || n == 0) return B200_OK;
-    static int sm_count = 0;
-    if (!sm_count) {
-        int dev = 0;
-        B200_CUDA_TRY(cudaGetDevice(&dev));
-        B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int sm_count = sm_count_current_device();
+    if (!sm_count) return B200_ERR_CUDA;
     const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
     int8_t * Q  = (int8_t *) workspace;
     float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
     // tile width: 256 columns (the tensor core takes ~120 clocks per instruction whether N is 128 or 256, see
     // profiles/r01/mmq_trace_v1.log) unless n is small; shapes with few tiles split K in two instead of narrowing tiles
     const int64_t mt = (m + MMQ_BM - 1) / MMQ_BM;
-    const char *  e  = getenv("B200_MMQ_BN");
-    int bn = e && atoi(e) > 0 ? atoi(e) : (n <= 128 ? 128 : 256);
+    int bn = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
     // CTA pairs (tcgen05 cta_group::2): B200_MMQ_PAIR=1
-    const char * pe = getenv("B200_MMQ_PAIR");
-    const bool   pair = pe && atoi(pe) == 1 && n > 128 && mt >= 2;
+    const bool   pair = env_flag("B200_MMQ_PAIR", 0) == 1 && n > 128 && mt >= 2;
     if (pair) bn = 256;
     const bool aligned   = m % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t) dst % 16 == 0;
     const bool can_split = !pair && mmq_nplanes(type) == 1 && aligned;
@@ -1279,12 +1257,8 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
                      const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
                      cudaStream_t stream) {
     if (nmat == 0 || n == 0) return B200_OK;
-    static int sm_count = 0;
-    if (!sm_count) {
-        int dev = 0;
-        B200_CUDA_TRY(cudaGetDevice(&dev));
-        B200_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int sm_count = sm_count_current_device();
+    if (!sm_count) return B200_ERR_CUDA;
     const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
     int8_t * Q  = (int8_t *) workspace;
     float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
@@ -1294,8 +1268,7 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
         total_mt += (m[i] + MMQ_BM - 1) / MMQ_BM;
         can_split = can_split && m[i] % 4 == 0 && dst_stride[i] % 4 == 0 && (uintptr_t) dst[i] % 16 == 0;
     }
-    const char * e  = getenv("B200_MMQ_BN");
-    const int    bn = e && atoi(e) > 0 ? atoi(e) : (n <= 128 ? 128 : 256);
+    const int    bn = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
     const int    ksplit = mmq_ksplit(total_mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
     {
         mmq_zero z = {};

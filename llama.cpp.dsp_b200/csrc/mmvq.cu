@@ -744,21 +744,18 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-static int env_int(const char * name, int dflt) {
-    const char * s = getenv(name);
-    return s && *s ? atoi(s) : dflt;
-}
+static int env_int(const char * name, int dflt) { return env_knob(name, dflt); }
 
-// tools/gemv_trace.py, tools/layer_trace.py: B200_GEMV_TRACE_PTR = base pointer, one slab of 4096 x 8 stamps per GEMV
-// launch, in launch order across all kernel variants, B200_GEMV_TRACE_LAUNCHES slabs in all (0 rewinds the counter)
+// tools/gemv_trace.py, tools/layer_trace.py (b200_debug_gemv_trace): base pointer + number of slabs; one slab of
+// 4096 x 8 stamps per GEMV launch, in launch order across all kernel variants
+static unsigned long long * g_trace_base = nullptr;
+static long long            g_trace_cap = 0, g_trace_seq = 0;
+void gemv_trace_set(void * base, long long launches) {
+    g_trace_base = (unsigned long long *) base, g_trace_cap = launches, g_trace_seq = 0;
+}
 static unsigned long long * next_trace_slab() {
-    static long long seq = 0;
-    const char * tp = getenv("B200_GEMV_TRACE_PTR");
-    if (!tp) return nullptr;
-    const long long cap = env_int("B200_GEMV_TRACE_LAUNCHES", 0);
-    if (cap == 0) seq = 0;
-    if (seq >= cap) return nullptr;
-    return (unsigned long long *) strtoull(tp, nullptr, 0) + (size_t) (seq++) * 4096 * 8;
+    if (!g_trace_base || g_trace_seq >= g_trace_cap) return nullptr;
+    return g_trace_base + (size_t) (g_trace_seq++) * 4096 * 8;
 }
 
 struct gemv_plan {
@@ -837,8 +834,6 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
     }
 }
 
-size_t gemv_q8_smem_bytes(int64_t k, int ncols) { (void) k, (void) ncols; return 0; }
-
 int gemv_max_cols(int type, int64_t k) {
     gemv_plan P;
     for (int n = 4; n >= 1; n--)
@@ -846,19 +841,10 @@ int gemv_max_cols(int type, int64_t k) {
     return 0;
 }
 
-static int g_sm_count = 0;
-
 template <int TYPE, int NCOLS, int V, int MINB>
 static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaStream_t stream) {
-    static bool attr_set = false;
     auto kern = k_gemv<TYPE, NCOLS, V, MINB>;
-    if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int) (MINB == 2 ? SMEM_2CTA : SMEM_1CTA)));
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                           cudaSharedmemCarveoutMaxShared));
-        attr_set = true;
-    }
+    B200_SMEM_ATTR_ONCE(kern, MINB == 2 ? SMEM_2CTA : SMEM_1CTA);
     gemv_kargs a;
     a.W = g.W, a.w_row_stride = g.w_row_stride, a.w_expert_stride = g.w_expert_stride;
     a.x = g.x, a.x_col_stride = g.x_col_stride, a.xq = g.xq;
@@ -903,11 +889,8 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
 
 template <int TYPE, int NCOLS>
 static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
-    if (!g_sm_count) {
-        int dev = 0;
-        B200_CUDA_TRY(cudaGetDevice(&dev));
-        B200_CUDA_TRY(cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int g_sm_count = sm_count_current_device();
+    if (!g_sm_count) return B200_ERR_CUDA;
     const int     row_bytes  = (int) (g.k / type_block_elems(TYPE)) * type_block_bytes(TYPE);
     const bool    contiguous = g.w_row_stride == row_bytes;
     const int64_t pairs      = g.it_hdr ? g.items_expected : g.ids ? g.npairs : 1;

@@ -26,7 +26,7 @@ EXPORTS = [
     "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mmq_chunk", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
     "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
-    "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle",
+    "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
 ]
 
 
@@ -96,6 +96,9 @@ def lib():
     L.b200_ipc_get_handle.argtypes = [vp, vp, C.POINTER(i64)]
     L.b200_ipc_open_handle.argtypes = [vp, i64, C.POINTER(vp)]
     L.b200_ipc_close_handle.argtypes = [vp, i64]
+    L.b200_reload_env.restype = None
+    L.b200_debug_gemv_trace.restype = None
+    L.b200_debug_gemv_trace.argtypes = [vp, i64]
     _lib = L
     return L
 
@@ -111,6 +114,21 @@ def check(status):
 
 def row_size(t, k):
     return k // BLOCK[t] * TYPE_SIZE[t]
+
+
+def reload_env():
+    """B200_* knobs are cached by the library at first use; call this after changing os.environ"""
+    lib().b200_reload_env()
+
+
+def setenv(**knobs):
+    """set (value) or remove (None) B200_* knobs and have the library read them again"""
+    for k, v in knobs.items():
+        if v is None:
+            os.environ.pop(k, None)
+        else:
+            os.environ[k] = str(v)
+    reload_env()
 
 
 def launch_count():

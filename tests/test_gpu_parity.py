@@ -24,6 +24,13 @@ def qmm():
     return q
 
 
+@pytest.fixture(autouse=True)
+def _knobs_reread_after_each_test(qmm):
+    """the library caches B200_* knobs; monkeypatch restores the environment at teardown, so have them read again"""
+    yield
+    qmm.reload_env()
+
+
 def dev(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
@@ -188,6 +195,7 @@ def test_mmq_split_k_is_exact_and_deterministic(qmm, monkeypatch, name, t, m, k,
     plane = qmm.build_plane(t, dev(w), m, k)
     xd = dev(x)
     monkeypatch.setenv("B200_MMQ_KSPLIT", "2")
+    qmm.reload_env()
     out = torch.full((n, m), 7.0, device="cuda")           # stale contents must not leak into the sum
     got = qmm.mul_mat_mmq(t, plane, xd, m, k, out=out).clone()
     for _ in range(3):
@@ -195,6 +203,7 @@ def test_mmq_split_k_is_exact_and_deterministic(qmm, monkeypatch, name, t, m, k,
         assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k, out=out), got)
     assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
     monkeypatch.setenv("B200_MMQ_KSPLIT", "1")
+    qmm.reload_env()
     one = qmm.mul_mat_mmq(t, plane, xd, m, k)
     assert qref.nmse(one.cpu().numpy(), got.cpu().numpy()) < 1e-11
 
@@ -215,6 +224,7 @@ def test_mmq_q8_0_plane_split_equals_accumulate_pass(qmm, monkeypatch, m, k, n):
     out.fill_(-1.0)
     assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k, out=out), got)
     monkeypatch.setenv("B200_MMQ_PLANE_SPLIT", "0")
+    qmm.reload_env()
     assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
     assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
 
@@ -233,8 +243,10 @@ def test_mmq_persistent_schedule(qmm, monkeypatch, name, t, m, k, n):
     got = qmm.mul_mat_mmq(t, plane, xd, m, k).clone()
     assert qref.nmse(qref.mul_mat_plane(t, w, x, m, k), got.cpu().numpy()) < NMSE_TIGHT
     monkeypatch.setenv("B200_MMQ_TAIL_HALVES", "0")
+    qmm.reload_env()
     assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
     monkeypatch.setenv("B200_MMQ_PERSIST", "0")
+    qmm.reload_env()
     assert torch.equal(qmm.mul_mat_mmq(t, plane, xd, m, k), got)
 
 
@@ -339,11 +351,13 @@ def test_mul_mat_id_grouped_by_expert(qmm, monkeypatch, name, t, n_expert, n_use
     ids = ids_full[:, :n_used]
     wd, bd = dev(w), dev(b)
     monkeypatch.setenv("B200_MMID_GROUP", "2")
+    qmm.reload_env()
     out = torch.full((n_tokens, n_used, m), 5.0, device="cuda")
     got = qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert, out=out).clone()
     for _ in range(3):
         assert torch.equal(qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert), got)
     monkeypatch.setenv("B200_MMID_GROUP", "0")
+    qmm.reload_env()
     plain = qmm.mul_mat_id(t, wd, bd, ids_dev, m, k, n_expert)
     g = got.cpu().numpy()
     assert qref.nmse(qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "q8_1"), g) < NMSE_TIGHT
@@ -454,6 +468,7 @@ def test_host_activations_zero_copy_equals_staged_copy(qmm, monkeypatch, pinned)
     want = qmm.mul_mat_multi([t for t, _ in spec], ws, xh.cuda(), [m for _, m in spec], k)
     for zc in ("1", "0"):
         monkeypatch.setenv("B200_HOST_ZEROCOPY", zc)
+        qmm.reload_env()
         outs = [torch.full((n, m), float("nan")) for _, m in spec]
         one = torch.full((n, 512), float("nan"))
         if pinned:                                              # results: copy kernel into pinned memory / cudaMemcpyAsync

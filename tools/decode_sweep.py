@@ -58,6 +58,7 @@ def main():
                 os.environ.pop(kn)
         for kn, v in knobs.items():
             os.environ[kn] = v
+        qmm.reload_env()
 
         def step():
             for call, x in calls:

@@ -90,6 +90,7 @@ def main():
                         os.environ.pop(kn, None)
                     for kn, v in cfg.items():
                         os.environ[kn] = str(v)
+                    qmm.reload_env()
                     try:
                         us = time_gemv(t, m, k, n, ws)
                     except Exception as e:  # noqa: BLE001

@@ -35,14 +35,13 @@ def run():
 run()
 torch.cuda.synchronize()
 trace = torch.zeros((launches, 4096, 8), dtype=torch.int64, device="cuda")
-os.environ["B200_GEMV_TRACE_PTR"] = hex(trace.data_ptr())
-os.environ["B200_GEMV_TRACE_LAUNCHES"] = str(launches)
+qmm.lib().b200_debug_gemv_trace(trace.data_ptr(), launches)
 s = torch.cuda.Stream()
 g = torch.cuda.CUDAGraph()
 with torch.cuda.stream(s):
     with torch.cuda.graph(g, stream=s):
         run()
-os.environ["B200_GEMV_TRACE_LAUNCHES"] = "0"
+qmm.lib().b200_debug_gemv_trace(None, 0)
 for _ in range(3):
     g.replay()
 torch.cuda.synchronize()

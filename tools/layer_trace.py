@@ -45,12 +45,11 @@ g = torch.cuda.CUDAGraph()
 with torch.cuda.stream(s):
     with torch.cuda.graph(g, stream=s):
         run(0, 8 * 4)
-        os.environ["B200_GEMV_TRACE_PTR"] = hex(trace.data_ptr())
-        os.environ["B200_GEMV_TRACE_LAUNCHES"] = str(nl)
+        qmm.lib().b200_debug_gemv_trace(trace.data_ptr(), nl)
         before = qmm.launch_count()
         run(8 * 4, len(calls))
         traced = qmm.launch_count() - before
-        os.environ["B200_GEMV_TRACE_LAUNCHES"] = "0"
+        qmm.lib().b200_debug_gemv_trace(None, 0)
 for _ in range(3):
     g.replay()
 torch.cuda.synchronize()

@@ -36,6 +36,7 @@ for label, m, k, bcast in (("gate/up", 14336, 4096, True), ("down", 4096, 14336,
         ref = None
         for mode in modes:
             os.environ["B200_MMID_GROUP"] = mode
+            qmm.reload_env()
             s = torch.cuda.Stream()
             with torch.cuda.stream(s):
                 for w in copies:

@@ -44,6 +44,7 @@ for name in ("q4_K", "q6_K"):
             out = torch.empty((n, m), device="cuda")
             for bn in ("128", "256"):
                 os.environ["B200_MMQ_BN"] = bn
+                qmm.reload_env()
                 for _ in range(3):
                     qmm.mul_mat_mmq(t, plane, x, m, k, out=out)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -56,3 +57,4 @@ for name in ("q4_K", "q6_K"):
                 print("%-5s m=%5d k=%5d n=%3d BN=%s: %8.1f us  %7.1f TOP/s" % (name, m, k, n, bn, us, 2.0 * m * n * k / us / 1e6),
                       flush=True)
             os.environ.pop("B200_MMQ_BN", None)
+            qmm.reload_env()

@@ -56,6 +56,7 @@ def main():
                 os.environ.pop(kn)
         for kn, v in cfg.items():
             os.environ[kn] = v
+        qmm.reload_env()
 
         def step():
             for call, x in calls:
