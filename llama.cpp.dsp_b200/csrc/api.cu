@@ -250,7 +250,7 @@ static bool use_mmq(int type, int64_t n, int64_t k) { return n >= mmq_min_batch(
 
 size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     if (!weight_type(type) || k <= 0 || n <= 0 || m <= 0) return 0;
-    if (use_mmq(type, n, k)) return ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k)) + mmq_workspace_bytes(n, k);
+    if (use_mmq(type, n, k)) return ws_align(mmq_plane_bytes(type, m, k)) + mmq_workspace_bytes(n, k);
     if (use_fused_quant(n, k)) return 0;
     return (size_t) n * q8_soa_layout(k).bytes;
 }
@@ -259,14 +259,14 @@ int    b200_mmq_min_batch(void) { return mmq_min_batch(); }
 int    b200_mmq_chunk(void) { return mmq_chunk(); }
 size_t b200_mmq_plane_size(int type, int64_t m, int64_t k) {
     if (!weight_type(type) || m < 0 || k < 0 || k % blck_of(type) != 0) return 0;
-    return mmq_nplanes(type) * mmq_plane_bytes(m, k);
+    return mmq_plane_bytes(type, m, k);
 }
 int b200_mmq_build_plane(int type, const void * W, int64_t w_row_stride, void * plane, size_t plane_bytes, int64_t m,
                          int64_t k, b200_stream_t stream) {
     int st = check_weights(type, W, w_row_stride, k);
     if (st != B200_OK) return st;
     if (m < 0) return B200_ERR_SHAPE;
-    if (!plane || plane_bytes < mmq_nplanes(type) * mmq_plane_bytes(m, k)) return B200_ERR_WORKSPACE;
+    if (!plane || plane_bytes < mmq_plane_bytes(type, m, k)) return B200_ERR_WORKSPACE;
     if ((uintptr_t) plane % 256 != 0) return B200_ERR_ALIGNMENT;
     return launch_plane_build(type, W, w_row_stride, plane, m, k, (cudaStream_t) stream);
 }
@@ -294,14 +294,15 @@ int b200_mul_mat_mmq_multi(int nmat, const int * types, const void * const * pla
     if (n < 0 || k <= 0 || x_row_stride < k || n > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
     if (!workspace || workspace_bytes < mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
     if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
-    // single-plane matrices share launches; two-plane types (Q8_0) take the two-pass path one by one
+    // matrices of one precision class (same number of weight / activation planes) share launches and one quantizer pass
     const void * pl[64];
     float *      ds[64];
     int64_t      st_[64], ms[64];
-    int cnt = 0;
+    int cnt = 0, cls_type = 0;
+    auto cls = [](int t) { return mmq_nplanes(t) * 4 + mmq_xplanes(t); };
     auto flush = [&]() -> int {
         if (!cnt) return B200_OK;
-        const int st = launch_mmq_multi(cnt, pl, x, x_row_stride, ds, st_, ms, n, k, workspace, (cudaStream_t) stream);
+        const int st = launch_mmq_multi(cls_type, cnt, pl, x, x_row_stride, ds, st_, ms, n, k, workspace, (cudaStream_t) stream);
         cnt = 0;
         return st;
     };
@@ -310,19 +311,13 @@ int b200_mul_mat_mmq_multi(int nmat, const int * types, const void * const * pla
         if (m[i] < 0 || m[i] > INT32_MAX || dst_row_stride[i] < m[i]) return B200_ERR_SHAPE;
         if (m[i] == 0) continue;
         if (!planes[i] || (uintptr_t) planes[i] % 256 != 0 || !dst[i]) return B200_ERR_ALIGNMENT;
-        if (mmq_nplanes(types[i]) != 1) {
-            int st = flush();
-            if (st != B200_OK) return st;
-            st = launch_mmq(types[i], planes[i], x, x_row_stride, dst[i], dst_row_stride[i], m[i], n, k, workspace,
-                            (cudaStream_t) stream);
-            if (st != B200_OK) return st;
-            continue;
-        }
-        pl[cnt] = planes[i], ds[cnt] = dst[i], st_[cnt] = dst_row_stride[i], ms[cnt] = m[i];
-        if (++cnt == 64) {
+        if (cnt && (cls(types[i]) != cls(cls_type) || cnt == 64)) {
             const int st = flush();
             if (st != B200_OK) return st;
         }
+        cls_type = types[i];
+        pl[cnt] = planes[i], ds[cnt] = dst[i], st_[cnt] = dst_row_stride[i], ms[cnt] = m[i];
+        cnt++;
     }
     return flush();
 }
@@ -342,7 +337,7 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
         return B200_OK;
     }
     if (use_mmq(type, n, k)) {  // tensor-core path with a transient plane carved from the workspace
-        const size_t pb = ws_align(mmq_nplanes(type) * mmq_plane_bytes(m, k));
+        const size_t pb = ws_align(mmq_plane_bytes(type, m, k));
         if (!workspace || workspace_bytes < pb + mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
         if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
         st = launch_plane_build(type, W, w_row_stride, workspace, m, k, stream);

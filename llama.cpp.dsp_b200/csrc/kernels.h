@@ -73,17 +73,19 @@ void   gemv_trace_set(void * base, long long launches);   // profiling aid (tool
 int    gemv_max_cols(int type, int64_t k);   // how many columns fit in shared memory next to a minimal ring
 int    launch_gemv(const gemv_args & a, cudaStream_t stream);
 
-// ---- batched matmul on tcgen05 (mmq.cu): int8 "prefill plane" of a weight tensor + the GEMM that consumes it
-size_t mmq_plane_bytes(int64_t m, int64_t k);
+// ---- batched matmul on tcgen05 (mmq.cu): int8 "prefill plane(s)" of a weight tensor + the GEMM that consumes them
+int    mmq_nplanes(int type);   // int8 planes per weight tensor (2 for Q8_0: value + residual)
+int    mmq_xplanes(int type);   // int8 planes of the activations multiplied with this type (2 for Q4_0 / Q8_0)
+size_t mmq_plane_bytes(int type, int64_t m, int64_t k);   // all planes of one tensor + their scales
 int    mmq_chunk();   // elements of k per scale (build-time: 256 or 512)
 size_t mmq_workspace_bytes(int64_t n, int64_t k);
-// several single-plane matrices of one k against the same activations: one activation quantizer, shared GEMM launches
-int    launch_mmq_multi(int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
-                        const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
-                        cudaStream_t stream);
 int    launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
                           cudaStream_t stream);
-int    mmq_nplanes(int type);   // int8 planes per weight tensor (2 for Q8_0: value + residual)
+// several matrices of one precision class (mmq_nplanes, mmq_xplanes of `type`) and one k against the same activations:
+// one activation quantizer, shared GEMM launches
+int    launch_mmq_multi(int type, int nmat, const void * const * planes, const float * x, int64_t x_stride,
+                        float * const * dst, const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k,
+                        void * workspace, cudaStream_t stream);
 int    launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                   int64_t n, int64_t k, void * workspace, cudaStream_t stream);
 

@@ -9,15 +9,26 @@
 //  * The reference applies one fp32 scale per 32 weights x one per 32 activations after EVERY K=32 mma.sync, on CUDA
 //    cores.  On B200 an M128 x N256 x K32 int8 MMA takes ~128 clocks while scaling its 32768 outputs takes ~1500 FMA-pipe
 //    clocks, so that scheme is capped near 10 % of the tensor peak.  Here scales are made SEPARABLE over
-//    256-element chunks of k: weights are re-expressed once per tensor as an int8 "prefill plane" with one fp32 scale
-//    per (row, chunk) -- w ~= s[i][c] * P[i][k] -- and activations are quantized with one scale per (column, chunk) --
-//    x ~= t[j][c] * Q[j][k], the same granularity ggml-cpu's q8_K uses for the K-quants (ggml-common.h:329-334).  Eight
-//    K=32 MMAs accumulate a chunk in TMEM as int32; the epilogue then does acc[i][j] += s[i][c] * t[j][c] * D[i][j] in
-//    fp32 registers while the tensor core works on the next chunk in the other TMEM buffer.
-//    Cost: +1 byte of HBM per weight for the plane (built lazily, cached by the caller; B200 has 180 GB) and a rounding
-//    error of ~3e-5 .. 1e-4 NMSE against ggml-cpu (bar 5e-4; tests/test_gpu_parity.py measures it).
-//  * Warp roles (one CTA per SM, 320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA
-//    issuer, warps 2..9 = epilogue (each owns 32 TMEM lanes x half of the tile's columns).
+//    chunks of MMQ_KC = 256 elements of k: weights are re-expressed once per tensor as an int8 "prefill plane" with one
+//    fp32 scale per (row, chunk) -- w ~= s[i][c] * P[i][k] -- and activations are quantized with one scale per (column,
+//    chunk) -- x ~= t[j][c] * Q[j][k], exactly the granularity of ggml-cpu's q8_K, which is what ggml-cpu multiplies the
+//    K-quants and IQ4_XS with (ggml-common.h:329-334, ggml-cpu.c:282-297).  Eight K=32 MMAs accumulate a chunk in TMEM as
+//    int32; the epilogue then does acc[i][j] += s[i][c] * t[j][c] * D[i][j] in fp32 registers while the tensor core works
+//    on the next chunk in the other TMEM buffer.
+//  * Precision where a single int8 per chunk is not enough comes from RESIDUAL planes laid side by side along k, so the
+//    GEMM stays ONE pass over a longer "virtual k":
+//      - Q8_0 weights keep two planes (value + residual of the first rounding): their per-32 fp16 scales have more dynamic
+//        range than one int8 per 256 can hold.
+//      - activations multiplied with the 32-block types (Q4_0, Q8_0) get two planes as well: ggml-cpu quantizes those
+//        activations per 32 (q8_0), so one scale per 256 is 8x coarser than the reference wherever a chunk holds an outlier
+//        channel; value + residual is ~15 bits per element and holds the harness bound on such data
+//        (profiles/r02/mmq_nmse_schemes_cpu_study.log).
+//    The kernel walks a short list of segments (weight-plane chunk offset, activation-plane chunk offset):
+//      K-quants / IQ4_XS: W0.X0      Q4_0: W0.X0 + W0.X1      Q8_0: W0.X0 + W0.X1 + W1.X0   (residual x residual dropped)
+//    Cost: +1 byte of HBM per weight for the plane (+2 for Q8_0; built lazily, cached by the caller) and a rounding error
+//    of 4e-5 .. 1.7e-4 NMSE against ggml-cpu (bar 5e-4; tests/test_gpu_parity.py measures it).
+//  * Warp roles (one CTA per SM, 576 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA
+//    issuer, warps 2..17 = epilogue (each owns 32 TMEM lanes x a quarter of the tile's columns).
 #include "actquant.cuh"
 #include "dequant.cuh"
 #include "kernels.h"
@@ -32,9 +43,13 @@ namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ layouts
 #ifndef B200_MMQ_KC
-#define B200_MMQ_KC 512
+#define B200_MMQ_KC 256
 #endif
-constexpr int MMQ_KC = B200_MMQ_KC;   // scale granularity along k (one TMEM accumulation chunk): 256 or 512
+// scale granularity along k (one TMEM accumulation chunk).  256 = ggml-cpu's q8_K block, the default: parity with
+// ggml-cpu holds on any data.  512 (make EXTRA=-DB200_MMQ_KC=512) halves the TMEM read-outs (+9 % pp512 in round 1) but is
+// 2x coarser than the reference: NMSE vs ggml-cpu 7.8e-4 with outlier channels, above the 5e-4 bar
+// (profiles/r02/mmq_nmse_schemes_cpu_study.log) -- not for production use.
+constexpr int MMQ_KC = B200_MMQ_KC;
 constexpr int MMQ_BM = 128;   // rows of W per CTA tile (= TMEM lanes)
 constexpr int MMQ_BK = 128;   // int8 elements per shared-memory stage row (= one 128-byte swizzle atom)
 constexpr int MMQ_KBC = MMQ_KC / MMQ_BK;   // k-blocks (shared-memory stages) per chunk
@@ -48,33 +63,36 @@ int mmq_chunk() { return MMQ_KC; }
 static inline int64_t mmq_kpad(int64_t k) { return (k + MMQ_KC - 1) / MMQ_KC * MMQ_KC; }
 static inline size_t  align256(size_t v) { return (v + 255) & ~(size_t) 255; }
 
-// plane = [P: m x kpad int8, row-major][s: nchunks x mpad f32, chunk-major so that a tile's 128 row scales of one chunk
-// are one contiguous bulk copy]   (mpad = m rounded up to the tile height)
-static inline int64_t mmq_mpad(int64_t m) { return (m + MMQ_BM - 1) / MMQ_BM * MMQ_BM; }
-size_t mmq_plane_bytes(int64_t m, int64_t k) {
-    const int64_t kp = mmq_kpad(k);
-    return align256((size_t) m * kp) + align256((size_t) mmq_mpad(m) * (kp / MMQ_KC) * 4);
-}
-// Q8_0 keeps two planes (value + residual); everything else one
+// Q8_0 keeps two weight planes (value + residual); everything else one
 int mmq_nplanes(int type) { return type == B200_TYPE_Q8_0 ? 2 : 1; }
-// activation scratch = [Q: n x kpad int8][t: nchunks x npad f32]   (npad = n rounded up to 4: float4 loads)
+// activations against the 32-block types are quantized to two planes (value + residual), see the file header
+int mmq_xplanes(int type) { return type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 ? 2 : 1; }
+// weight plane(s) of one tensor = [P: m x (nwp * kpad) int8, row-major, plane p in columns [p * kpad, (p+1) * kpad)]
+//                                 [s: (nwp * nchunks) x mpad f32, chunk-major so that a tile's 128 row scales of one chunk
+//                                  are one contiguous bulk copy]   (mpad = m rounded up to the tile height)
+static inline int64_t mmq_mpad(int64_t m) { return (m + MMQ_BM - 1) / MMQ_BM * MMQ_BM; }
+size_t mmq_plane_bytes(int type, int64_t m, int64_t k) {
+    const int64_t kp = mmq_kpad(k), nwp = mmq_nplanes(type);
+    return align256((size_t) m * nwp * kp) + align256((size_t) mmq_mpad(m) * nwp * (kp / MMQ_KC) * 4);
+}
+// activation scratch = [Q: n x (nxp * kpad) int8][t: (nxp * nchunks) x npad f32]   (npad = n rounded up to 4)
 static inline int64_t mmq_npad(int64_t n) { return (n + 3) & ~(int64_t) 3; }
-size_t mmq_act_bytes(int64_t n, int64_t k) {
+size_t mmq_act_bytes(int64_t n, int64_t k, int nxp) {
     const int64_t kp = mmq_kpad(k);
-    return align256((size_t) n * kp) + align256((size_t) (kp / MMQ_KC) * mmq_npad(n) * 4);
+    return align256((size_t) n * nxp * kp) + align256((size_t) nxp * (kp / MMQ_KC) * mmq_npad(n) * 4);
 }
 
 // ------------------------------------------------------------------------------------------------ plane builder
 // One thread per (row, 32-element group): dequantize the group bit-exactly, find the chunk's amax over the 8 threads
-// of the chunk, re-quantize to int8 with s = amax / 127.
-// RESID: build the plane of the residual w - s0 * P0 left by a first plane (P0, S0): two int8 planes give ~15 bits
-// of weight precision, used for Q8_0 whose 8-bit blocks would otherwise lose their per-32 scales' dynamic range.
+// of the chunk, re-quantize to int8 with s = amax / 127.  P has row pitch ldp = nwp * kp; plane p occupies columns
+// [p * kp, (p+1) * kp) and scale rows [p * nch, (p+1) * nch).
+// RESID: build plane 1 = the residual w - s0 * P0 left by plane 0: two int8 planes give ~15 bits of weight precision,
+// used for Q8_0 whose 8-bit blocks would otherwise lose their per-32 scales' dynamic range.
 template <int TYPE, bool RESID>
 __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict__ w, int64_t w_stride,
                                                      int8_t * __restrict__ P, float * __restrict__ S, int64_t m, int64_t k,
-                                                     int64_t kp, int64_t mpad, const int8_t * __restrict__ P0,
-                                                     const float * __restrict__ S0) {
-    const int64_t gpr = kp / 32;
+                                                     int64_t kp, int64_t ldp, int64_t mpad) {
+    const int64_t gpr = kp / 32, nch = kp / MMQ_KC;
     const int64_t g   = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const bool    in  = g < gpr * m;
     const int64_t row = in ? g / gpr : 0;
@@ -87,8 +105,8 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
         for (int i = 0; i < 32; i++) v[i] = 0.f;
     }
     if (RESID && in) {
-        const float    s0 = S0[(gi / MMQ_G32) * mpad + row];
-        const int8_t * p0 = P0 + row * kp + gi * 32;
+        const float    s0 = S[(gi / MMQ_G32) * mpad + row];
+        const int8_t * p0 = P + row * ldp + gi * 32;
 #pragma unroll
         for (int i = 0; i < 32; i++) v[i] = __fsub_rn(v[i], __fmul_rn(s0, (float) p0[i]));
     }
@@ -110,14 +128,16 @@ __global__ void __launch_bounds__(256) k_plane_build(const uint8_t * __restrict_
         out[i] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (c & 0xff) << 16) |
                  ((uint32_t) (d & 0xff) << 24);
     }
-    uint4 * dst = reinterpret_cast<uint4 *>(P + row * kp + gi * 32);
+    uint4 * dst = reinterpret_cast<uint4 *>(P + row * ldp + (RESID ? kp : 0) + gi * 32);
     dst[0] = make_uint4(out[0], out[1], out[2], out[3]);
     dst[1] = make_uint4(out[4], out[5], out[6], out[7]);
-    if ((gi % MMQ_G32) == 0) S[(gi / MMQ_G32) * mpad + row] = s;
+    if ((gi % MMQ_G32) == 0) S[((RESID ? nch : 0) + gi / MMQ_G32) * mpad + row] = s;
 }
 
 // ------------------------------------------------------------------------------------------------ activation quantizer
-// One warp per (column j, chunk c): 8 floats per lane, t = amax / 127, Q = rint(x / t).
+// One warp per (column j, chunk c): KC/32 floats per lane, t = amax / 127, Q = rint(x / t).  NXP = 2 adds the residual
+// plane: r = x - t * Q (rounded per operation, like the plane builder), t1 = amax(r) / 127, Q1 = rint(r / t1), stored in
+// columns [kp, 2 kp) of the row and scale rows [nch, 2 nch).
 // Also zeroes the results of a split-K GEMM (mmq_zero: up to 4 dst matrices of n rows, m % 4 == 0, 16-byte aligned rows),
 // whose two K halves are then added with red.global.add -- two addends onto zero give the same bits in either order.
 struct mmq_zero {
@@ -126,6 +146,7 @@ struct mmq_zero {
     int64_t stride[4];   // elements between rows
     int64_t m[4];
 };
+template <int NXP>
 __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ x, int64_t x_stride, int8_t * __restrict__ Q,
                                                      float * __restrict__ Tt, int64_t n, int64_t k, int64_t kp,
                                                      int64_t npad, const mmq_zero z, bool vec) {
@@ -161,24 +182,32 @@ __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ 
 #pragma unroll
         for (int i = 0; i < PL; i++) v[i] = e0 + i < k ? xr[i] : 0.f;
     }
-    float amax = 0.f;
 #pragma unroll
-    for (int i = 0; i < PL; i++) amax = fmaxf(amax, fabsf(v[i]));
+    for (int pl = 0; pl < NXP; pl++) {
+        float amax = 0.f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-    const float t  = amax / 127.0f;
-    const float it = t > 0.f ? 1.0f / t : 0.f;
-    uint32_t o2[PL / 4];
+        for (int i = 0; i < PL; i++) amax = fmaxf(amax, fabsf(v[i]));
 #pragma unroll
-    for (int h = 0; h < PL / 4; h++) {
-        const int a = __float2int_rn(v[4 * h] * it), b = __float2int_rn(v[4 * h + 1] * it);
-        const int cc = __float2int_rn(v[4 * h + 2] * it), d = __float2int_rn(v[4 * h + 3] * it);
-        o2[h] = (uint32_t) (a & 0xff) | ((uint32_t) (b & 0xff) << 8) | ((uint32_t) (cc & 0xff) << 16) |
-                ((uint32_t) (d & 0xff) << 24);
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float t  = amax / 127.0f;
+        const float it = t > 0.f ? 1.0f / t : 0.f;
+        uint32_t o2[PL / 4];
+#pragma unroll
+        for (int h = 0; h < PL / 4; h++) {
+            int q[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                q[e] = __float2int_rn(v[4 * h + e] * it);
+                if (pl + 1 < NXP) v[4 * h + e] = __fsub_rn(v[4 * h + e], __fmul_rn(t, (float) q[e]));   // residual
+            }
+            o2[h] = (uint32_t) (q[0] & 0xff) | ((uint32_t) (q[1] & 0xff) << 8) | ((uint32_t) (q[2] & 0xff) << 16) |
+                    ((uint32_t) (q[3] & 0xff) << 24);
+        }
+        int8_t * qd = Q + j * (NXP * kp) + pl * kp + e0;
+        if (PL == 8) *reinterpret_cast<uint2 *>(qd) = make_uint2(o2[0], o2[1]);
+        else *reinterpret_cast<uint4 *>(qd) = make_uint4(o2[0], o2[1], o2[PL / 4 - 2], o2[PL / 4 - 1]);
+        if (lane == 0) Tt[(pl * nch + c) * npad + j] = t;
     }
-    if (PL == 8) *reinterpret_cast<uint2 *>(Q + j * kp + e0) = make_uint2(o2[0], o2[1]);
-    else *reinterpret_cast<uint4 *>(Q + j * kp + e0) = make_uint4(o2[0], o2[1], o2[PL / 4 - 2], o2[PL / 4 - 1]);
-    if (lane == 0) Tt[c * npad + j] = t;
 }
 
 // ------------------------------------------------------------------------------------------------ PTX helpers (sm_100a)
@@ -188,18 +217,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
             dst_smem),
         "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
-}
-// pull a tensor-map box into L2 only (no shared memory, nothing to wait for)
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap * map, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap * map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
@@ -356,13 +373,12 @@ struct mmq_kargs {
     const float * Tt;     // activation scales [nch][npad] (+ slack: tiles may overhang)
     float *       dst;    // [n][dst_stride], m contiguous
     int64_t       dst_stride;
-    int           m, n, nch, npad, mpad;
-    int           accumulate;   // dst += result (second plane of a two-plane weight)
-    int           plane_split;  // with ksplit = 2: grid.z selects the PLANE of a two-plane weight (Q8_0: value, residual;
-                                // second plane in mapAx.m[0] / Sx[0]) instead of a K half -- the same two addends as the
-                                // sequential accumulate pass, on twice as many SMs
-    int           ksplit;       // 1, or 2: grid.z halves of the chunk range, results added with red.global.add onto a
-                                // zeroed dst (few-tile shapes: m = 4096 at n = 512 fills 64 of 148 SMs otherwise)
+    int           m, n, nch, npad, mpad;   // nch = chunks per PLANE (kpad / MMQ_KC)
+    // virtual k: nseg segments of nch chunks each; segment s multiplies weight-plane chunks seg_a[s] + i with
+    // activation-plane chunks seg_b[s] + i  (W0.X0 | W0.X1 | W1.X0, see the file header)
+    int           nseg, seg_a[3], seg_b[3];
+    int           ksplit;       // 1, or 2: grid.z halves of the virtual chunk range, results added with red.global.add onto
+                                // a zeroed dst (few-tile shapes: m = 4096 at n = 512 fills 64 of 148 SMs otherwise)
     int           dbg;          // experiments (B200_MMQ_DEBUG): 1 = persistent kernel skips the second B box (wrong results,
                                 // 2/3 of the L2->SM traffic), 2 = every item reads the A tile of m-tile 0
     long long *   trace;        // -DB200_MMQ_TRACE builds only: 16 clock counters per CTA (tools/mmq_trace.py), else unused
@@ -378,6 +394,14 @@ struct mmq_kargs {
 struct mmq_maps3 {
     CUtensorMap m[3];
 };
+// virtual chunk -> (weight-plane chunk, activation-plane chunk)
+__device__ __forceinline__ void mmq_vchunk(const mmq_kargs & a, int vc, int & ac, int & bc) {
+    int seg = 0, i = vc;
+    if (i >= a.nch) seg = 1, i -= a.nch;
+    if (i >= a.nch) seg = 2, i -= a.nch;
+    ac = (seg == 0 ? a.seg_a[0] : seg == 1 ? a.seg_a[1] : a.seg_a[2]) + i;
+    bc = (seg == 0 ? a.seg_b[0] : seg == 1 ? a.seg_b[1] : a.seg_b[2]) + i;
+}
 
 // Role-level wait accounting (trace builds only): TW(slot, wait) adds the clocks spent in `wait` to counter `slot`.
 #ifdef B200_MMQ_TRACE
@@ -440,10 +464,9 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
         tile -= first;
     }
     const int m0 = tile * MMQ_BM, n0 = blockIdx.y * BN;
-    // this CTA's chunk range [cb, cb + nch): everything below counts chunks and k-blocks locally
-    if (a.plane_split && blockIdx.z == 1) pA = &mapAx.m[0], S = a.Sx[0];
-    const int cper = a.plane_split ? a.nch : (a.nch + a.ksplit - 1) / a.ksplit, cb = a.plane_split ? 0 : (int) blockIdx.z * cper;
-    const int nch = min(cper, a.nch - cb), nkb = MMQ_KBC * nch;
+    // this CTA's range [cb, cb + nch) of VIRTUAL chunks: everything below counts chunks and k-blocks locally
+    const int nvc = a.nseg * a.nch, cper = (nvc + a.ksplit - 1) / a.ksplit, cb = (int) blockIdx.z * cper;
+    const int nch = min(cper, nvc - cb), nkb = MMQ_KBC * nch;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
@@ -468,21 +491,24 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
     if (warp == 0) {
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
+            int ac = 0, bc = 0;
             for (int kb = 0; kb < nkb; kb++) {
-                if ((kb % MMQ_KBC) == 0) {                       // this chunk's scale vectors, ahead of its tiles
+                const int h = kb % MMQ_KBC;
+                if (h == 0) {                                    // this chunk's scale vectors, ahead of its tiles
                     const int c = kb / MMQ_KBC, b = c % SH::NSC;
+                    mmq_vchunk(a, cb + c, ac, bc);
                     TW(0, mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1));
                     const uint32_t sd = scales + b * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
-                    tma_load_1d(sd, S + (int64_t) (cb + c) * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
-                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) (cb + c) * a.npad + n0, BN * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd, S + (int64_t) ac * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * b);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) bc * a.npad + n0, BN * 4, bar_sfull + 8 * b);
                 }
                 const int s = kb % NS, ph = (kb / NS) & 1;
                 TW(1, mbar_wait(bar_empty + 8 * s, ph ^ 1));
                 const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
                 mbar_expect_tx(bar_full + 8 * s, SH::STAGE);
-                tma_load_2d(sa, pA, (MMQ_KBC * cb + kb) * MMQ_BK, m0, bar_full + 8 * s);
-                tma_load_2d(sb, &mapB, (MMQ_KBC * cb + kb) * MMQ_BK, n0, bar_full + 8 * s);
+                tma_load_2d(sa, pA, (MMQ_KBC * ac + h) * MMQ_BK, m0, bar_full + 8 * s);
+                tma_load_2d(sb, &mapB, (MMQ_KBC * bc + h) * MMQ_BK, n0, bar_full + 8 * s);
             }
 #ifdef B200_MMQ_TRACE
             if (a.trace) {
@@ -551,7 +577,7 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
                 if (j < a.n) {                                   // lanes = consecutive rows: coalesced
                     float * d = dstp + (int64_t) j * dstride + row;
                     if (a.ksplit > 1) atomicAdd(d, acc[i]);      // RED.ADD.F32: fire and forget
-                    else *d = a.accumulate ? acc[i] + *d : acc[i];
+                    else *d = acc[i];
                 }
             }
         }
@@ -581,7 +607,6 @@ __global__ void __launch_bounds__(mmq_shape<BN>::THREADS, 1) k_mmq(const __grid_
 // B tiles are always loaded as 128-row boxes (two per k-block for a 256-wide item), so one tensor map serves both widths;
 // the UMMA N comes from a per-item instruction descriptor; TMEM holds two 256-column accumulator buffers.
 struct mmq_pargs {
-    int pf;        // weight tiles are prefetched into L2 this many k-blocks ahead of their load (0 = off)
     int ntn;       // 256-wide n-tiles per m-tile
     int mtiles;    // m-tiles of all matrices of the launch
     int raster;    // 0: consecutive items walk n first, 1: m first (B200_MMQ_RASTER)
@@ -631,7 +656,7 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
     const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
                    bar_tempty = bar_tfull + 8 * NB, bar_sfull = bar_tempty + 8 * NB, bar_sempty = bar_sfull + 8 * NSC;
     const uint32_t scales = tiles + NS * SH::STAGE;
-    const int      nch = a.nch;
+    const int      nch = a.nseg * a.nch;                        // virtual chunks per item
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 1), mbar_init(bar_empty + 8 * s, 1);
@@ -673,24 +698,22 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 const bool     two = I.bn == 256 && !(a.dbg & 1);
                 const uint32_t stage_tx = SH::A_BYTES + (two ? 256u : 128u) * MMQ_BK, scale_tx = (MMQ_BM + (uint32_t) I.bn) * 4;
                 for (int c = 0; c < nch; c++) {
+                    int ac, bc;
+                    mmq_vchunk(a, c, ac, bc);
                     TW(0, mbar_wait(bar_sempty + 8 * sc, sc_ph ^ 1));  // this chunk's scale vectors, ahead of its tiles
                     const uint32_t sd = scales + sc * SH::SC_FLTS * 4;
                     mbar_expect_tx(bar_sfull + 8 * sc, scale_tx);
-                    tma_load_1d(sd, S + (int64_t) c * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * sc);
-                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + I.n0, I.bn * 4, bar_sfull + 8 * sc);
+                    tma_load_1d(sd, S + (int64_t) ac * mpad + m0, MMQ_BM * 4, bar_sfull + 8 * sc);
+                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) bc * a.npad + I.n0, I.bn * 4, bar_sfull + 8 * sc);
                     if (++sc == NSC) sc = 0, sc_ph ^= 1;
 #pragma unroll
                     for (int h = 0; h < MMQ_KBC; h++) {
                         TW(1, mbar_wait(bar_empty + 8 * st, st_ph ^ 1));
                         const uint32_t sa = tiles + st * SH::STAGE, sb = sa + SH::A_BYTES;
                         mbar_expect_tx(bar_full + 8 * st, stage_tx);
-                        tma_load_2d(sa, pA, (MMQ_KBC * c + h) * MMQ_BK, m0, bar_full + 8 * st);
-                        tma_load_2d(sb, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0, bar_full + 8 * st);
-                        // the weight plane is streamed from HBM once per n-tile: ask L2 for the tile `pf` k-blocks ahead
-                        // now, so that its load finds it there (activation tiles are L2-resident anyway)
-                        if (p.pf && MMQ_KBC * c + h + p.pf < MMQ_KBC * nch)
-                            tma_prefetch_2d(pA, (MMQ_KBC * c + h + p.pf) * MMQ_BK, m0);
-                        if (two) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (MMQ_KBC * c + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
+                        tma_load_2d(sa, pA, (MMQ_KBC * ac + h) * MMQ_BK, m0, bar_full + 8 * st);
+                        tma_load_2d(sb, &mapB, (MMQ_KBC * bc + h) * MMQ_BK, I.n0, bar_full + 8 * st);
+                        if (two) tma_load_2d(sb + 128 * MMQ_BK, &mapB, (MMQ_KBC * bc + h) * MMQ_BK, I.n0 + 128, bar_full + 8 * st);
                         if (++st == NS) st = 0, st_ph ^= 1;
                     }
                 }
@@ -793,7 +816,7 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 float *   d  = dstp + (int64_t) (I.n0 + col0) * dstride + row;
 #pragma unroll
                 for (int i = 0; i < 64; i++) {                   // lanes = consecutive rows: coalesced
-                    if (i < jn) *d = a.accumulate ? acc[i] + *d : acc[i];
+                    if (i < jn) *d = acc[i];
                     d += dstride;
                 }
             }
@@ -814,186 +837,6 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<512>(tmem);
-}
-
-// ------------------------------------------------------------------------------------------------ CTA-pair GEMM kernel
-// The same pipeline with tcgen05.mma.cta_group::2: two CTAs on neighbouring SMs (a cluster of 2 along m) execute ONE
-// M256 x N256 x K32 instruction per step.  Each CTA stages its own 128 weight rows and only HALF of the activation tile
-// (128 of the 256 columns); the tensor cores of both SMs read both halves.  Per CTA and 256-chunk that is 64 KB of
-// TMA writes + 64 KB of operand reads instead of 96 + 96 -- the single-CTA kernel above is bound by exactly that
-// shared-memory traffic (ncu: no pipe, L2 or DRAM above 40 %, MMA issue waiting on operands).
-// Roles: both CTAs run a TMA producer and the eight epilogue warps; only the leader (cluster rank 0) issues MMAs.
-//   full[s]   lives in the leader: 2 arrivals (one per producer) + the bytes of all four TMA boxes
-//   empty[s]  in each CTA, signalled by the leader's tcgen05.commit multicast
-//   tfull[b]  in each CTA, same multicast;  tempty[b] in the leader: 16 arrivals (8 epilogue warps x 2 CTAs)
-__device__ __forceinline__ uint32_t mapa_cluster(uint32_t saddr, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst_smem, const CUtensorMap * map, int c0, int c1,
-                                                 uint32_t bar_cluster_addr) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst_smem), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
-        : "memory");
-}
-template <int COLS>
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_result) {  // one warp in EACH CTA of the pair
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "n"(COLS) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-template <int COLS>
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
-}
-__device__ __forceinline__ void mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void mma_commit_pair(uint32_t bar, uint16_t cta_mask) {
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-                 "h"(cta_mask)
-                 : "memory");
-}
-
-struct mmq_pair_shape {
-    static constexpr int BN      = 256;                               // columns of the pair's tile
-    static constexpr int NS      = 6;
-    static constexpr int A_BYTES = MMQ_BM * MMQ_BK;                   // own 128 rows: 16 KB
-    static constexpr int B_BYTES = (BN / 2) * MMQ_BK;                 // own half of the columns: 16 KB
-    static constexpr int STAGE   = A_BYTES + B_BYTES;
-    static constexpr int NSC     = 4;
-    static constexpr int SC_FLTS = MMQ_BM + BN;
-    static constexpr int SMEM    = NS * STAGE + NSC * SC_FLTS * 4 + 1024;
-    static constexpr int THREADS = 320;
-};
-
-__global__ void __launch_bounds__(320, 1) k_mmq_pair(const __grid_constant__ CUtensorMap mapA,
-                                                     const __grid_constant__ CUtensorMap mapB, const mmq_kargs a) {
-    using SH = mmq_pair_shape;
-    constexpr int NS = SH::NS, BN = SH::BN;
-    extern __shared__ uint8_t mmq_smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * NS + 4 + 2 * SH::NSC];
-    __shared__ uint32_t tmem_slot;
-
-    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tiles = (smem_u32(mmq_smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * NS, bar_tfull = bar_empty + 8 * NS,
-                   bar_tempty = bar_tfull + 16, bar_sfull = bar_tempty + 16, bar_sempty = bar_sfull + 8 * SH::NSC;
-    const uint32_t scales = tiles + NS * SH::STAGE;
-    const uint32_t crank  = cluster_ctarank();
-    const bool     leader = crank == 0;
-    const int m0 = blockIdx.x * MMQ_BM, n0 = blockIdx.y * BN;   // blockIdx.x = 2 * pair + rank: my own 128 rows
-    const int ms0 = min(m0, a.mpad - MMQ_BM);
-    const int nch = a.nch, nkb = MMQ_KBC * nch;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < NS; s++) mbar_init(bar_full + 8 * s, 2), mbar_init(bar_empty + 8 * s, 1);
-        for (int b = 0; b < 2; b++) mbar_init(bar_tfull + 8 * b, 1), mbar_init(bar_tempty + 8 * b, 16);
-        for (int b = 0; b < SH::NSC; b++) mbar_init(bar_sfull + 8 * b, 1), mbar_init(bar_sempty + 8 * b, 8);
-        mbar_fence_init();
-        prefetch_tmap(&mapA);
-        prefetch_tmap(&mapB);
-    }
-    if (warp == 1) tmem_alloc_pair<2 * BN>(smem_u32(&tmem_slot));
-    tc_fence_before();
-    __syncthreads();
-    cluster_sync_all();                                         // both CTAs' barriers and TMEM exist
-    tc_fence_after();
-    const uint32_t tmem = tmem_slot;
-    pdl_launch_dependents();
-    pdl_wait();
-
-    if (warp == 0) {
-        // ------------------------------------------------------------------------------------------ TMA producer (both CTAs)
-        if (lane == 0) {
-            for (int kb = 0; kb < nkb; kb++) {
-                if ((kb % MMQ_KBC) == 0) {
-                    const int c = kb / MMQ_KBC, b = c % SH::NSC;
-                    mbar_wait(bar_sempty + 8 * b, ((c / SH::NSC) & 1) ^ 1);
-                    const uint32_t sd = scales + b * SH::SC_FLTS * 4;
-                    mbar_expect_tx(bar_sfull + 8 * b, SH::SC_FLTS * 4);
-                    tma_load_1d(sd, a.S + (int64_t) c * a.mpad + ms0, MMQ_BM * 4, bar_sfull + 8 * b);
-                    tma_load_1d(sd + MMQ_BM * 4, a.Tt + (int64_t) c * a.npad + n0, BN * 4, bar_sfull + 8 * b);
-                }
-                const int s = kb % NS, ph = (kb / NS) & 1;
-                mbar_wait(bar_empty + 8 * s, ph ^ 1);            // the pair's MMAs have read my copy of this stage
-                const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
-                const uint32_t lf = mapa_cluster(bar_full + 8 * s, 0);   // completion is counted in the LEADER's barrier
-                tma_load_2d_pair(sa, &mapA, kb * MMQ_BK, m0, lf);
-                tma_load_2d_pair(sb, &mapB, kb * MMQ_BK, n0 + (int) crank * (BN / 2), lf);
-                if (leader) mbar_expect_tx(bar_full + 8 * s, 2 * SH::STAGE);
-                else mbar_arrive_cluster(lf);
-            }
-        }
-    } else if (warp == 1) {
-        // ------------------------------------------------------------------------------------------ MMA issuer (leader only)
-        if (lane == 0 && leader) {
-            constexpr uint32_t idesc = idesc_i8(2 * MMQ_BM, BN);
-            for (int c = 0; c < nch; c++) {
-                const int buf = c & 1;
-                mbar_wait(bar_tempty + 8 * buf, ((c >> 1) & 1) ^ 1);   // both CTAs' epilogues have drained this accumulator
-                tc_fence_after();
-                for (int h = 0; h < MMQ_KBC; h++) {
-                    const int kb = MMQ_KBC * c + h, s = kb % NS, ph = (kb / NS) & 1;
-                    mbar_wait(bar_full + 8 * s, ph);
-                    tc_fence_after();
-                    const uint32_t sa = tiles + s * SH::STAGE, sb = sa + SH::A_BYTES;
-                    const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
-#pragma unroll
-                    for (int kk = 0; kk < MMQ_BK / 32; kk++)
-                        mma_i8_pair(tmem + buf * BN, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) ((h | kk) != 0));
-                    mma_commit_pair(bar_empty + 8 * s, 3);
-                }
-                mma_commit_pair(bar_tfull + 8 * buf, 3);
-            }
-        }
-    } else {
-        // ------------------------------------------------------------------------------------------ epilogue warps (both CTAs)
-        constexpr int CW = BN / 2;
-        const int q = warp & 3, half = (warp - 2) >> 2;
-        const int row = m0 + q * 32 + lane, col0 = half * CW;
-        __align__(8) float acc[CW];
-#pragma unroll
-        for (int i = 0; i < CW; i++) acc[i] = 0.f;
-        const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
-        const uint32_t lte0 = mapa_cluster(bar_tempty, 0);
-        for (int c = 0; c < nch; c++) {
-            const int buf = c & 1, sb = c % SH::NSC;
-            mbar_wait(bar_sfull + 8 * sb, (c / SH::NSC) & 1);
-            const float *  sv  = sring + sb * SH::SC_FLTS;
-            const float    sic = sv[q * 32 + lane];
-            const float4 * tp  = reinterpret_cast<const float4 *>(sv + MMQ_BM + col0);
-            mbar_wait(bar_tfull + 8 * buf, (c >> 1) & 1);
-            tc_fence_after();
-            epi_chunk<MMQ_EPI_DEFAULT, CW>(tmem + ((uint32_t) (q * 32) << 16) + buf * BN + col0, tp, sic, acc,
-                             [&] { if (lane == 0) mbar_arrive_cluster(lte0 + 8 * buf); });
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_sempty + 8 * sb);
-        }
-        if (row < a.m) {
-#pragma unroll
-            for (int i = 0; i < CW; i++) {
-                const int j = n0 + col0 + i;
-                if (j < a.n) {
-                    float * d = a.dst + (int64_t) j * a.dst_stride + row;
-                    *d = a.accumulate ? acc[i] + *d : acc[i];
-                }
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    cluster_sync_all();
-    if (warp == 1) tmem_dealloc_pair<2 * BN>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -1037,48 +880,33 @@ static int make_map(CUtensorMap * map, const void * base, int64_t rows, int64_t 
 int launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
                        cudaStream_t stream) {
     if (m == 0 || k == 0) return B200_OK;
-    const int64_t kp = mmq_kpad(k);
+    const int64_t kp = mmq_kpad(k), nwp = mmq_nplanes(type), ldp = nwp * kp;
     int8_t *      P  = (int8_t *) plane;
-    float *       S  = (float *) ((uint8_t *) plane + align256((size_t) m * kp));
+    float *       S  = (float *) ((uint8_t *) plane + align256((size_t) m * ldp));
     const int64_t total = (kp / 32) * m, mpad = mmq_mpad(m);
     const unsigned grid = (unsigned) ((total + 255) / 256);
     const uint8_t * wp = (const uint8_t *) W;
     switch (type) {
-        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
-        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
-        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
-        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
-        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, mpad, nullptr, nullptr); break;
+        case B200_TYPE_Q4_0:   k_plane_build<B200_TYPE_Q4_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad); break;
+        case B200_TYPE_Q8_0:   k_plane_build<B200_TYPE_Q8_0, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad); break;
+        case B200_TYPE_Q4_K:   k_plane_build<B200_TYPE_Q4_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad); break;
+        case B200_TYPE_Q6_K:   k_plane_build<B200_TYPE_Q6_K, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad); break;
+        case B200_TYPE_IQ4_XS: k_plane_build<B200_TYPE_IQ4_XS, false><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad); break;
         default: return B200_ERR_TYPE;
     }
     note_launch();
-    if (mmq_nplanes(type) == 2) {  // residual plane right behind the first one
-        uint8_t * plane2 = (uint8_t *) plane + mmq_plane_bytes(m, k);
-        int8_t *  P2 = (int8_t *) plane2;
-        float *   S2 = (float *) (plane2 + align256((size_t) m * kp));
-        k_plane_build<B200_TYPE_Q8_0, true><<<grid, 256, 0, stream>>>(wp, w_stride, P2, S2, m, k, kp, mpad, P, S);
+    if (nwp == 2) {  // residual plane beside the first one (stream order: plane 0 is complete)
+        k_plane_build<B200_TYPE_Q8_0, true><<<grid, 256, 0, stream>>>(wp, w_stride, P, S, m, k, kp, ldp, mpad);
         note_launch();
     }
     return check_cuda(cudaGetLastError(), "k_plane_build");
 }
 
-// workspace of the GEMM proper: quantized activations + their scales (+ slack for overhanging tiles)
-size_t mmq_workspace_bytes(int64_t n, int64_t k) { return mmq_act_bytes(n, k) + 2048; }
+// workspace of the GEMM proper: quantized activations + their scales, sized for two activation planes whatever the type
+// (the C ABI's size query has no type argument), + slack for overhanging tiles
+size_t mmq_workspace_bytes(int64_t n, int64_t k) { return mmq_act_bytes(n, k, 2) + 2048; }
 
-template <int BN, int EPI>
-static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
-                             int mtiles, cudaStream_t stream);
-// epilogue flavour: B200_MMQ_EPI = 0 (I2FP), 1 (magic-number conversion), 2 (magic + packed fp32; default)
-template <int BN>
-static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
-                         int mtiles, cudaStream_t stream) {
-    const int    epi = MMQ_KC > 256 ? 0 : env_flag("B200_MMQ_EPI", MMQ_EPI_DEFAULT);
-    switch (epi) {
-        case 0: return launch_mmq_bn_epi<BN, 0>(mapA, mapB, a, mapAx, mtiles, stream);
-        case 1: return launch_mmq_bn_epi<BN, 1>(mapA, mapB, a, mapAx, mtiles, stream);
-        default: return launch_mmq_bn_epi<BN, 2>(mapA, mapB, a, mapAx, mtiles, stream);
-    }
-}
+// epilogue flavour: B200_MMQ_EPI = 0 (I2FP), 1 (magic-number conversion), 2 (magic + packed fp32; default at chunk 256)
 template <int BN, int EPI>
 static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
                              int mtiles, cudaStream_t stream) {
@@ -1103,6 +931,16 @@ static int launch_mmq_bn_epi(const CUtensorMap & mapA, const CUtensorMap & mapB,
     note_launch();
     return B200_OK;
 }
+template <int BN>
+static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, const mmq_maps3 & mapAx,
+                         int mtiles, cudaStream_t stream) {
+    const int epi = MMQ_KC > 256 ? 0 : env_flag("B200_MMQ_EPI", MMQ_EPI_DEFAULT);
+    switch (epi) {
+        case 0: return launch_mmq_bn_epi<BN, 0>(mapA, mapB, a, mapAx, mtiles, stream);
+        case 1: return launch_mmq_bn_epi<BN, 1>(mapA, mapB, a, mapAx, mtiles, stream);
+        default: return launch_mmq_bn_epi<BN, 2>(mapA, mapB, a, mapAx, mtiles, stream);
+    }
+}
 
 // persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
@@ -1111,7 +949,6 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
     mmq_pargs p;
     p.ntn = (a.n + 255) / 256;
-    p.pf  = env_flag("B200_MMQ_PF", 0);   // measured: no gain at 4, 8, 16 (profiles/r01/pp_sweep_l2_lookahead.log)
     p.mtiles = mtiles;
     p.raster = env_flag("B200_MMQ_RASTER", 0);
     const int tiles = mtiles * p.ntn;
@@ -1139,27 +976,8 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     return B200_OK;
 }
 
-static int launch_mmq_pair(const CUtensorMap & mapA, const CUtensorMap & mapB, const mmq_kargs & a, cudaStream_t stream) {
-    B200_SMEM_ATTR_ONCE(k_mmq_pair, mmq_pair_shape::SMEM);
-    cudaLaunchConfig_t cfg = {};
-    const unsigned mt = (unsigned) ((a.m + MMQ_BM - 1) / MMQ_BM);
-    cfg.gridDim          = dim3((mt + 1) / 2 * 2, (unsigned) ((a.n + mmq_pair_shape::BN - 1) / mmq_pair_shape::BN), 1);
-    cfg.blockDim         = dim3(mmq_pair_shape::THREADS, 1, 1);
-    cfg.dynamicSmemBytes = mmq_pair_shape::SMEM;
-    cfg.stream           = stream;
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    attr[1].id = cudaLaunchAttributeClusterDimension;
-    attr[1].val.clusterDim.x = 2, attr[1].val.clusterDim.y = 1, attr[1].val.clusterDim.z = 1;
-    cfg.attrs = attr, cfg.numAttrs = 2;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_mmq_pair, mapA, mapB, a));
-    note_launch();
-    return B200_OK;
-}
-
-static int launch_quantize_x8(const float * x, int64_t x_stride, int8_t * Q, float * Tt, int64_t n, int64_t k, int64_t kp,
-                              int64_t npad, const mmq_zero & z, cudaStream_t stream) {
+static int launch_quantize_x8(int nxp, const float * x, int64_t x_stride, int8_t * Q, float * Tt, int64_t n, int64_t k,
+                              int64_t kp, int64_t npad, const mmq_zero & z, cudaStream_t stream) {
     const int64_t warps = n * (kp / MMQ_KC);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim  = dim3((unsigned) ((warps + 7) / 8), 1, 1);
@@ -1170,129 +988,74 @@ static int launch_quantize_x8(const float * x, int64_t x_stride, int8_t * Q, flo
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
     const bool vec = (uintptr_t) x % 16 == 0 && x_stride % 4 == 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
+    if (nxp == 2) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<2>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
+    else          B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<1>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
     note_launch();
     return B200_OK;
 }
 
-// split-K decision: two K halves when one would leave more than half of the SMs without a tile (B200_MMQ_KSPLIT=1/2 forces)
-static int mmq_ksplit(int64_t tiles, int64_t nch, int sm_count, bool allowed) {
+// split-K decision: two halves of the (virtual) chunk range when one launch would leave more than half of the SMs without
+// a tile (B200_MMQ_KSPLIT=1/2 forces)
+static int mmq_ksplit(int64_t tiles, int64_t nvc, int sm_count, bool allowed) {
     const int e = env_flag("B200_MMQ_KSPLIT", 0);
-    if (!allowed || nch < 4) return 1;
+    if (!allowed || nvc < 4) return 1;
     if (e) return e == 2 ? 2 : 1;
     return tiles * 2 <= sm_count ? 2 : 1;
 }
 
-int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
-               int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
-    if (m == 0 || n == 0) return B200_OK;
-    const int sm_count = sm_count_current_device();
-    if (!sm_count) return B200_ERR_CUDA;
-    const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
-    int8_t * Q  = (int8_t *) workspace;
-    float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
-    // tile width: 256 columns (the tensor core takes ~120 clocks per instruction whether N is 128 or 256, see
-    // profiles/r01/mmq_trace_v1.log) unless n is small; shapes with few tiles split K in two instead of narrowing tiles
-    const int64_t mt = (m + MMQ_BM - 1) / MMQ_BM;
-    int bn = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
-    // CTA pairs (tcgen05 cta_group::2): B200_MMQ_PAIR=1
-    const bool   pair = env_flag("B200_MMQ_PAIR", 0) == 1 && n > 128 && mt >= 2;
-    if (pair) bn = 256;
-    const bool aligned   = m % 4 == 0 && dst_stride % 4 == 0 && (uintptr_t) dst % 16 == 0;
-    const bool can_split = !pair && mmq_nplanes(type) == 1 && aligned;
-    // two-plane weights with few tiles: both planes in one launch, grid.z = plane (same addends as the accumulate pass)
-    const bool plane_split = !pair && mmq_nplanes(type) == 2 && aligned && mt * ((n + bn - 1) / bn) * 2 <= sm_count &&
-                             env_flag("B200_MMQ_PLANE_SPLIT", 1);
-    const int  ksplit = plane_split ? 2 : mmq_ksplit(mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
-    {
-        mmq_zero z = {};
-        if (ksplit > 1) z.cnt = 1, z.p[0] = dst, z.stride[0] = dst_stride, z.m[0] = m;
-        const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
-        if (st != B200_OK) return st;
-    }
-    const bool persist = !pair && ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1);
-    CUtensorMap mapA, mapB;
-    int st = make_map(&mapB, Q, n, kp, (pair || persist) ? 128 : bn);
-    if (st != B200_OK) return st;
-    if (plane_split) {
-        const uint8_t * p0 = (const uint8_t *) plane, * p1 = p0 + mmq_plane_bytes(m, k);
-        mmq_maps3 mx = {};
-        st = make_map(&mapA, p0, m, kp, MMQ_BM);
-        if (st != B200_OK) return st;
-        st = make_map(&mx.m[0], p1, m, kp, MMQ_BM);
-        if (st != B200_OK) return st;
-        mmq_kargs a = {};
-        a.S = (const float *) (p0 + align256((size_t) m * kp)), a.Sx[0] = (const float *) (p1 + align256((size_t) m * kp));
-        a.Tt = Tt, a.dst = dst, a.dst_stride = dst_stride;
-        a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
-        a.ksplit = 2, a.plane_split = 1, a.nmat = 1;
-        return bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, (int) mt, stream)
-                         : launch_mmq_bn<128>(mapA, mapB, a, mx, (int) mt, stream);
-    }
-    for (int pl = 0; pl < mmq_nplanes(type); pl++) {
-        const uint8_t * pb = (const uint8_t *) plane + (size_t) pl * mmq_plane_bytes(m, k);
-        st = make_map(&mapA, pb, m, kp, MMQ_BM);
-        if (st != B200_OK) return st;
-        mmq_kargs a = {};
-        a.S   = (const float *) (pb + align256((size_t) m * kp));
-        a.Tt  = Tt, a.dst = dst, a.dst_stride = dst_stride;
-        a.m = (int) m, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.mpad = (int) mmq_mpad(m);
-        a.accumulate = pl > 0;
-        a.ksplit = ksplit;
-        a.nmat = 1;
-        static const mmq_maps3 none = {};
-        st = pair ? launch_mmq_pair(mapA, mapB, a, stream)
-                  : persist ? launch_mmq_persistent(mapA, mapB, a, none, (int) mt, sm_count, stream)
-                  : bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, none, (int) mt, stream)
-                              : launch_mmq_bn<128>(mapA, mapB, a, none, (int) mt, stream);
-        if (st != B200_OK) return st;
-    }
-    return B200_OK;
-}
-
-// Several prepared planes (single-plane types, same k) against the same activations: x is quantized ONCE and the m-tiles
-// of all matrices share one grid (up to 4 matrices per launch), so that small matrices (k/v projections: 8 m-tiles) do not
-// leave the machine empty and every launch's fixed costs are paid once per group.
-int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
+// Prepared planes of ONE precision class (same number of weight and activation planes: K-quants + IQ4_XS | Q4_0 | Q8_0)
+// and one k against the same activations: x is quantized ONCE and the m-tiles of all matrices share one grid (up to 4
+// matrices per launch), so that small matrices (k/v projections: 8 m-tiles) do not leave the machine empty and every
+// launch's fixed costs are paid once per group.
+int launch_mmq_multi(int type, int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
                      const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
                      cudaStream_t stream) {
     if (nmat == 0 || n == 0) return B200_OK;
     const int sm_count = sm_count_current_device();
     if (!sm_count) return B200_ERR_CUDA;
+    const int     nwp = mmq_nplanes(type), nxp = mmq_xplanes(type);
     const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, npad = mmq_npad(n);
     int8_t * Q  = (int8_t *) workspace;
-    float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * kp));
+    float *  Tt = (float *) ((uint8_t *) workspace + align256((size_t) n * nxp * kp));
+    // segments of the virtual k (chunk offsets into the weight planes / the activation planes)
+    int nseg = 1, seg_a[3] = {0, 0, 0}, seg_b[3] = {0, 0, 0};
+    if (nxp == 2) seg_a[nseg] = 0, seg_b[nseg] = (int) nch, nseg++;          // W0 . X1
+    if (nwp == 2) seg_a[nseg] = (int) nch, seg_b[nseg] = 0, nseg++;          // W1 . X0
     int64_t total_mt = 0;
     bool    can_split = nmat <= 4;
     for (int i = 0; i < nmat; i++) {
         total_mt += (m[i] + MMQ_BM - 1) / MMQ_BM;
         can_split = can_split && m[i] % 4 == 0 && dst_stride[i] % 4 == 0 && (uintptr_t) dst[i] % 16 == 0;
     }
-    const int    bn = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
-    const int    ksplit = mmq_ksplit(total_mt * ((n + bn - 1) / bn), nch, sm_count, can_split);
+    // tile width: 256 columns (the tensor core takes ~120 clocks per instruction whether N is 128 or 256, see
+    // profiles/r01/mmq_trace_v1.log) unless n is small; shapes with few tiles split the virtual k in two instead
+    const int bn     = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
+    const int ksplit = mmq_ksplit(total_mt * ((n + bn - 1) / bn), nseg * nch, sm_count, can_split);
     {
         mmq_zero z = {};
         if (ksplit > 1)
             for (int i = 0; i < nmat; i++) z.p[z.cnt] = dst[i], z.stride[z.cnt] = dst_stride[i], z.m[z.cnt] = m[i], z.cnt++;
-        const int st = launch_quantize_x8(x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
+        const int st = launch_quantize_x8(nxp, x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
         if (st != B200_OK) return st;
     }
     const bool persist = ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1);
     CUtensorMap mapB;
-    int st = make_map(&mapB, Q, n, kp, persist ? 128 : bn);
+    int st = make_map(&mapB, Q, n, nxp * kp, persist ? 128 : bn);
     if (st != B200_OK) return st;
     for (int i0 = 0; i0 < nmat; i0 += 4) {
         const int cnt = nmat - i0 < 4 ? nmat - i0 : 4;
         CUtensorMap mapA;
         mmq_maps3   mx = {};
         mmq_kargs   a  = {};
-        a.Tt = Tt, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.accumulate = 0, a.nmat = cnt, a.ksplit = ksplit;
+        a.Tt = Tt, a.n = (int) n, a.nch = (int) nch, a.npad = (int) npad, a.nmat = cnt, a.ksplit = ksplit;
+        a.nseg = nseg;
+        for (int s = 0; s < 3; s++) a.seg_a[s] = seg_a[s], a.seg_b[s] = seg_b[s];
         int tiles = 0;
         for (int j = 0; j < cnt; j++) {
             const int64_t   mj = m[i0 + j];
             const uint8_t * pb = (const uint8_t *) planes[i0 + j];
-            const float *   Sj = (const float *) (pb + align256((size_t) mj * kp));
-            st = make_map(j == 0 ? &mapA : &mx.m[j - 1], pb, mj, kp, MMQ_BM);
+            const float *   Sj = (const float *) (pb + align256((size_t) mj * nwp * kp));
+            st = make_map(j == 0 ? &mapA : &mx.m[j - 1], pb, mj, nwp * kp, MMQ_BM);
             if (st != B200_OK) return st;
             if (j == 0) {
                 a.S = Sj, a.dst = dst[i0], a.dst_stride = dst_stride[i0], a.m = (int) mj, a.mpad = (int) mmq_mpad(mj);
@@ -1309,6 +1072,11 @@ int launch_mmq_multi(int nmat, const void * const * planes, const float * x, int
         if (st != B200_OK) return st;
     }
     return B200_OK;
+}
+
+int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
+               int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
+    return launch_mmq_multi(type, 1, &plane, x, x_stride, &dst, &dst_stride, &m, n, k, workspace, stream);
 }
 
 }  // namespace b200

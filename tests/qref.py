@@ -150,8 +150,9 @@ PLANE_KC = 256   # scale granularity of the tensor-core path; GPU tests set it f
 
 def mul_mat_plane(t, w, x, m, k, kc=None):
     """numpy restatement of the tensor-core path's arithmetic (llama.cpp.dsp_b200/csrc/mmq.cu): weights dequantized
-    bit-exactly, re-expressed as int8 with one f32 scale per (row, 256-chunk); activations int8 with one scale per
-    (column, chunk); exact integer chunk dot products; f32 scale-accumulate in chunk order.  -> f32 [n, m]"""
+    bit-exactly, re-expressed as int8 with one f32 scale per (row, chunk) -- Q8_0: value + residual plane; activations
+    int8 with one scale per (column, chunk) -- against Q4_0 / Q8_0: value + residual plane; exact integer chunk dot
+    products; f32 scale-accumulate over the segments W0.X0 | W0.X1 | W1.X0 in chunk order.  -> f32 [n, m]"""
     f32 = np.float32
     kc = kc or PLANE_KC
     x = np.ascontiguousarray(x, dtype=f32).reshape(-1, k)
@@ -169,19 +170,23 @@ def mul_mat_plane(t, w, x, m, k, kc=None):
         q = np.rint((c * inv[:, :, None]).astype(f32)).astype(np.int32)
         return q, s
 
-    Q, T = q8(Xf)
+    def planes(a, count):
+        out = []
+        for _ in range(count):
+            q, s = q8(a)
+            out.append((q, s))
+            a = (a - (s[:, :, None] * q.astype(f32)).astype(f32).reshape(a.shape)).astype(f32)   # fsub(fmul), per op
+        return out
 
-    def gemm(P, S, acc):
+    WP = planes(Wf, 2 if t == Q8_0 else 1)
+    XP = planes(Xf, 2 if t in (Q4_0, Q8_0) else 1)
+    acc = np.zeros((n, m), dtype=f32)
+    for wi, xi in [(0, 0), (0, 1), (1, 0)]:
+        if wi >= len(WP) or xi >= len(XP):
+            continue
+        (P, S), (Q, T) = WP[wi], XP[xi]
         for c in range(kp // kc):
             D = (Q[:, c, :].astype(np.int64) @ P[:, c, :].astype(np.int64).T).astype(f32)        # [n, m], exact
             st = (S[None, :, c] * T[:, None, c]).astype(f32)
             acc = (D.astype(np.float64) * st.astype(np.float64) + acc.astype(np.float64)).astype(f32)   # one fma rounding
-        return acc
-
-    P, S = q8(Wf)
-    out = gemm(P, S, np.zeros((n, m), dtype=f32))
-    if t == Q8_0:   # second plane: the residual w - s * P, accumulated onto the first pass (dst = acc + dst)
-        W1 = (S[:, :, None] * P.astype(f32)).astype(f32).reshape(m, kp)
-        P2, S2 = q8((Wf - W1).astype(f32))
-        out = (gemm(P2, S2, np.zeros((n, m), dtype=f32)) + out).astype(f32)
-    return out
+    return acc
