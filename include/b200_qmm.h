@@ -37,7 +37,8 @@ typedef enum {
     B200_ERR_WORKSPACE   = 4, /* workspace missing or too small */
     B200_ERR_NO_DEVICE   = 5, /* no CUDA device of compute capability 10.x */
     B200_ERR_CUDA        = 6, /* a CUDA runtime call failed: see b200_last_cuda_error() */
-    B200_ERR_UNSUPPORTED = 7
+    B200_ERR_UNSUPPORTED = 7,
+    B200_ERR_TOO_LARGE   = 8  /* b200_mul_mat_noalloc: the problem needs more than its built-in scratch */
 } b200_status;
 
 /* weight types, numerically equal to enum ggml_type (ggml/include/ggml.h:350-392) */
@@ -124,6 +125,24 @@ B200_API size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int6
 B200_API int    b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x, int64_t x_row_stride,
                              float * dst, int64_t dst_row_stride, int64_t m, int64_t n, int64_t k, void * workspace,
                              size_t workspace_bytes, b200_stream_t stream);
+
+/*
+ * b200_mul_mat for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as b200_mul_mat's batch <= 8 path (activation quantizer + GEMV kernel), minus the
+ * workspace: the q8_1 activation scratch is a __device__ array inside the library of B200_NOALLOC_SCRATCH_BYTES, which
+ * every GPU that loads the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree).
+ * Limits: n <= 8, k <= 32768 and n * (k + 12 * k/32, sections rounded to 16) <= B200_NOALLOC_SCRATCH_BYTES; anything
+ * larger returns B200_ERR_TOO_LARGE (text in b200_last_cuda_error()).
+ * All calls on one GPU share the scratch and it keeps the last call's contents (nothing in it needs to start at zero:
+ * each call's quantizer overwrites every byte its GEMV reads).  Calls that OVERLAP on one GPU race on it: serialize
+ * them on one stream, or use b200_mul_mat with one workspace per stream.
+ */
+#define B200_NOALLOC_SCRATCH_BYTES (384 * 1024)
+B200_API size_t b200_noalloc_scratch_size(void);            /* = B200_NOALLOC_SCRATCH_BYTES */
+B200_API int b200_mul_mat_noalloc(int type, const void * W_device, int64_t w_row_stride, const float * x_device,
+                                  int64_t x_row_stride, float * dst_device, int64_t dst_row_stride, int64_t m, int64_t n,
+                                  int64_t k, b200_stream_t stream);
 
 /*
  * nmat MUL_MATs that read the SAME activations x (q/k/v of one attention block, gate/up of one FFN): dst[i] = W[i] x^T.

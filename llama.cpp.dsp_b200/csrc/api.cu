@@ -181,6 +181,7 @@ const char * b200_status_string(int s) {
         case B200_ERR_NO_DEVICE: return "no sm_100 CUDA device";
         case B200_ERR_CUDA: return "CUDA runtime error";
         case B200_ERR_UNSUPPORTED: return "unsupported configuration";
+        case B200_ERR_TOO_LARGE: return "problem exceeds the built-in scratch of the no-alloc entry point";
     }
     return "unknown status";
 }

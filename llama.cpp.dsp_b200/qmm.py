@@ -27,6 +27,7 @@ EXPORTS = [
     "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
+    "b200_noalloc_scratch_size", "b200_mul_mat_noalloc",
 ]
 
 
@@ -96,6 +97,8 @@ def lib():
     L.b200_ipc_get_handle.argtypes = [vp, vp, C.POINTER(i64)]
     L.b200_ipc_open_handle.argtypes = [vp, i64, C.POINTER(vp)]
     L.b200_ipc_close_handle.argtypes = [vp, i64]
+    L.b200_noalloc_scratch_size.restype = sz
+    L.b200_mul_mat_noalloc.argtypes = [i32, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp]
     L.b200_reload_env.restype = None
     L.b200_debug_gemv_trace.restype = None
     L.b200_debug_gemv_trace.argtypes = [vp, i64]
@@ -107,7 +110,7 @@ def check(status):
     if status != 0:
         L = lib()
         msg = L.b200_status_string(status).decode()
-        if status in (5, 6):
+        if status in (5, 6, 8):
             msg += ": " + L.b200_last_cuda_error().decode()
         raise B200Error("b200_qmm: %s (status %d)" % (msg, status))
 
