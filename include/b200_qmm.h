@@ -224,6 +224,39 @@ B200_API int    b200_mul_mat_multi_host(int nmat, const int * types, const void 
 /* ---- MUL_MAT_ID ------------------------------------------------------------------------------------------------ */
 
 /*
+ * A SEQUENCE of MUL_MAT groups at batch 1 (the decode token) as ONE persistent kernel launch -- replaces the per-node
+ * launch loop of the decode graph (ggml_cuda_compute_forward -> ggml_cuda_mul_mat -> quantize_row_q8_1_cuda +
+ * mul_mat_vec_q per node, ggml/src/ggml-cuda/ggml-cuda.cu:2646-2706, 1877-1938), which the reference amortizes with
+ * CUDA-graph capture (ggml-cuda.cu:2470-2781).
+ * A group = up to 4 weight matrices (any mix of the five types, packed rows) multiplied with the same activation vector
+ * x[k] (q/k/v; gate/up), results dst[i][m[i]].  Groups run in list order.  `dependent` != 0: the group starts only after
+ * every earlier group of the sequence is complete (what stream order gives consecutive b200_mul_mat calls) -- set it
+ * when x, or a dst the group overwrites, is touched by an earlier group.  Groups with dependent == 0 may overlap the
+ * tail of earlier groups and must not alias their dst.  Results are bit-identical to b200_mul_mat.
+ * The PLAN (group list + geometry + arrival counters) lives in caller-owned device memory of b200_sequence_plan_size()
+ * bytes, 16-byte aligned; build it once per set of pointers (outside graph capture), run it every token.  A plan must
+ * not be run concurrently with itself.  Limits: n = 1, k <= 32768; B200_ERR_UNSUPPORTED otherwise (use b200_mul_mat_multi).
+ */
+typedef struct {
+    const float * x_device;      /* [k] f32 */
+    int64_t       k;
+    int           nmat;          /* 1..4 */
+    int           dependent;
+    int           type[4];
+    const void *  W_device[4];   /* m[i] packed rows */
+    float *       dst_device[4]; /* [m[i]] f32 */
+    int64_t       m[4];
+} b200_seq_group;
+B200_API size_t b200_sequence_plan_size(int ngroups);
+B200_API int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes,
+                                      b200_stream_t stream);
+B200_API int b200_sequence_run(void * plan_device, b200_stream_t stream);
+/* *error_group = 0: fine; g > 0: dependent group g timed out waiting for earlier groups (synchronizes the stream) */
+B200_API int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t stream);
+/* profiling aid (tools/seq_trace.py): later runs write 8 globaltimer stamps per (group, CTA) to trace_device; NULL = off */
+B200_API int b200_debug_sequence_trace(void * plan_device, void * trace_device, b200_stream_t stream);
+
+/*
  * dst[t][s][:] = as[ids[t][s]] * b[t][s % ne11][:]        (ggml_mul_mat_id, ggml/src/ggml.c:2771-2799)
  * Entirely on the device: the expert ids are read by the kernel, there is NO device->host copy or stream sync.
  * Replaces ggml_cuda_mul_mat_id + k_copy_src1_to_contiguous + k_copy_dst_from_contiguous,

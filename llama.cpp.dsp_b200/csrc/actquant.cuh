@@ -64,6 +64,11 @@ __device__ __forceinline__ float4 load_f4(const float * p, bool vec) {
     if (vec) return *reinterpret_cast<const float4 *>(p);
     return make_float4(p[0], p[1], p[2], p[3]);
 }
+// same through L2 only (ld.global.cg): for data another CTA of the SAME kernel may have written (gemvseq.cu)
+__device__ __forceinline__ float4 load_f4_cg(const float * p, bool vec) {
+    if (vec) return __ldcg(reinterpret_cast<const float4 *>(p));
+    return make_float4(__ldcg(p), __ldcg(p + 1), __ldcg(p + 2), __ldcg(p + 3));
+}
 
 // Quantize one row of k f32 (k % 32 == 0) into the SoA layout at `out` (generic pointer: shared or global).
 // Called by `nwarps` warps of a CTA; warp `warp` takes blocks 4*warp + i*4*nwarps .. (+3).
@@ -71,7 +76,7 @@ __device__ __forceinline__ float4 load_f4(const float * p, bool vec) {
 // IQ4_XS kernel's prmt codebook lookup emits weights.
 // UNROLL: how many of a warp's iterations issue their global loads back to back before any arithmetic (the GEMV's
 // fused prologue uses 4 so that a row costs one L2 round trip instead of one per iteration).
-template <bool INTERLEAVE, int UNROLL = 1>
+template <bool INTERLEAVE, int UNROLL = 1, bool CG = false>
 __device__ __forceinline__ void quantize_row_q8_soa(const float * __restrict__ x, int64_t k, uint8_t * out,
                                                     q8_layout L, int warp, int nwarps, int lane, bool vec) {
     const int nb   = (int) (k / 32);
@@ -85,7 +90,7 @@ __device__ __forceinline__ void quantize_row_q8_soa(const float * __restrict__ x
         for (int j = 0; j < UNROLL; j++) {
             const int b = b0 + j * step + (lane >> 3);
             vv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (b < nb) vv[j] = load_f4(x + (int64_t) b * 32 + 4 * sub, vec);
+            if (b < nb) vv[j] = CG ? load_f4_cg(x + (int64_t) b * 32 + 4 * sub, vec) : load_f4(x + (int64_t) b * 32 + 4 * sub, vec);
         }
 #pragma unroll
         for (int j = 0; j < UNROLL; j++) {

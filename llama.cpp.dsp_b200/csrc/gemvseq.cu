@@ -1,0 +1,517 @@
+// gemvseq.cu -- batch-1 decode as ONE persistent launch over a SEQUENCE of matmul groups (b200_sequence_*).
+//
+// Replaces (reference): the per-node launch loop of the decode graph -- ggml_cuda_compute_forward -> ggml_cuda_mul_mat ->
+// quantize_row_q8_1_cuda + mul_mat_vec_q per MUL_MAT node (ggml/src/ggml-cuda/ggml-cuda.cu:2646-2706, 1877-1938;
+// mmvq.cu:130-206; quantize.cu:4-38), which the reference amortizes with CUDA-graph capture (ggml-cuda.cu:2470-2781).
+//
+// Why (profiles/r01/layer_trace_v1.log): with one launch per group, 3-5 us of every 4-16 us group are a
+// dependency chain (previous grid drains -> quantizer grid -> GEMV grid released -> activations loaded) during which HBM
+// is idle because the next GEMV's CTAs cannot even become resident before the previous ones leave (both need the whole
+// 226 KB of shared memory).  Here one CTA per SM stays resident for the whole sequence:
+//  * a "group" = up to 4 weight matrices that read the same activation vector (q/k/v, gate/up), exactly the unit of
+//    b200_mul_mat_multi; groups are executed in list order;
+//  * warp 16 walks the (group, stage) list of its CTA and keeps issuing bulk TMA copies of weight rows into ONE ring of
+//    uniform slots shared by all groups (stage number q -> slot q % NS, mbarrier phase q / NS), so the next group's first
+//    stages are requested while the compute warps finish the current one, wait for the other CTAs and quantize the next
+//    activations: weights never depend on earlier results.  Consumers look at a stage's barrier only after the issue
+//    warp has published "stage q issued" -- the slot's previous phase is then known to be complete, which is what makes
+//    parity waits safe although teams of different groups share slots;
+//  * every CTA quantizes the group's activation vector itself into shared memory (16 warps, one pass over <= 56 KB from
+//    L2, the arithmetic of quantize_row_q8_1_ref -- actquant.cuh), so there is no quantizer kernel and no q8 scratch;
+//  * a group marked DEPENDENT starts only after every CTA has finished all earlier groups (a release/acquire counter per
+//    group in the plan: same ordering a stream gives consecutive launches).  Groups not marked dependent only need their
+//    own inputs and may overlap the tail of earlier groups;
+//  * with 226 KB of shared memory carved out L1 is a few KB, so the descriptor of the group in work is staged in shared
+//    memory (compute warps: at the boundary; issue warp: cp.async one group ahead) and all per-stage bookkeeping is
+//    incremental -- per-stage reads of the plan from global memory cost an L2 round trip each and made the first version
+//    2.6x slower (profiles/r02/seq_bench_*.log);
+//  * per-stage compute is the code of mmvq.cu (gemv_core.cuh): one 64-element unit of k per lane in registers, dp4a,
+//    butterfly over V rows, deterministic team reduction.  Results are bit-identical to b200_mul_mat.
+// Measured (8B token, 129 dependent groups, profiles/r02/seq_trace_v4_slot24k.log): steady-state streaming inside a
+// group reaches 6.7 TB/s, a group boundary costs ~3.2 us (1.0 grid-wide arrival + 1.1 quantize + 1.1 first weights), the
+// token 1.74 ms as one launch -- better than 1.85 ms of eager per-group launches, behind their CUDA-graph replay (1.54 ms):
+// the dot products issue at about the HBM rate, so compute-warp idle time at a boundary is not made up afterwards.
+// n = 1 only (the decode token); larger batches keep the per-group entry points.
+#include "gemv_core.cuh"
+#include "kernels.h"
+
+#include <cstddef>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace b200 {
+
+constexpr int SEQ_NW       = 16;                 // compute warps; warp SEQ_NW issues the TMA copies
+constexpr int SEQ_THREADS  = (SEQ_NW + 1) * 32;
+constexpr int SEQ_MAXSLOTS = 32;                 // ring slots
+constexpr int SEQ_SMEM     = 226 * 1024;
+constexpr int SEQ_CTRL     = 1280;               // barriers, counters, three staged group descriptors
+constexpr int SEQ_PART     = 256;                // bytes of partial sums per slot: V * T <= 64 floats
+constexpr int SEQ_MAXSEG   = 4;
+
+struct seq_seg {            // one weight matrix of a group
+    const uint8_t * W;      // packed rows
+    float *         dst;    // m floats
+    int             m, type, row_bytes;
+    int             stage0; // first stage of this matrix in the group's stage list
+};
+struct seq_group {
+    const float * x;        // k floats
+    int           k, nseg;
+    int           dep;      // 1: starts only after ALL earlier groups of the sequence are complete on every CTA
+    int           interleave;   // activation layout class: 1 = IQ4_XS (pair-interleaved q8), 0 = everything else
+    int           T, nteams, V, nstages;
+    seq_seg       seg[SEQ_MAXSEG];
+    int           pad[2];   // sizeof = 176: copied to shared memory as 11 x 16 bytes
+};
+static_assert(sizeof(seq_group) == 176, "seq_group layout");
+struct seq_header {         // first bytes of the plan (device memory)
+    int ngroups, exitc, error, act_bytes;   // act_bytes: shared memory reserved for the quantized activations
+    int nslots, slot_bytes, pad[2];          // ring geometry, the same for every group of the sequence
+    unsigned long long * trace;              // profiling aid (tools/seq_trace.py): 8 globaltimer stamps per (group, CTA)
+    unsigned long long   pad2;
+};
+// plan = [seq_header][done: ngroups ints, padded to 16][seq_group x ngroups]
+__host__ __device__ static inline size_t seq_done_bytes(int ng) { return ((size_t) ng * 4 + 15) & ~(size_t) 15; }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_gpu(const int * p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void seq_stamp(unsigned long long * tr, int g, int ncta, int cta, int i) {
+    if (tr) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        tr[((size_t) g * ncta + cta) * 8 + i] = t;
+    }
+}
+__device__ __forceinline__ void red_release_gpu_add(int * p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// stage `st` of group G -> (matrix, first row, rows)
+__device__ __forceinline__ int seq_locate(const seq_group * __restrict__ G, int nseg, int V, int st, int & r0, int & nr) {
+    int s = 0;
+#pragma unroll
+    for (int i = 1; i < SEQ_MAXSEG; i++)
+        if (i < nseg && st >= G->seg[i].stage0) s = i;
+    r0 = (st - G->seg[s].stage0) * V;
+    nr = min(V, G->seg[s].m - r0);
+    return s;
+}
+#endif
+
+}  // namespace b200
+
+namespace b200 {
+
+// One stage = V rows of one matrix in shared memory at `base` (+ c0: the bulk copy began at the 16-byte boundary below
+// the first row).  Every lane dots its unit with the V rows, one transposing butterfly leaves lane group r with row r's
+// warp sum, written to the team's partial slots p[row * T + wt].
+template <int TYPE, int V>
+__device__ __forceinline__ void seq_stage(uint32_t base, uint32_t row_bytes, uint32_t c0, int nr, int ugc, bool have, int k32,
+                                          const q8_unit & u, float * p, int T, int wt, int lane) {
+    if constexpr (V == 1) {
+        float out[1] = {0.f};
+        unit_dot<TYPE, 1>(base + c0, ugc, k32, &u, out);
+        const float v = warp_sum(have ? out[0] : 0.f);
+        if (lane == 0) p[wt] = v;
+    } else {
+        float acc[V];
+#pragma unroll
+        for (int v = 0; v < V; v++) {
+            float out[1] = {0.f};
+            if (v < nr) unit_dot<TYPE, 1>(base + v * row_bytes + c0, ugc, k32, &u, out);   // warp-uniform branch
+            acc[v] = have ? out[0] : 0.f;
+        }
+        butterfly_rows<V>(acc, lane);
+        if ((lane & (32 / V - 1)) == 0) p[butterfly_row<V>(lane) * T + wt] = acc[0];
+    }
+}
+template <int TYPE>
+__device__ __forceinline__ void seq_stage_v(int V, uint32_t base, uint32_t row_bytes, uint32_t c0, int nr, int ugc, bool have,
+                                            int k32, const q8_unit & u, float * p, int T, int wt, int lane) {
+    if (V == 8) seq_stage<TYPE, 8>(base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane);
+    else if (V == 4) seq_stage<TYPE, 4>(base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane);
+    else if (V == 2) seq_stage<TYPE, 2>(base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane);
+    else seq_stage<TYPE, 1>(base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane);
+}
+
+__device__ __forceinline__ void st_release_cta_shared(uint32_t addr, int v) {
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta_shared(uint32_t addr) {
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restrict__ plan, int evict_first) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    seq_header *      H      = reinterpret_cast<seq_header *>(plan);
+    const int         ng     = H->ngroups;
+    int *             done   = reinterpret_cast<int *>(plan + sizeof(seq_header));
+    const seq_group * groups = reinterpret_cast<const seq_group *>(plan + sizeof(seq_header) + seq_done_bytes(ng));
+    const int         act_bytes = H->act_bytes, NS = H->nslots, S = H->slot_bytes;
+    unsigned long long * const trace = H->trace;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = gridDim.x, cta = blockIdx.x;
+
+    // shared memory: [control][partial sums: 256 B per slot][q8 activations: act_bytes][ring: NS slots of S bytes]
+    //   control: full[32], empty[32] mbarriers; arrived[32] ints; issued (stages the producer has issued so far)
+    // Stage number q (this CTA's stages of all groups, in order) lives in slot q % NS, barrier phase q / NS.
+    const uint32_t ctrl      = smem_u32(smem);
+    const uint32_t bar_full  = ctrl, bar_empty = ctrl + 8 * SEQ_MAXSLOTS;
+    int * const    arrived   = reinterpret_cast<int *>(smem + 16 * SEQ_MAXSLOTS);
+    const uint32_t issued_a  = ctrl + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS;
+    // With 226 KB of shared memory carved out, L1 is a few KB: a descriptor field read from global memory is an L2 round
+    // trip.  The group in work is therefore staged in shared memory, one copy for the compute warps (written at the group
+    // boundary) and one for the producer (which runs ahead).
+    seq_group * const Gc  = reinterpret_cast<seq_group *>(smem + 704);
+    seq_group * const Gq2 = reinterpret_cast<seq_group *>(smem + 704 + sizeof(seq_group));   // [2]: this group / the next one
+    float * const  partials  = reinterpret_cast<float *>(smem + SEQ_CTRL);
+    uint8_t * const act      = smem + SEQ_CTRL + SEQ_PART * SEQ_MAXSLOTS;
+    const uint32_t  ring     = ctrl + SEQ_CTRL + SEQ_PART * SEQ_MAXSLOTS + act_bytes;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < SEQ_MAXSLOTS; i++) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, 1);
+            arrived[i] = 0;
+        }
+        *reinterpret_cast<volatile int *>(smem + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS) = 0;
+        mbar_fence_init();
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+
+    auto nloc_of = [&](int g, int & s0) {
+        const int nstages = groups[g].nstages;
+        s0 = (int) ((int64_t) cta * nstages / G);
+        return (int) ((int64_t) (cta + 1) * nstages / G) - s0;
+    };
+
+    if (warp == SEQ_NW) {
+        // ---------------------------------------------------------------------------------------- TMA issue warp (lane 0)
+        if (lane == 0) {
+            const uint64_t policy = evict_first ? l2_policy_evict_first() : 0;
+            int q = 0, slot = 0, eph = 1;                       // stages issued; slot = q % NS; parity of empty[slot]'s LAST phase
+            // descriptors come through cp.async, one group ahead, so that a group switch costs no L2 round trip
+            auto fetch = [&](int g) {
+                const uint32_t d = smem_u32(&Gq2[g & 1]);
+                const uint8_t * src = reinterpret_cast<const uint8_t *>(&groups[g]);
+#pragma unroll
+                for (int i = 0; i < 11; i++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 16 * i), "l"(src + 16 * i) : "memory");
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            };
+            fetch(0);
+            for (int g = 0; g < ng; g++) {
+                if (g + 1 < ng) {
+                    fetch(g + 1);
+                    asm volatile("cp.async.wait_group 1;" ::: "memory");
+                } else {
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");
+                }
+                const seq_group * Gq = &Gq2[g & 1];
+                int       s0;
+                const int nstages = Gq->nstages;
+                s0 = (int) ((int64_t) cta * nstages / G);
+                const int nloc = (int) ((int64_t) (cta + 1) * nstages / G) - s0;
+                if (nloc == 0) continue;
+                const int V = Gq->V, nseg = Gq->nseg, s1 = s0 + nloc;
+                int st = s0;
+                while (st < s1) {
+                    // the matrix that holds stage st, and how many of this CTA's stages lie in it
+                    int seg = 0;
+                    for (int i = 1; i < nseg; i++)
+                        if (st >= Gq->seg[i].stage0) seg = i;
+                    const int m = Gq->seg[seg].m, row_bytes = Gq->seg[seg].row_bytes;
+                    const int seg_end = seg + 1 < nseg ? Gq->seg[seg + 1].stage0 : nstages;
+                    const int end = seg_end < s1 ? seg_end : s1;
+                    int       r0 = (st - Gq->seg[seg].stage0) * V;
+                    uint64_t  ga = (uint64_t) (Gq->seg[seg].W + (int64_t) r0 * row_bytes);
+                    const uint32_t step = (uint32_t) V * (uint32_t) row_bytes;
+                    for (; st < end; st++, q++) {
+                        if (q >= NS) mbar_wait(bar_empty + 8 * slot, (uint32_t) eph);   // stage q - NS is consumed
+                        const int      nr   = V < m - r0 ? V : m - r0;
+                        const uint64_t g0   = ga & ~(uint64_t) 15;
+                        const uint32_t span = (uint32_t) (((ga + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
+                        const uint32_t bar  = bar_full + 8 * slot;
+                        mbar_expect_tx(bar, span);
+                        if (evict_first) tma_load_1d_hint(ring + slot * S, (const void *) g0, span, bar, policy);
+                        else tma_load_1d(ring + slot * S, (const void *) g0, span, bar);
+                        // consumers look at a stage's barrier only once it has been issued: the slot's previous phase is
+                        // then known to be complete, so a parity wait cannot be satisfied by the phase before it
+                        st_release_cta_shared(issued_a, q + 1);
+                        if (++slot == NS) slot = 0, eph ^= 1;
+                        ga += step, r0 += V;
+                    }
+                }
+            }
+        }
+    } else {
+        // -------------------------------------------------------------------------------------------- compute warps
+        pdl_wait();                                             // x and dst may still be in use by the previous kernel
+        int qbase = 0;                                          // this CTA's stages in earlier groups
+        for (int g = 0; g <= ng; g++) {
+            // ---- group boundary: every compute warp is done with the previous group's stages, activations and descriptor
+            named_bar_sync(1, SEQ_NW * 32);
+            if (threadIdx.x == 0 && g > 0) {
+                // the barrier ordered every warp's dst stores of group g - 1 before this thread: one gpu-scope release
+                // publishes this CTA's rows of it.  Every CTA arrives for every group, in order (with or without rows in it),
+                // so done[g - 1] == gridDim.x means that ALL groups <= g - 1 are complete everywhere.
+                __threadfence();
+                red_release_gpu_add(&done[g - 1], 1);
+            }
+            if (g == ng) break;
+            int       s0;
+            const int nloc = nloc_of(g, s0);
+            if (nloc == 0) continue;
+            if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 0);   // boundary reached: previous group done on this CTA
+            if (warp == 0) {
+                const int dep = lane == 0 ? __ldcg(&groups[g].dep) : 0;
+                if (lane < 11) reinterpret_cast<uint4 *>(Gc)[lane] = __ldcg(reinterpret_cast<const uint4 *>(&groups[g]) + lane);
+                if (lane == 0 && dep && g > 0) {                // all CTAs have published every earlier group
+                    const long long t0 = clock64();
+                    while (ld_acquire_gpu(&done[g - 1]) < G) {
+                        if (clock64() - t0 > (1ll << 31)) {     // ~1 s: leave a mark instead of hanging the GPU
+                            atomicExch(&H->error, g);
+                            break;
+                        }
+                    }
+                }
+            }
+            named_bar_sync(1, SEQ_NW * 32);
+            if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 1);   // earlier groups complete everywhere
+            const int k = Gc->k, T = Gc->T, nteams = Gc->nteams, V = Gc->V, nseg = Gc->nseg;
+            // ---- quantize x into shared memory (every CTA for itself; L2-coherent loads: x may be an earlier group's dst)
+            const q8_layout L = q8_soa_layout(k);
+            const float *   x = Gc->x;
+            const bool      vec = ((uintptr_t) x & 15) == 0;
+            if (Gc->interleave) quantize_row_q8_soa<true, 4, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            else                quantize_row_q8_soa<false, 4, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            named_bar_sync(1, SEQ_NW * 32);
+            if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 2);   // activations quantized
+
+            const int team = warp / T, wt = warp - team * T;
+            if (team < nteams) {                                // (spare warps of this group's team layout skip the stages)
+                const int  k32 = k / 32, upr = (k + 63) / 64;
+                const int  ug = wt * 32 + lane;
+                const bool have = ug < upr;
+                const int  ugc = have ? ug : upr - 1;
+                const int  st1 = nseg > 1 ? Gc->seg[1].stage0 : INT32_MAX, st2 = nseg > 2 ? Gc->seg[2].stage0 : INT32_MAX,
+                           st3 = nseg > 3 ? Gc->seg[3].stage0 : INT32_MAX;
+                q8_unit u;
+                int     cur_q6 = -1;                            // register layout of u: 1 = Q6_K grouping, 0 = two 32-blocks
+                int     q = qbase + team, slot = q % NS, ph = (q / NS) & 1;
+                for (int li = team; li < nloc; li += nteams) {
+                    const int st = s0 + li;
+                    const int s  = st >= st3 ? 3 : st >= st2 ? 2 : st >= st1 ? 1 : 0;
+                    const seq_seg * sg = &Gc->seg[s];
+                    const int type = sg->type, row_bytes = sg->row_bytes;
+                    const int r0 = (st - sg->stage0) * V, nr = min(V, sg->m - r0);
+                    const int q6 = type == B200_TYPE_Q6_K;
+                    if (q6 != cur_q6) {
+                        if (q6) make_unit_q8<B200_TYPE_Q6_K, true>(u, act, L, k, ugc);
+                        else    make_unit_q8<B200_TYPE_Q4_K, true>(u, act, L, k, ugc);
+                        cur_q6 = q6;
+                    }
+                    while (ld_acquire_cta_shared(issued_a) <= q) {}
+                    mbar_wait(bar_full + 8 * slot, (uint32_t) ph);
+                    if (threadIdx.x == 0 && li == team) seq_stamp(trace, g, G, cta, 3);   // first weights of the group in hand
+                    const uint32_t base = ring + slot * S;
+                    const uint32_t c0   = (uint32_t) ((uint64_t) (sg->W + (int64_t) r0 * row_bytes) & 15);
+                    float * p = partials + slot * (SEQ_PART / 4);
+                    switch (type) {
+                        case B200_TYPE_Q4_K:   seq_stage_v<B200_TYPE_Q4_K>(V, base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane); break;
+                        case B200_TYPE_Q6_K:   seq_stage_v<B200_TYPE_Q6_K>(V, base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane); break;
+                        case B200_TYPE_Q4_0:   seq_stage_v<B200_TYPE_Q4_0>(V, base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane); break;
+                        case B200_TYPE_Q8_0:   seq_stage_v<B200_TYPE_Q8_0>(V, base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane); break;
+                        default:               seq_stage_v<B200_TYPE_IQ4_XS>(V, base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane); break;
+                    }
+                    // the LAST warp of the team to get here sums the T partials of every row in a fixed order
+                    // (deterministic), stores them and hands the slot back to the producer
+                    __syncwarp();
+                    int last = 0;
+                    if (lane == 0) {
+                        __threadfence_block();
+                        last = atomicAdd(&arrived[slot], 1) == T - 1;
+                    }
+                    last = __shfl_sync(0xffffffffu, last, 0);
+                    if (last) {
+                        if (lane == 0) arrived[slot] = 0;
+                        __threadfence_block();
+                        if (lane < nr) {
+                            const volatile float * pq = p + lane * T;
+                            float v = 0.f;
+                            for (int w = 0; w < T; w++) v += pq[w];
+                            sg->dst[r0 + lane] = v;
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_empty + 8 * slot);
+                    }
+                    q += nteams, slot += nteams;
+                    while (slot >= NS) slot -= NS, ph ^= 1;
+                }
+                if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 4);   // team 0's share of the group done
+            }
+            qbase += nloc;
+        }
+    }
+    // ---- exit: the last CTA to leave re-arms the plan's counters for the next launch
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&H->exitc, 1) == G - 1) {
+            for (int g = 0; g < ng; g++) done[g] = 0;
+            __threadfence();
+            atomicExch(&H->exitc, 0);
+        }
+    }
+}
+
+}  // namespace b200
+
+// ------------------------------------------------------------------------------------------------ host side
+using namespace b200;
+
+static int seq_block_elems(int type) { return type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 ? 32 : 256; }
+static int seq_align(int type) { return type == B200_TYPE_Q4_K ? 16 : type == B200_TYPE_IQ4_XS ? 8 : 2; }
+
+// per-group geometry inside ring slots of `slot_bytes`: rows per stage V (as many as fit, but few enough that every
+// team of the CTA gets a stage) and the team layout; false if one row does not fit or the row is too long for a CTA
+static bool seq_geometry(seq_group & g, int slot_bytes, int ncta) {
+    const int upr = (g.k + 63) / 64;
+    g.T = (upr + 31) / 32;
+    if (g.T > SEQ_NW) return false;
+    g.nteams = SEQ_NW / g.T;
+    int     rowmax = 0;
+    int64_t rows = 0;
+    for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax, rows += g.seg[i].m;
+    const int64_t rows_per_cta = (rows + ncta - 1) / ncta;
+    int V = 8;
+    while (V > 1 && (V * rowmax + 15 + 16 > slot_bytes || V * g.T > SEQ_PART / 4 || rows_per_cta < (int64_t) g.nteams * V)) V >>= 1;
+    if (V * rowmax + 15 + 16 > slot_bytes) return false;
+    g.V = V;
+    int st = 0;
+    for (int i = 0; i < g.nseg; i++) g.seg[i].stage0 = st, st += (g.seg[i].m + V - 1) / V;
+    g.nstages = st;
+    return true;
+}
+
+extern "C" {
+
+size_t b200_sequence_plan_size(int ngroups) {
+    if (ngroups <= 0) return 0;
+    const int ng = 2 * ngroups;   // a group that mixes IQ4_XS with other types is split in two (different q8 layouts)
+    return sizeof(seq_header) + seq_done_bytes(ng) + (size_t) ng * sizeof(seq_group);
+}
+
+int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes,
+                             b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (!groups || ngroups <= 0) return B200_ERR_SHAPE;
+    if (!plan_device || plan_bytes < b200_sequence_plan_size(ngroups)) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) plan_device % 16 != 0) return B200_ERR_ALIGNMENT;
+    const int ncta = sm_count_current_device();
+    if (!ncta) return B200_ERR_CUDA;
+    std::vector<seq_group> out;
+    int64_t kmax = 0;
+    for (int gi = 0; gi < ngroups; gi++) {
+        const b200_seq_group & in = groups[gi];
+        if (in.nmat < 1 || in.nmat > SEQ_MAXSEG || in.k <= 0 || in.k > 32768 || !in.x_device) return B200_ERR_SHAPE;
+        if ((uintptr_t) in.x_device % 4 != 0) return B200_ERR_ALIGNMENT;
+        kmax = in.k > kmax ? in.k : kmax;
+        for (int cls = 0; cls < 2; cls++) {                     // 0: plain q8 layout, 1: IQ4_XS (pair-interleaved)
+            seq_group g = {};
+            g.x = in.x_device, g.k = (int) in.k, g.dep = in.dependent ? 1 : 0, g.interleave = cls;
+            for (int i = 0; i < in.nmat; i++) {
+                const int type = in.type[i];
+                if (!b200_type_supported(type)) return B200_ERR_TYPE;
+                if ((type == B200_TYPE_IQ4_XS) != (cls == 1)) continue;
+                if (in.k % seq_block_elems(type) != 0 || in.m[i] < 0 || in.m[i] > INT32_MAX) return B200_ERR_SHAPE;
+                if (in.m[i] == 0) continue;
+                if (!in.W_device[i] || !in.dst_device[i]) return B200_ERR_SHAPE;
+                if ((uintptr_t) in.W_device[i] % seq_align(type) != 0 || (uintptr_t) in.dst_device[i] % 4 != 0) return B200_ERR_ALIGNMENT;
+                seq_seg & s = g.seg[g.nseg++];
+                s.W = (const uint8_t *) in.W_device[i], s.dst = in.dst_device[i], s.m = (int) in.m[i], s.type = type;
+                s.row_bytes = (int) b200_row_size(type, in.k);
+            }
+            if (g.nseg) out.push_back(g);
+        }
+    }
+    if (out.empty()) return B200_ERR_SHAPE;
+    seq_header H = {};
+    H.ngroups    = (int) out.size();
+    H.act_bytes  = (int) ((q8_soa_layout(kmax).bytes + 127) & ~127u);
+    // one slot size for the whole sequence: room for the longest row, at least 24 KB by default (8 rows of a k = 4096 Q4_K matrix: measured best, profiles/r02/seq_bench_*.log)
+    int rowmax = 0;
+    for (auto & g : out)
+        for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax;
+    const int ring_bytes = SEQ_SMEM - SEQ_CTRL - SEQ_PART * SEQ_MAXSLOTS - H.act_bytes;
+    int slot = (rowmax + 15 + 16 + 127) & ~127;
+    const int want = env_knob("B200_SEQ_SLOT_BYTES", 24576);
+    if (slot < want) slot = (want + 127) & ~127;
+    H.slot_bytes = slot;
+    H.nslots     = ring_bytes / slot < SEQ_MAXSLOTS ? ring_bytes / slot : SEQ_MAXSLOTS;
+    if (H.nslots < 2) return B200_ERR_UNSUPPORTED;
+    for (auto & g : out)
+        if (!seq_geometry(g, H.slot_bytes, ncta)) return B200_ERR_UNSUPPORTED;
+    const size_t done_b = seq_done_bytes(H.ngroups);
+    std::vector<uint8_t> host(sizeof(H) + done_b + out.size() * sizeof(seq_group), 0);
+    memcpy(host.data(), &H, sizeof(H));
+    memcpy(host.data() + sizeof(H) + done_b, out.data(), out.size() * sizeof(seq_group));
+    // pageable source: cudaMemcpyAsync returns once the bytes are staged, so `host` may go out of scope
+    B200_CUDA_TRY(cudaMemcpyAsync(plan_device, host.data(), host.size(), cudaMemcpyHostToDevice, stream));
+    return B200_OK;
+}
+
+int b200_sequence_run(void * plan_device, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (!plan_device) return B200_ERR_WORKSPACE;
+    const int ncta = sm_count_current_device();
+    if (!ncta) return B200_ERR_CUDA;
+    B200_SMEM_ATTR_ONCE(k_gemv_seq, SEQ_SMEM);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) ncta, 1, 1);
+    cfg.blockDim         = dim3(SEQ_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = SEQ_SMEM;
+    cfg.stream           = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = env_knob("B200_PDL", 1);
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_gemv_seq, (uint8_t *) plan_device, env_knob("B200_GEMV_EVICT_FIRST", 1)));
+    note_launch();
+    return B200_OK;
+}
+
+// profiling aid: 8 globaltimer stamps per (group, CTA) are written to `trace_device` (ngroups * sm_count * 8 u64) by every
+// later run of the plan; NULL switches it off
+int b200_debug_sequence_trace(void * plan_device, void * trace_device, b200_stream_t stream_) {
+    if (!plan_device) return B200_ERR_SHAPE;
+    B200_CUDA_TRY(cudaMemcpyAsync((uint8_t *) plan_device + offsetof(seq_header, trace), &trace_device, sizeof(void *),
+                                  cudaMemcpyHostToDevice, (cudaStream_t) stream_));
+    B200_CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream_));
+    return B200_OK;
+}
+
+// 0 = the last runs of this plan completed normally; g > 0 = a dependent group g gave up waiting for earlier groups
+// (copies 4 bytes device -> host and synchronizes the stream)
+int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t stream_) {
+    if (!plan_device || !error_group) return B200_ERR_SHAPE;
+    seq_header H;
+    B200_CUDA_TRY(cudaMemcpyAsync(&H, plan_device, sizeof(H), cudaMemcpyDeviceToHost, (cudaStream_t) stream_));
+    B200_CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream_));
+    *error_group = H.error;
+    return B200_OK;
+}
+
+}  // extern "C"

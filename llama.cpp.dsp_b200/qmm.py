@@ -28,7 +28,14 @@ EXPORTS = [
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
     "b200_noalloc_scratch_size", "b200_mul_mat_noalloc",
+    "b200_sequence_plan_size", "b200_sequence_plan_build", "b200_sequence_run", "b200_sequence_status",
+    "b200_debug_sequence_trace",
 ]
+
+
+class SeqGroup(C.Structure):   # b200_seq_group
+    _fields_ = [("x", C.c_void_p), ("k", C.c_int64), ("nmat", C.c_int), ("dependent", C.c_int), ("type", C.c_int * 4),
+                ("W", C.c_void_p * 4), ("dst", C.c_void_p * 4), ("m", C.c_int64 * 4)]
 
 
 class B200Error(RuntimeError):
@@ -99,6 +106,12 @@ def lib():
     L.b200_ipc_close_handle.argtypes = [vp, i64]
     L.b200_noalloc_scratch_size.restype = sz
     L.b200_mul_mat_noalloc.argtypes = [i32, vp, i64, vp, i64, vp, i64, i64, i64, i64, vp]
+    L.b200_sequence_plan_size.restype = sz
+    L.b200_sequence_plan_size.argtypes = [i32]
+    L.b200_sequence_plan_build.argtypes = [vp, i32, vp, sz, vp]
+    L.b200_sequence_run.argtypes = [vp, vp]
+    L.b200_sequence_status.argtypes = [vp, C.POINTER(i32), vp]
+    L.b200_debug_sequence_trace.argtypes = [vp, vp, vp]
     L.b200_reload_env.restype = None
     L.b200_debug_gemv_trace.restype = None
     L.b200_debug_gemv_trace.argtypes = [vp, i64]
@@ -296,6 +309,38 @@ class MultiMatMulMMQ:
         ws, wsz = _workspace(self.device, self.ws_bytes)
         check(lib().b200_mul_mat_mmq_multi(self.nmat, self.types, self.P, x.data_ptr(), x.stride(0), self.dst,
                                            self.dstride, self.m, self.n, self.k, ws, wsz, _stream_ptr(stream)))
+
+
+class Sequence:
+    """b200_sequence_*: a list of MUL_MAT groups at batch 1 run as ONE persistent launch.
+    groups: [(x [1, k] or [k] f32 cuda, k, [(type, w, m, out [m] or [1, m] f32 cuda), ...], dependent)]"""
+
+    def __init__(self, groups, stream=None):
+        import torch
+        n = len(groups)
+        arr = (SeqGroup * n)()
+        self.keep = []
+        for g, (x, k, mats, dep) in zip(arr, groups):
+            _require_cuda(x)
+            assert x.dtype == torch.float32 and x.numel() == k and x.is_contiguous()
+            g.x, g.k, g.nmat, g.dependent = x.data_ptr(), k, len(mats), 1 if dep else 0
+            self.keep.append(x)
+            for i, (t, w, m, out) in enumerate(mats):
+                _require_cuda(w, out)
+                assert out.dtype == torch.float32 and out.numel() == m and out.is_contiguous()
+                g.type[i], g.W[i], g.dst[i], g.m[i] = t, w.data_ptr(), out.data_ptr(), m
+                self.keep += [w, out]
+        nbytes = lib().b200_sequence_plan_size(n)
+        self.plan = torch.zeros(nbytes, dtype=torch.uint8, device=self.keep[0].device)
+        check(lib().b200_sequence_plan_build(arr, n, self.plan.data_ptr(), nbytes, _stream_ptr(stream)))
+
+    def __call__(self, stream=None):
+        check(lib().b200_sequence_run(self.plan.data_ptr(), _stream_ptr(stream)))
+
+    def status(self, stream=None):
+        err = C.c_int(0)
+        check(lib().b200_sequence_status(self.plan.data_ptr(), C.byref(err), _stream_ptr(stream)))
+        return err.value
 
 
 def mul_mat_multi(types, ws, x, ms, k, outs=None, stream=None):

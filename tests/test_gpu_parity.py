@@ -500,3 +500,93 @@ def test_host_activations_zero_copy_equals_staged_copy(qmm, monkeypatch, pinned)
         for got, w_ in zip(outs, want):
             assert torch.equal(got, w_.cpu())
         assert torch.equal(one, want[0].cpu())
+
+
+# ------------------------------------------------------------------------------------------------ sequence (one launch)
+def _seq_reference(qmm, groups):
+    """the same groups through the existing entry point, one b200_mul_mat per matrix, in order"""
+    for x, k, mats, _ in groups:
+        for t, w, m, out in mats:
+            qmm.mul_mat(t, w, x.view(1, k), m, k, out=out.view(1, m))
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_sequence_dependent_chain_bit_identical(qmm, seed):
+    """b200_sequence_*: a chain in which every group's activation vector IS the previous group's result (so a missing
+    or early group-to-group synchronization shows up as wrong numbers), mixed types inside a group (q/k Q4_K + v Q6_K;
+    an IQ4_XS member forces the split into two layout classes), ragged m, k from 256 to 14336, more stages than ring
+    slots and fewer stages than CTAs.  Must equal consecutive b200_mul_mat calls BIT FOR BIT, run after run (the plan's
+    counters re-arm themselves), and leave no error mark."""
+    rng = np.random.default_rng(100 + seed)
+    T = qref.WEIGHT_TYPES
+    # (k -> [(type, m)]) ; the first matrix of each group feeds the next group: m_first(g) == k(g+1)
+    chain = [(4096, [("q4_K", 4096), ("q4_K", 1024), ("q6_K", 1024)]),
+             (4096, [("q4_K", 14336), ("q4_K", 14336)]),
+             (14336, [("q6_K", 2048)]),
+             (2048, [("q8_0", 256), ("iq4_xs", 520), ("q4_0", 264)]),
+             (256, [("q4_0", 1024), ("q8_0", 40)]),
+             (1024, [("iq4_xs", 4096)]),
+             (4096, [("q6_K", 4096), ("q4_K", 8)]),
+             (4096, [("q4_K", 512)])]
+    scale = 6.0   # keeps activations O(1) down the chain (weights are ~0.02 * N(0,1)-like)
+
+    def build():
+        groups, x = [], dev(rng.uniform(-1, 1, (chain[0][0],)).astype(np.float32))
+        for k, mats in chain:
+            ms = []
+            for name, m in mats:
+                w = dev(qref.random_blocks(T[name], m, k, rng, scale=0.02 * scale))
+                ms.append((T[name], w, m, torch.full((m,), float("nan"), device="cuda")))
+            groups.append((x, k, ms, True))
+            x = ms[0][3]
+        return groups
+    state = rng.bit_generator.state
+    g_seq = build()
+    rng.bit_generator.state = state
+    g_ref = build()
+    assert torch.equal(g_seq[0][0], g_ref[0][0])
+    _seq_reference(qmm, g_ref)
+    torch.cuda.synchronize()
+    seq = qmm.Sequence(g_seq)
+    for rep in range(3):
+        for _, _, mats, _ in g_seq:
+            for _, _, _, out in mats:
+                out.fill_(float("nan"))
+        seq()
+        torch.cuda.synchronize()
+        assert seq.status() == 0
+        for (_, _, ma, _), (_, _, mb, _) in zip(g_seq, g_ref):
+            for (_, _, _, a), (_, _, _, b) in zip(ma, mb):
+                assert torch.isfinite(b).all()
+                assert torch.equal(a, b), (rep, a.numel(), float((a - b).abs().max()))
+
+
+def test_sequence_many_independent_groups_and_limits(qmm):
+    """40 groups that only share their input (dependent = 0; more groups than ring halves, alternating k), then the
+    argument checks: n_mat, k beyond one CTA's reach, a plan buffer that is too small."""
+    rng = np.random.default_rng(7)
+    T = qref.WEIGHT_TYPES
+    xs = {k: dev(rng.uniform(-1, 1, (k,)).astype(np.float32)) for k in (1024, 4096)}
+    names = list(T)
+    g_seq, g_ref = [], []
+    for i in range(40):
+        k = 1024 if i % 3 else 4096
+        name, m = names[i % 5], [200, 1536, 72, 4096][i % 4]
+        w = dev(qref.random_blocks(T[name], m, k, rng))
+        g_seq.append((xs[k], k, [(T[name], w, m, torch.zeros(m, device="cuda"))], False))
+        g_ref.append((xs[k], k, [(T[name], w, m, torch.zeros(m, device="cuda"))], False))
+    _seq_reference(qmm, g_ref)
+    seq = qmm.Sequence(g_seq)
+    seq()
+    seq()
+    torch.cuda.synchronize()
+    assert seq.status() == 0
+    for (_, _, ma, _), (_, _, mb, _) in zip(g_seq, g_ref):
+        assert torch.equal(ma[0][3], mb[0][3])
+    w = dev(qref.random_blocks(qref.Q4_K, 8, 65536, rng))
+    with pytest.raises(qmm.B200Error):
+        qmm.Sequence([(torch.zeros(65536, device="cuda"), 65536, [(qref.Q4_K, w, 8, torch.zeros(8, device="cuda"))], True)])
+    L = qmm.lib()
+    assert L.b200_sequence_plan_size(0) == 0
+    grp = (qmm.qmm.SeqGroup * 1)()
+    assert L.b200_sequence_plan_build(grp, 1, None, 0, None) != 0
