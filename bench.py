@@ -6,10 +6,14 @@
 
 One "step" = one decode token's pass over the hot path: every quantized MUL_MAT of a Llama-shaped transformer
 (7 per layer + the output head) at batch 1, weights random-init in the GGUF block formats and resident in HBM.
-  * N = 1  : BASELINE.json configs[1], Llama-3-8B-shaped Q4_K_M (225 matmuls, 4.6 GB of weights per token).
-  * N > 1  : BASELINE.json configs[4], Llama-3-70B-shaped Q4_K_M, split-mode row: every weight's output rows are
-             sharded over the ranks (get_row_split rule) and the per-rank dst slices are all-gathered (NCCL) after each
-             matmul.  Strong scaling: the model is fixed, per-GPU work shrinks with N.
+ONE workload for every N, so that the driver's 1 -> 8 GPU scaling compares like with like: BASELINE.json configs[4],
+Llama-3-70B-shaped Q4_K_M (561 matmuls, 41.9 GB of weights per token; it fits one B200).
+  * N = 1  : all rows on one GPU.  The line also carries BASELINE.json configs[1] -- Llama-3-8B-shaped Q4_K_M: tg128,
+             pp512 (tensor roofline), e2e, MUL_MAT_ID -- as the sub-object "llama3_8b_q4_k_m", measured by a sub-run of
+             this script (--workload llama3-8b-q4_k_m) on the same GPU.
+  * N > 1  : split-mode row: every weight's output rows are sharded over the ranks (get_row_split rule) and every rank
+             ends up with the whole result (fused peer stores from the GEMV epilogue; NCCL all-gather as the baseline).
+             Strong scaling: the model is fixed, per-GPU work shrinks with N.
 value   = tokens/s with inputs resident in HBM (device-timed with CUDA events, max over ranks).
 e2e     = the same step through the host-buffer C-ABI call b200_mul_mat_host: activations start in pinned host
           memory and results end there, per matmul (what the ggml scheduler does around a MUL_MAT-only backend).
@@ -232,12 +236,19 @@ def main():
                     help="N=1: one b200_mul_mat call per MUL_MAT node instead of b200_mul_mat_multi per src1 group")
     ap.add_argument("--no-single", action="store_true", help="N>1: skip the same-workload single-GPU leg on rank 0")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA-graph replay")
+    ap.add_argument("--no-sub", action="store_true", help="N=1: skip the llama3-8b-q4_k_m sub-run (configs[1])")
+    ap.add_argument("--sub", action="store_true", help="this IS the sub-run: full single-GPU legs, no sub-run of its own")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    model = args.workload or ("llama3-8b-q4_k_m" if max(world, args.gpus) == 1 else "llama3-70b-q4_k_m")
+    model = args.workload or "llama3-70b-q4_k_m"     # the same workload at every N (see the module docstring)
+    # the headline run at N = 1 leaves pp512 / MUL_MAT_ID (quoted on the 8B config) to the sub-run
+    with_sub = world == 1 and args.gpus == 1 and not args.sub and not args.no_sub and model != "llama3-8b-q4_k_m" \
+        and args.impl == "b200"
+    if with_sub:
+        args.no_pp = True
 
     if args.impl == "reference":
         return reference_arm(args, model)
@@ -395,6 +406,61 @@ def main():
         per_node = {"value": 1e3 / ms_node, "unit": "tok/s", "ms_per_step": ms_node, "launches_per_step": l_node,
                     "hbm_gbs": step_bytes / ms_node / 1e6}
         del run_n
+
+    # ---- N = 1: the same token as ONE persistent launch (b200_sequence_run): every group marked dependent on the groups
+    #      before it, i.e. the ordering consecutive calls on a stream have.  Checked bit for bit against the grouped calls.
+    sequence = None
+    if world == 1 and token_step is not token_step_per_node:
+        seq_groups = []
+        for (_, k, members), (call, x) in zip(node_groups, calls):
+            seq_groups.append((x, k, [(t, w, m, o) for (_, t, m, w), o in zip(members, call.keep[1])], True))
+        token_step()
+        torch.cuda.synchronize()
+        want = {b: o.clone() for b, o in out_node.items()}
+        for o in out_node.values():
+            o.zero_()
+        seq = qmm.Sequence(seq_groups)
+        seq()
+        torch.cuda.synchronize()
+        same = all(torch.equal(out_node[b], want[b]) for b in out_node) and seq.status() == 0
+        gs = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(stream):
+            seq()
+            stream.synchronize()
+            with torch.cuda.graph(gs, stream=stream):
+                seq()
+        ms_seq = timed(gs.replay, max(8, args.steps // 2), 3)
+        ms_seq_eager = timed(seq, max(8, args.steps // 4), 3)
+        sequence = {"value": 1e3 / ms_seq, "unit": "tok/s", "ms_per_step": ms_seq, "ms_per_step_eager": ms_seq_eager,
+                    "launches_per_step": 1, "groups": len(seq_groups), "bit_identical_to_grouped_calls": bool(same),
+                    "hbm_gbs": step_bytes / ms_seq / 1e6,
+                    "api": "b200_sequence_plan_build once + b200_sequence_run per token (one persistent kernel, in-CTA "
+                           "activation quantizer, release/acquire counters between dependent groups)"}
+        del gs
+
+    # ---- N = 1: e2e THROUGH THE REFERENCE'S ggml API and the plug-in: host tensors -> ggml_backend_tensor_set ->
+    #      ggml_backend_graph_compute(libggml-b200.so) -> ggml_backend_tensor_get, per group of nodes sharing src1
+    #      (oracle/ggml_graph_bench.cpp; its own weights, same shapes).  What a ggml caller gets.
+    e2e_ggml = None
+    if world == 1:
+        exe = os.path.join(ROOT, "oracle", "_ref", "ggml-graph-bench")
+        plug = os.path.join(ROOT, "llama.cpp.dsp_b200", "lib", "libggml-b200.so")
+        if os.path.exists(exe) and os.path.exists(plug):
+            c = MODELS[model]
+            cmd = [exe, "--backend", "B200_%d" % local_rank, "--steps", str(max(8, args.steps // 4)), "--warmup", "3",
+                   "--layers", str(c["n_layer"]), "--embd", str(c["n_embd"]), "--ff", str(c["n_ff"]), "--kv", str(c["n_kv"]),
+                   "--vocab", str(c["vocab"])] + (["--q4_0"] if c["recipe"] == "q4_0" else [])
+            try:
+                out = subprocess.run(cmd, check=True, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=600,
+                                     env=dict(os.environ, GGML_BACKEND_PATH=plug)).stdout
+                r = json.loads([ln for ln in out.splitlines() if ln.startswith("{")][-1])
+                e2e_ggml = {"value": r["tok_s"], "unit": "tok/s", "ms_per_step": r["ms_per_step"],
+                            "h2d_bytes_per_step": r["h2d_bytes_per_step"], "d2h_bytes_per_step": r["d2h_bytes_per_step"],
+                            "graph_compute_calls_per_step": r["graph_compute_calls"], "host_buffer": r["host_buffer"],
+                            "api": "ggml_backend_tensor_set + ggml_backend_graph_compute + ggml_backend_tensor_get through "
+                                   "libggml-b200.so (GGML_BACKEND_PATH), one graph per group of MUL_MAT nodes sharing src1"}
+            except Exception as e:  # noqa: BLE001
+                e2e_ggml = {"value": None, "error": str(e)[:200]}
 
     # ---- N > 1: the fused path -- each GEMV stores its rows into every rank's dst over NVLink, a stream wait-value
     #      replaces the collective (b200_mul_mat_rowsplit_fused + b200_rowsplit_wait).  When it runs, it is the headline
@@ -680,6 +746,11 @@ def main():
             except Exception:  # noqa: BLE001
                 int8_peak, int8_how = 3180.0, "fallback 2 x 1.59 PFLOP/s"
         tops = flops / ms_pp / 1e9
+        try:
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            bf16_burst, bf16_sust = float(mp["bf16_tflops"]), float(mp.get("bf16_tflops_sustained", 0) or 0)
+        except Exception:  # noqa: BLE001
+            bf16_burst, bf16_sust = 1590.0, 1400.0
         pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp,
               "steps": 8, "launch": "cuda_graph_replay" if (use_graph and ms_pp_graph <= ms_pp_eager) else "eager",
               "ms_per_step_eager": ms_pp_eager, "ms_per_step_graph": ms_pp_graph if use_graph else None,
@@ -687,7 +758,12 @@ def main():
               "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),
               "roofline": {"bound": "tensor", "achieved": tops, "peak": int8_peak, "unit": "TOP/s (int8)",
                            "frac": tops / int8_peak, "peak_source": int8_how, "nominal_int8_tops": 4500.0,
-                           "frac_of_nominal": tops / 4500.0, "kernel": "k_mmq_p / k_mmq (tcgen05.mma kind::i8, TMEM accumulators)"},
+                           "frac_of_nominal": tops / 4500.0,
+                           # driver-written denominator: int8 dense = 2 x the measured bf16 GEMM throughput
+                           "peak_2x_bf16_burst": 2 * bf16_burst, "frac_of_2x_bf16_burst": tops / (2 * bf16_burst),
+                           "peak_2x_bf16_sustained": 2 * bf16_sust or None,
+                           "frac_of_2x_bf16_sustained": tops / (2 * bf16_sust) if bf16_sust else None,
+                           "kernel": "k_mmq_p / k_mmq (tcgen05.mma kind::i8, TMEM accumulators)"},
               "per_node_calls": {"value": npp * 1e3 / ms_pp_node, "unit": "tok/s", "ms_per_step": ms_pp_node},
               "planes": {"cached": True, "bytes": plane_bytes, "build_seconds_once": plane_build_s},
               "transient_planes": {"value": npp * 1e3 / ms_pp_transient, "unit": "tok/s", "ms_per_step": ms_pp_transient}}
@@ -790,6 +866,20 @@ def main():
         except Exception as e:  # noqa: BLE001
             cpu = {"value": None, "unit": "tok/s", "cores": threads, "kind": "reference", "sample": "failed: " + str(e)[:160]}
 
+    # ---- N = 1 headline run: BASELINE configs[1] (llama3-8b-q4_k_m: tg128, pp512, e2e, MUL_MAT_ID) as a sub-run
+    sub8b = None
+    if with_sub:
+        try:
+            cmd = [sys.executable, os.path.abspath(__file__), "--workload", "llama3-8b-q4_k_m", "--sub", "--steps",
+                   str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu"] if args.no_cpu else [])
+            out = subprocess.run(cmd, check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900).stdout
+            full = json.loads([ln for ln in out.splitlines() if ln.startswith("{")][-1])
+            sub8b = {k: full.get(k) for k in ("metric", "value", "unit", "ms_per_step", "ms_per_step_eager", "roofline",
+                                               "cpu_baseline", "e2e", "e2e_ggml", "sequence", "per_node_calls", "pp512",
+                                               "mul_mat_id", "gpu_launches", "clocks", "config")}
+        except Exception as e:  # noqa: BLE001
+            sub8b = {"error": str(e)[:300]}
+
     if rank == 0:
         peak, how = peaks()
         # DRAM bytes of all GEMV launches of one step, from the committed ncu pass over the same workload (None otherwise)
@@ -821,6 +911,9 @@ def main():
             "clocks": clocks,
             "ms_per_step_eager": ms_eager,
             "per_node_calls": per_node,
+            "sequence": sequence,
+            "e2e_ggml": e2e_ggml,
+            "llama3_8b_q4_k_m": sub8b,
             "pp512": pp,
             "mul_mat_id": moe,
             "single_gpu_same_workload": single,

@@ -64,3 +64,44 @@ def test_reference_test_backend_ops_passes(op):
         assert len(mine) >= (10 if op == "MUL_MAT" else 2), (t, len(mine))
     m = re.search(r"(\d+)/(\d+) tests passed", out)
     assert m and m.group(1) == m.group(2), out[-2000:]
+
+
+SPLIT_TEST = os.path.join(ROOT, "oracle", "_ref", "ggml-split-test")
+GRAPH_BENCH = os.path.join(ROOT, "oracle", "_ref", "ggml-graph-bench")
+
+
+@pytest.mark.gpu
+@needs_plugin
+def test_split_buffer_type_row_split_is_bit_identical():
+    """--split-mode row through the public ggml API (oracle/ggml_split_test.cpp): the registry answers
+    "ggml_backend_split_buffer_type" (ggml-cuda.cu:3418-3422), a weight allocated in that buffer type is scattered over
+    the devices by set_tensor and gathered by get_tensor, and MUL_MAT on it equals MUL_MAT on the unsplit weight bit for
+    bit for all five types, n = 1 .. 512, uneven tensor_split, either device as the main one.  Needs two B200s in one
+    process: skipped on a one-GPU box (exit code 77)."""
+    if not os.path.exists(SPLIT_TEST):
+        pytest.skip("oracle/_ref/ggml-split-test not built")
+    r = subprocess.run([SPLIT_TEST], env=dict(os.environ, GGML_BACKEND_PATH=PLUGIN), capture_output=True, text=True, timeout=900)
+    if r.returncode == 77:
+        pytest.skip(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0, (r.stdout + r.stderr)[-4000:]
+    assert "PASS" in r.stdout
+
+
+@pytest.mark.gpu
+@needs_plugin
+def test_registry_answers_split_buffer_type_and_host_buffer_type():
+    """one-GPU part of the same contract: the proc address exists, the device offers a pinned host buffer type, and a
+    small decode token runs through tensor_set_async / graph_compute_async / tensor_get_async (oracle/ggml_graph_bench.cpp)"""
+    if not os.path.exists(GRAPH_BENCH):
+        pytest.skip("oracle/_ref/ggml-graph-bench not built")
+    import json
+    for extra in ([], ["--sync"]):
+        r = subprocess.run([GRAPH_BENCH, "--backend", "B200_0", "--steps", "2", "--warmup", "1", "--layers", "2", "--vocab", "4096"]
+                           + extra, env=dict(os.environ, GGML_BACKEND_PATH=PLUGIN), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, (r.stdout + r.stderr)[-2000:]
+        line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+        assert line["backend"] == "B200_0" and line["host_buffer"] == "B200_Host" and line["nodes"] == 15
+    C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libggml-base.so"), mode=C.RTLD_GLOBAL)
+    L = C.CDLL(PLUGIN)
+    L.ggml_backend_b200_reg.restype = C.c_void_p
+    assert L.ggml_backend_b200_reg()
