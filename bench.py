@@ -769,6 +769,45 @@ def main():
               "transient_planes": {"value": npp * 1e3 / ms_pp_transient, "unit": "tok/s", "ms_per_step": ms_pp_transient}}
         del planes
 
+    # ---- N > 1: pp512 with split-mode row: every rank multiplies its row slice on the tensor cores (cached planes of the
+    #      slice) and the [512 x rows] result slices are all-gathered per matmul -- MB-sized messages, bandwidth-bound, so
+    #      the NCCL collective is the right tool here (the fused peer-store epilogue exists for the 4-32 KB decode results)
+    if world > 1 and not args.no_pp:
+        npp = 512
+        xpp = {k: torch.rand((npp, k), device=dev, generator=gen) * 2 - 1 for k in ks}
+        sel = [(i, mm) for i, mm in enumerate(mms[:-1])]
+        planes = [qmm.build_plane(mms[i][1], weights[i], slices[i][1] - slices[i][0], mms[i][3]) if weights[i] is not None else None
+                  for i, _ in sel]
+        opp_l = {m: torch.empty((npp, maxrows[m]), device=dev) for _, (_, _, m, _) in sel}
+        opp_f = {m: torch.empty((world, npp, maxrows[m]), device=dev) for _, (_, _, m, _) in sel}
+
+        def prefill_step_split():
+            for (i, (name, t, m, k)), pl in zip(sel, planes):
+                lo, hi, _ = slices[i]
+                if pl is not None:
+                    qmm.mul_mat_mmq(t, pl, xpp[k], hi - lo, k, out=opp_l[m][:, :hi - lo])   # (dst row stride = widest slice)
+                dist.all_gather_into_tensor(opp_f[m], opp_l[m])
+        for _ in range(2):
+            prefill_step_split()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms_pp = timed(prefill_step_split, 6, 2)
+        flops = sum(2.0 * m * k * npp for _, (_, _, m, k) in sel)
+        try:
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            bf16_burst = float(mp["bf16_tflops"])
+        except Exception:  # noqa: BLE001
+            bf16_burst = 1590.0
+        tops = flops / ms_pp / 1e9
+        pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 6,
+              "launch": "eager", "collective": "dist.all_gather_into_tensor per matmul (NCCL)",
+              "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),
+              "roofline": {"bound": "tensor", "achieved": tops, "unit": "TOP/s (int8), all GPUs", "peak": world * 2 * bf16_burst,
+                           "frac": tops / (world * 2 * bf16_burst),
+                           "peak_source": "n_gpus x 2 x MEASURED_PEAKS.json bf16_tflops (int8 dense = 2 x bf16)"}}
+        del planes, opp_l, opp_f
+        torch.cuda.empty_cache()
+
     # ---- MUL_MAT_ID, batched decode (BASELINE config 4): Mixtral-8x7B-shaped Q4_K experts, 2 of 8 used, ids = random
     #      permutation prefix per token (tests/test-backend-ops.cpp:2121-2140), three weight copies cycled (> L2).
     #      Algorithmic bytes = distinct experts touched x expert bytes + activations + results.

@@ -267,6 +267,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[8]) { tmem_ld8(taddr, r); }
 __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld32(taddr, r); }
 __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld16(taddr, r); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -763,19 +770,8 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         uint32_t sc = 0, sc_ph = 0, buf = 0, buf_ph = 0;
         for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-            const mmq_item I = mmq_item_of(it, p);
-            float *  dstp = a.dst;
-            int64_t  dstride = a.dst_stride;
-            int      mrows = a.m, tile = I.mt;
-            if (a.nmat > 1) {
-                int first = 0;
-#pragma unroll
-                for (int i = 0; i < 3; i++)
-                    if (i + 1 < a.nmat && I.mt >= a.tile0[i]) dstp = a.dstx[i], dstride = a.dst_stridex[i], mrows = a.mx[i], first = a.tile0[i];
-                tile -= first;
-            }
-            const int ncw = I.bn >> 2, ng = ncw >> 4;            // columns per warp (64 / 32), 16-column groups (4 / 2)
-            const int row = tile * MMQ_BM + q * 32 + lane, col0 = part * ncw;
+            const int ncw = (it < p.n_main ? 256 : 128) >> 2;   // columns per warp (64 / 32)
+            const int col0 = part * ncw;
             __align__(8) float acc[64];
 #pragma unroll
             for (int i = 0; i < 64; i++) acc[i] = 0.f;
@@ -787,20 +783,29 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 TW(1, mbar_wait(bar_tfull + 8 * buf, buf_ph));
                 tc_fence_after();
                 const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + buf * 256 + col0;
-                // (one 16-column load in flight per warp: with 64 accumulators a second load buffer does not fit the
-                // 96 registers that 18 warps leave per thread; the other 3-4 warps of the scheduler cover the latency)
+                // Software pipeline over 8-column loads: the load of group g + 1 is in flight while group g is scaled and
+                // accumulated (tcgen05.wait::ld waits for ALL outstanding loads, so the next load is issued right after the
+                // wait that delivered the current one).  All 16 epilogue warps start a chunk together, so without this they
+                // would alternate "everybody loads" / "everybody computes" and the load latency would never be hidden.
+                // Two 8-column buffers cost the registers of one 16-column load (64 accumulators leave no more under the
+                // 96 registers that 18 warps get).
+                {
+                    const int ng8 = ncw >> 3;                    // 8 or 4 groups
+                    uint32_t r[2][8];
+                    tmem_ldw(tbase, r[0]);
 #pragma unroll
-                for (int g = 0; g < 4; g++) {
-                    if (g < ng) {                                // warp-uniform
-                        uint32_t r[16];
-                        tmem_ldw(tbase + g * 16, r);
-                        tmem_ld_wait();
-                        if (g + 1 == ng) {                       // accumulator fully read: hand it back to the tensor core
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                    for (int g = 0; g < 8; g++) {
+                        if (g < ng8) {                           // warp-uniform
+                            tmem_ld_wait();
+                            if (g + 1 < ng8) {
+                                tmem_ldw(tbase + (g + 1) * 8, r[(g + 1) & 1]);
+                            } else {                             // accumulator fully read: hand it back to the tensor core
+                                tc_fence_before();
+                                __syncwarp();
+                                if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                            }
+                            epi_accumulate<EPI, 8>(r[g & 1], tp + g * 2, sic, acc + g * 8);
                         }
-                        epi_accumulate<EPI, 16>(r, tp + g * 4, sic, acc + g * 16);
                     }
                 }
                 __syncwarp();
@@ -811,6 +816,19 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
 #ifdef B200_MMQ_TRACE
             const long long t_st = clock64();
 #endif
+            // where the item's results go (worked out only now: it would cost ten live registers across the chunk loop)
+            const mmq_item I = mmq_item_of(it, p);
+            float *  dstp = a.dst;
+            int64_t  dstride = a.dst_stride;
+            int      mrows = a.m, tile = I.mt;
+            if (a.nmat > 1) {
+                int first = 0;
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+                    if (i + 1 < a.nmat && I.mt >= a.tile0[i]) dstp = a.dstx[i], dstride = a.dst_stridex[i], mrows = a.mx[i], first = a.tile0[i];
+                tile -= first;
+            }
+            const int row = tile * MMQ_BM + q * 32 + lane;
             if (row < mrows) {
                 const int jn = min(ncw, a.n - (I.n0 + col0));    // columns of this warp inside the matrix
                 float *   d  = dstp + (int64_t) (I.n0 + col0) * dstride + row;

@@ -719,8 +719,8 @@ static void b200_compute_mul_mat_split(b200_backend_context * ctx, ggml_tensor *
     const int64_t xs = (int64_t) (src1->nb[1] / sizeof(float)), ys = (int64_t) (dst->nb[1] / sizeof(float));
     const bool    mmq = n >= b200_mmq_min_batch();
     ctx->enable_peer_access();
+    set_device(ctx->device);                                        // (the peer-access loop leaves another device current)
     if (!ctx->split_start) CUDA_CHECK(cudaEventCreateWithFlags(&ctx->split_start, cudaEventDisableTiming));
-    set_device(ctx->device);
     CUDA_CHECK(cudaEventRecord(ctx->split_start, ctx->stream));    // x is ready / dst may be overwritten from here on
     for (int d = 0; d < ndev; d++) {
         const int64_t rows = extra->row_high[d] - extra->row_low[d];
