@@ -821,16 +821,24 @@ def main():
         for label, m_e, k_e, bcast in (("ffn_gate/up_exps", 14336, 4096, True), ("ffn_down_exps", 4096, 14336, False)):
             copies = [gen_weights(torch, Q4_K, n_expert * m_e, k_e, gen, dev) for _ in range(3)]
             ebytes = m_e * row_bytes(Q4_K, k_e)
-            for nt in (1, 8, 32):
+            plane_e = None
+            for nt in (1, 8, 32, 64, 512):
                 ne11 = 1 if bcast else n_used
                 bb = torch.rand((nt, ne11, k_e), device=dev, generator=gen) * 2 - 1
                 ids_np = np.stack([rng.permutation(n_expert)[:n_used] for _ in range(nt)]).astype(np.int32)
                 ids_t = torch.from_numpy(ids_np).to(dev)
                 oo = torch.empty((nt, n_used, m_e), device=dev)
 
+                use_tc = bool(qmm.lib().b200_mul_mat_id_prefers_mmq(m_e, n_expert, n_used, nt))
+                if use_tc and plane_e is None:      # stacked planes of the three weight copies (+1 byte per weight each)
+                    plane_e = [qmm.build_plane(Q4_K, w_, n_expert * m_e, k_e) for w_ in copies]
+
                 def moe_step():
-                    for w_ in copies:
-                        qmm.mul_mat_id(Q4_K, w_, bb, ids_t, m_e, k_e, n_expert, out=oo)
+                    for ci, w_ in enumerate(copies):
+                        if use_tc:
+                            qmm.mul_mat_id_mmq(Q4_K, plane_e[ci], bb, ids_t, m_e, k_e, n_expert, out=oo)
+                        else:
+                            qmm.mul_mat_id(Q4_K, w_, bb, ids_t, m_e, k_e, n_expert, out=oo)
                 moe_run = moe_step
                 if use_graph:
                     gm = torch.cuda.CUDAGraph()
@@ -844,11 +852,12 @@ def main():
                 distinct = len(set(ids_np.flatten().tolist()))
                 algo = distinct * ebytes + bb.numel() * 4 + oo.numel() * 4
                 moe["cases"].append({"tensor": label, "m": m_e, "k": k_e, "n_tokens": nt, "distinct_experts": distinct,
+                                     "path": "tensor cores (b200_mul_mat_id_mmq)" if use_tc else "GEMV (b200_mul_mat_id)",
                                      "us_per_call": us, "algorithmic_gbs": algo / us / 1e3,
                                      "frac_of_hbm_peak": algo / us / 1e3 / hbm_peak})
                 if use_graph:
                     del gm
-            del copies
+            del copies, plane_e
             torch.cuda.empty_cache()
 
     # ---- N > 1: the SAME workload on ONE GPU (rank 0 alone, the other ranks wait), so that the line carries the

@@ -278,6 +278,25 @@ B200_API int    b200_mul_mat_id(int type, const void * as, int64_t expert_stride
 /* ---- multi-GPU row split ---------------------------------------------------------------------------------------- */
 
 /*
+ * MUL_MAT_ID for BATCHES on the tensor cores -- replaces the host loop of ggml_cuda_mul_mat_id for ne12 > 1
+ * (ggml/src/ggml-cuda/ggml-cuda.cu:2008-2011: ids copied to the host + stream synchronize; :2059-2118: per expert gather
+ * (k_copy_src1_to_contiguous), GEMM, scatter).  Here a device-side plan sorts the (token, slot) pairs by expert, the
+ * activation quantizer gathers rows in that order, ONE persistent tcgen05 GEMM walks the plan's work items over the stacked
+ * planes of all experts and scatters each column to its dst row.  No host synchronization; ids stay on the device.
+ * `plane` = b200_mmq_build_plane over the n_expert * m rows of the packed expert tensor (b200_mmq_plane_size(type,
+ * n_expert * m, k) bytes).  Needs m % 128 == 0.  Same argument meaning as b200_mul_mat_id otherwise.
+ * b200_mul_mat_id_prefers_mmq: 1 when the batch is large enough for this path to win over the GEMV (a few pairs per expert).
+ */
+B200_API int    b200_mul_mat_id_prefers_mmq(int64_t m, int64_t n_expert, int64_t n_used, int64_t n_tokens);
+B200_API size_t b200_mul_mat_id_mmq_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used,
+                                                   int64_t n_tokens);
+B200_API int b200_mul_mat_id_mmq(int type, const void * plane_device, const float * b_device, int64_t b_token_stride,
+                                 int64_t b_slot_stride, int64_t ne11, const int32_t * ids_device, int64_t ids_row_stride,
+                                 float * dst_device, int64_t dst_token_stride, int64_t dst_slot_stride, int64_t m, int64_t k,
+                                 int64_t n_expert, int64_t n_used, int64_t n_tokens, void * workspace_device,
+                                 size_t workspace_bytes, b200_stream_t stream);
+
+/*
  * Row range [*row_low, *row_high) of an m-row weight owned by `rank` of `world` under the reference's tensor_split
  * rule: cumulative fractions, boundaries rounded down to a multiple of 128 rows, last rank takes the remainder
  * (get_row_split / get_row_rounding, ggml/src/ggml-cuda/ggml-cuda.cu:727-753).  tensor_split == NULL => equal split.

@@ -660,6 +660,35 @@ int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const floa
     return B200_OK;
 }
 
+// MUL_MAT_ID for batches on the tensor cores: the plane is that of ALL experts stacked (b200_mmq_build_plane over
+// n_expert * m rows).  Worth it from a few pairs per expert on: the GEMV streams an expert once per 4 pairs.
+int b200_mul_mat_id_prefers_mmq(int64_t m, int64_t n_expert, int64_t n_used, int64_t n_tokens) {
+    const int64_t avg = env_knob("B200_MMID_MMQ_MIN_AVG", 6);   // pairs per expert on average
+    return m > 0 && m % 128 == 0 && n_expert > 0 && n_expert <= 1024 && n_tokens * n_used >= avg * n_expert ? 1 : 0;
+}
+size_t b200_mul_mat_id_mmq_workspace_size(int type, int64_t m, int64_t k, int64_t n_expert, int64_t n_used, int64_t n_tokens) {
+    if (!weight_type(type) || k <= 0 || n_used <= 0 || n_tokens <= 0) return 0;
+    return mmid_mmq_workspace_bytes(m, k, n_expert, n_used * n_tokens);
+}
+int b200_mul_mat_id_mmq(int type, const void * plane, const float * b, int64_t b_token_stride, int64_t b_slot_stride, int64_t ne11,
+                        const int32_t * ids, int64_t ids_row_stride, float * dst, int64_t dst_token_stride,
+                        int64_t dst_slot_stride, int64_t m, int64_t k, int64_t n_expert, int64_t n_used, int64_t n_tokens,
+                        void * workspace, size_t workspace_bytes, b200_stream_t stream) {
+    if (!weight_type(type)) return B200_ERR_TYPE;
+    if (m < 0 || k <= 0 || k % blck_of(type) != 0 || n_expert <= 0 || n_used < 0 || n_tokens < 0 || ne11 <= 0 ||
+        ne11 > (n_used > 0 ? n_used : 1) || ids_row_stride < n_used || k > INT32_MAX)
+        return B200_ERR_SHAPE;
+    if (m == 0 || n_used == 0 || n_tokens == 0) return B200_OK;
+    if (m % 128 != 0) return B200_ERR_UNSUPPORTED;
+    if (!plane || (uintptr_t) plane % 256 != 0 || (uintptr_t) b % 4 != 0 || (uintptr_t) dst % 4 != 0) return B200_ERR_ALIGNMENT;
+    const size_t need = mmid_mmq_workspace_bytes(m, k, n_expert, n_used * n_tokens);
+    if (!need) return B200_ERR_UNSUPPORTED;
+    if (!workspace || workspace_bytes < need) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
+    return launch_mmid_mmq(type, plane, b, b_token_stride, b_slot_stride, ne11, ids, ids_row_stride, dst, dst_token_stride,
+                           dst_slot_stride, m, k, n_expert, n_used, n_tokens, workspace, (cudaStream_t) stream);
+}
+
 // ---------------------------------------------------------------------------------------------------- row split
 int b200_row_split(int64_t m, int world, int rank, const float * tensor_split, int64_t * row_low, int64_t * row_high) {
     if (world <= 0 || rank < 0 || rank >= world || m < 0 || !row_low || !row_high) return B200_ERR_SHAPE;

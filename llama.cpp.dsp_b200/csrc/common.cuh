@@ -82,14 +82,18 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// try_wait with a suspend-time hint: a warp whose barrier phase is not complete sleeps in hardware (up to ~the hint, it is
+// woken by the arrival) instead of spinning.  Without it the polling loops of the waiting roles (TMA producer, MMA issuer,
+// epilogue warps at a chunk start) were 19 % of all issued instructions of the prefill GEMM and competed with the
+// epilogue math for issue slots (profiles/r02/ncu_mmq_p_*_source_summary.txt: BRA / SYNCS / NOP / YIELD).
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(bar), "r"(parity)
+        : "r"(bar), "r"(parity), "r"(0x989680u)
         : "memory");
     return ok != 0;
 }

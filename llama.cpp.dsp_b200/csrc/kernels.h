@@ -89,4 +89,11 @@ int    launch_mmq_multi(int type, int nmat, const void * const * planes, const f
 int    launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                   int64_t n, int64_t k, void * workspace, cudaStream_t stream);
 
+// MUL_MAT_ID on the tensor cores over the stacked plane of all experts (m % 128 == 0, packed experts)
+size_t mmid_mmq_workspace_bytes(int64_t m, int64_t k, int64_t n_expert, int64_t npairs);
+int    launch_mmid_mmq(int type, const void * plane, const float * b, int64_t b_token_stride, int64_t b_slot_stride, int64_t ne11,
+                       const int32_t * ids, int64_t ids_row_stride, float * dst, int64_t dst_token_stride, int64_t dst_slot_stride,
+                       int64_t m, int64_t k, int64_t n_expert, int64_t n_used, int64_t n_tokens, void * workspace,
+                       cudaStream_t stream);
+
 }  // namespace b200

@@ -146,10 +146,17 @@ struct mmq_zero {
     int64_t stride[4];   // elements between rows
     int64_t m[4];
 };
+// MUL_MAT_ID on the tensor cores: output row j of the quantizer is the activation row of the (token, slot) pair that the
+// device-side plan sorted to position j (sorted[j] < 0: padding between two experts' ranges -> a row of zeros)
+struct mmq_gather {
+    const int32_t * sorted;      // nullptr: no gather, row j of x
+    int             n_used, ne11;
+    int64_t         x_token_stride, x_slot_stride;   // elements
+};
 template <int NXP>
 __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ x, int64_t x_stride, int8_t * __restrict__ Q,
                                                      float * __restrict__ Tt, int64_t n, int64_t k, int64_t kp,
-                                                     int64_t npad, const mmq_zero z, bool vec) {
+                                                     int64_t npad, const mmq_zero z, bool vec, const mmq_gather gt) {
     pdl_launch_dependents();   // the GEMM behind us sets up its barriers / TMEM and prefetches its tensor maps meanwhile
     pdl_wait();                // x comes from the previous kernel, and dst may still be read by it
     if (z.cnt) {
@@ -172,7 +179,16 @@ __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ 
     const int64_t e0 = c * MMQ_KC + lane * PL;
     float v[PL];
     const float * xr = x + j * x_stride + e0;
-    if (vec && e0 + PL <= k) {                                  // 16-byte loads (x and its row stride 16-byte aligned)
+    bool          pad_row = false;
+    if (gt.sorted) {
+        const int p = gt.sorted[j];
+        pad_row = p < 0;
+        if (!pad_row) xr = x + (int64_t) (p / gt.n_used) * gt.x_token_stride + (int64_t) ((p % gt.n_used) % gt.ne11) * gt.x_slot_stride + e0;
+    }
+    if (pad_row) {
+#pragma unroll
+        for (int i = 0; i < PL; i++) v[i] = 0.f;
+    } else if (vec && e0 + PL <= k) {                           // 16-byte loads (x and its row stride 16-byte aligned)
 #pragma unroll
         for (int i = 0; i < PL / 4; i++) {
             const float4 f = __ldg(reinterpret_cast<const float4 *>(xr) + i);
@@ -207,6 +223,57 @@ __global__ void __launch_bounds__(256) k_quantize_x8(const float * __restrict__ 
         if (PL == 8) *reinterpret_cast<uint2 *>(qd) = make_uint2(o2[0], o2[1]);
         else *reinterpret_cast<uint4 *>(qd) = make_uint4(o2[0], o2[1], o2[PL / 4 - 2], o2[PL / 4 - 1]);
         if (lane == 0) Tt[(pl * nch + c) * npad + j] = t;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT_ID plan (tensor cores)
+// Replaces the host side of ggml_cuda_mul_mat_id for batches (ggml-cuda.cu:2008-2011 copies ids to the host and SYNCHRONIZES,
+// :2059-2118 gathers rows per expert with k_copy_src1_to_contiguous, runs one GEMM per expert, scatters back): here one
+// CTA sorts the (token, slot) pairs by expert on the device -- every expert's range starts at a multiple of 32 positions so
+// that tiles and scale vectors stay 16-byte aligned -- and writes the GEMM's work items; ids never leave the device.
+//   plan = [hdr: n_items, positions used, 0, 0][sorted: maxpos ints, -1 = padding][items: max_items x {row tile in the stacked
+//           expert matrix, first position, columns, UMMA N}]
+constexpr int MMIDQ_PAD = 32, MMIDQ_MAX_EXPERTS = 1024;
+static inline int64_t mmidq_maxpos(int64_t npairs, int64_t n_expert) { return npairs + MMIDQ_PAD * (n_expert < npairs ? n_expert : npairs); }
+static inline int64_t mmidq_max_items(int64_t npairs, int64_t n_expert, int64_t mt) {
+    return mt * ((n_expert < npairs ? n_expert : npairs) + npairs / 256);
+}
+__global__ void __launch_bounds__(1024) k_mmid_sort(const int32_t * __restrict__ ids, int64_t ids_row_stride, int npairs, int n_used,
+                                                    int n_expert, int mt, int maxpos, int32_t * __restrict__ hdr,
+                                                    int32_t * __restrict__ sorted, int4 * __restrict__ items) {
+    __shared__ int cnt[MMIDQ_MAX_EXPERTS], off[MMIDQ_MAX_EXPERTS], cur[MMIDQ_MAX_EXPERTS], ibase[MMIDQ_MAX_EXPERTS];
+    pdl_launch_dependents();
+    pdl_wait();                                                 // ids come from the router kernels before us
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) cnt[e] = 0, cur[e] = 0;
+    for (int i = threadIdx.x; i < maxpos; i += blockDim.x) sorted[i] = -1;
+    __syncthreads();
+    for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
+        const int e = ids[(int64_t) (p / n_used) * ids_row_stride + p % n_used];
+        if (e >= 0 && e < n_expert) atomicAdd(&cnt[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int pos = 0, it = 0;
+        for (int e = 0; e < n_expert; e++) {
+            off[e] = pos, ibase[e] = it;
+            pos += (cnt[e] + MMIDQ_PAD - 1) / MMIDQ_PAD * MMIDQ_PAD;
+            it  += (cnt[e] + 255) / 256 * mt;
+        }
+        hdr[0] = it, hdr[1] = pos, hdr[2] = hdr[3] = 0;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
+        const int e = ids[(int64_t) (p / n_used) * ids_row_stride + p % n_used];
+        if (e < 0 || e >= n_expert) continue;                   // (an invalid id leaves its dst row untouched)
+        sorted[off[e] + atomicAdd(&cur[e], 1)] = p;             // order inside an expert's range does not matter: every
+    }                                                           // column of the GEMM is computed on its own
+    // items: per expert, 256-position tiles outermost, the expert's m-tiles innermost (they share the activation tile)
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) {
+        int it = ibase[e];
+        for (int n0 = 0; n0 < cnt[e]; n0 += 256) {
+            const int ncols = min(256, cnt[e] - n0), bn = (ncols + 31) / 32 * 32;
+            for (int t = 0; t < mt; t++) items[it++] = make_int4(e * mt + t, off[e] + n0, ncols, bn);
+        }
     }
 }
 
@@ -371,6 +438,27 @@ __device__ __forceinline__ void epi_chunk(uint32_t tbase, const float4 * tp, flo
             release();
         }
         epi_accumulate<EPI, LW>(r[g & 1], tp + g * (LW / 4), sic, acc + g * LW);
+    }
+}
+
+// The same for the persistent kernel, where 64 accumulators per thread leave room for two 8-column load buffers only
+// (96 registers with 18 warps).  NG8 = 8-column groups of this warp's slice (compile time: no per-group predicates, TMEM
+// addresses are immediates).
+template <int EPI, int NG8, typename Release>
+__device__ __forceinline__ void epi_chunk8(uint32_t tbase, const float4 * tp, float sic, float * acc, Release release) {
+    uint32_t r[2][8];
+    tmem_ldw(tbase, r[0]);
+#pragma unroll
+    for (int g = 0; g < NG8; g++) {
+        tmem_ld_wait();
+        if (g + 1 < NG8) {
+            tmem_ldw(tbase + (g + 1) * 8, r[(g + 1) & 1]);
+        } else {                                                 // accumulator fully read: hand it back to the tensor core
+            tc_fence_before();
+            __syncwarp();
+            release();
+        }
+        epi_accumulate<EPI, 8>(r[g & 1], tp + g * 2, sic, acc + g * 8);
     }
 }
 
@@ -619,6 +707,14 @@ struct mmq_pargs {
     int raster;    // 0: consecutive items walk n first, 1: m first (B200_MMQ_RASTER)
     int n_main;    // 128 x 256 items
     int n_items;   // n_main + 128 x 128 tail items
+    // MUL_MAT_ID (k_mmq_p<EPI, true>): the items come from the device-side plan (k_mmid_sort), A is the stacked plane of all
+    // experts, B the activation rows gathered in sorted order, and the epilogue scatters column j to the dst row of pair
+    // sorted[n0 + j]
+    const int4 *    items;
+    const int32_t * hdr;         // hdr[0] = number of items
+    const int32_t * sorted;
+    int             n_used, mt_expert, m_expert;
+    int64_t         dst_token_stride, dst_slot_stride;
 };
 struct mmq_pshape {
     static constexpr int NS      = 4;
@@ -635,6 +731,8 @@ struct mmq_pshape {
 struct mmq_item {
     int mt, n0, bn;    // global m-tile (over all matrices of the launch), first column, width
 };
+template <bool MMID>
+__device__ __forceinline__ mmq_item mmq_item_get(int it, const mmq_pargs & p, int & ncols);
 __device__ __forceinline__ mmq_item mmq_item_of(int it, const mmq_pargs & p) {
     int t, half = 0, bn = 256;
     if (it < p.n_main) t = it;
@@ -648,7 +746,20 @@ __device__ __forceinline__ mmq_item mmq_item_of(int it, const mmq_pargs & p) {
     return r;
 }
 
-template <int EPI>
+template <bool MMID>
+__device__ __forceinline__ mmq_item mmq_item_get(int it, const mmq_pargs & p, int & ncols) {
+    if (MMID) {
+        const int4 v = __ldg(p.items + it);
+        mmq_item r;
+        r.mt = v.x, r.n0 = v.y, r.bn = v.w, ncols = v.z;
+        return r;
+    }
+    const mmq_item r = mmq_item_of(it, p);
+    ncols = r.bn;
+    return r;
+}
+
+template <int EPI, bool MMID>
 __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_constant__ CUtensorMap mapA,
                                                 const __grid_constant__ CUtensorMap mapB, const mmq_kargs a,
                                                 const __grid_constant__ mmq_maps3 mapAx, const mmq_pargs p) {
@@ -680,6 +791,7 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
     const uint32_t tmem = tmem_slot;
     pdl_launch_dependents();
     pdl_wait();                                                 // activations come from the quantizer kernel before us
+    const int n_items = MMID ? __ldg(p.hdr) : p.n_items;        // (MUL_MAT_ID: written by the plan kernel two launches ago)
 
 #ifdef B200_MMQ_TRACE
     long long tw[4] = {0, 0, 0, 0};
@@ -689,8 +801,9 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
         // ------------------------------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             uint32_t st = 0, st_ph = 0, sc = 0, sc_ph = 0;      // stage / scale-slot cursors with their phase bits
-            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-                const mmq_item I = mmq_item_of(it, p);
+            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+                int            ncols_;
+                const mmq_item I = mmq_item_get<MMID>(it, p, ncols_);
                 const CUtensorMap * pA = &mapA;
                 const float *       S  = a.S;
                 int                 mpad = a.mpad, tile = I.mt;
@@ -702,7 +815,7 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                     tile -= first;
                 }
                 const int      m0 = (a.dbg & 2) ? 0 : tile * MMQ_BM;
-                const bool     two = I.bn == 256 && !(a.dbg & 1);
+                const bool     two = I.bn > 128 && !(a.dbg & 1);
                 const uint32_t stage_tx = SH::A_BYTES + (two ? 256u : 128u) * MMQ_BK, scale_tx = (MMQ_BM + (uint32_t) I.bn) * 4;
                 for (int c = 0; c < nch; c++) {
                     int ac, bc;
@@ -736,8 +849,9 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
         // ------------------------------------------------------------------------------------------ MMA issuer
         if (lane == 0) {
             uint32_t st = 0, st_ph = 0, buf = 0, buf_ph = 0;
-            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-                const uint32_t idesc = it < p.n_main ? idesc_i8(MMQ_BM, 256) : idesc_i8(MMQ_BM, 128);
+            for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+                const uint32_t idesc = MMID ? idesc_i8(MMQ_BM, __ldg(p.items + it).w)
+                                            : it < p.n_main ? idesc_i8(MMQ_BM, 256) : idesc_i8(MMQ_BM, 128);
                 for (int c = 0; c < nch; c++) {
                     TW(0, mbar_wait(bar_tempty + 8 * buf, buf_ph ^ 1));   // epilogue has drained this accumulator
                     tc_fence_after();
@@ -769,8 +883,8 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
         const int q = warp & 3, part = (warp - 2) >> 2;          // TMEM lane quarter (warp id % 4), column part 0..3
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         uint32_t sc = 0, sc_ph = 0, buf = 0, buf_ph = 0;
-        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-            const int ncw = (it < p.n_main ? 256 : 128) >> 2;   // columns per warp (64 / 32)
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+            const int ncw = (MMID ? __ldg(p.items + it).w : it < p.n_main ? 256 : 128) >> 2;   // columns per warp (8 .. 64)
             const int col0 = part * ncw;
             __align__(8) float acc[64];
 #pragma unroll
@@ -785,29 +899,16 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + buf * 256 + col0;
                 // Software pipeline over 8-column loads: the load of group g + 1 is in flight while group g is scaled and
                 // accumulated (tcgen05.wait::ld waits for ALL outstanding loads, so the next load is issued right after the
-                // wait that delivered the current one).  All 16 epilogue warps start a chunk together, so without this they
-                // would alternate "everybody loads" / "everybody computes" and the load latency would never be hidden.
-                // Two 8-column buffers cost the registers of one 16-column load (64 accumulators leave no more under the
-                // 96 registers that 18 warps get).
-                {
-                    const int ng8 = ncw >> 3;                    // 8 or 4 groups
-                    uint32_t r[2][8];
-                    tmem_ldw(tbase, r[0]);
-#pragma unroll
-                    for (int g = 0; g < 8; g++) {
-                        if (g < ng8) {                           // warp-uniform
-                            tmem_ld_wait();
-                            if (g + 1 < ng8) {
-                                tmem_ldw(tbase + (g + 1) * 8, r[(g + 1) & 1]);
-                            } else {                             // accumulator fully read: hand it back to the tensor core
-                                tc_fence_before();
-                                __syncwarp();
-                                if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
-                            }
-                            epi_accumulate<EPI, 8>(r[g & 1], tp + g * 2, sic, acc + g * 8);
-                        }
-                    }
-                }
+                // wait that delivered the current one).
+                auto release = [&] { if (lane == 0) mbar_arrive(bar_tempty + 8 * buf); };
+                if (ncw == 64) epi_chunk8<EPI, 8>(tbase, tp, sic, acc, release);
+                else if (!MMID || ncw == 32) epi_chunk8<EPI, 4>(tbase, tp, sic, acc, release);
+                else if (ncw == 8)  epi_chunk8<EPI, 1>(tbase, tp, sic, acc, release);
+                else if (ncw == 16) epi_chunk8<EPI, 2>(tbase, tp, sic, acc, release);
+                else if (ncw == 24) epi_chunk8<EPI, 3>(tbase, tp, sic, acc, release);
+                else if (ncw == 40) epi_chunk8<EPI, 5>(tbase, tp, sic, acc, release);
+                else if (ncw == 48) epi_chunk8<EPI, 6>(tbase, tp, sic, acc, release);
+                else                epi_chunk8<EPI, 7>(tbase, tp, sic, acc, release);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_sempty + 8 * sc);
                 if (++sc == NSC) sc = 0, sc_ph ^= 1;
@@ -816,6 +917,30 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
 #ifdef B200_MMQ_TRACE
             const long long t_st = clock64();
 #endif
+            if (MMID) {
+                // scatter: column j of the item belongs to pair sorted[n0 + j]; lanes look the dst rows up together
+                int            ncols;
+                const mmq_item I = mmq_item_get<true>(it, p, ncols);
+                const int      row = (I.mt % p.mt_expert) * MMQ_BM + q * 32 + lane;
+                int64_t        off[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int j = col0 + 32 * h + lane;
+                    off[h] = -1;
+                    if (32 * h + lane < ncw && j < ncols) {
+                        const int pr = __ldg(p.sorted + I.n0 + j);
+                        if (pr >= 0) off[h] = (int64_t) (pr / p.n_used) * p.dst_token_stride + (int64_t) (pr % p.n_used) * p.dst_slot_stride;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 64; i++) {
+                    if (i < ncw) {                               // warp-uniform
+                        const int64_t o = __shfl_sync(0xffffffffu, off[i >> 5], i & 31);
+                        if (o >= 0 && row < p.m_expert) a.dst[o + row] = acc[i];
+                    }
+                }
+                continue;
+            }
             // where the item's results go (worked out only now: it would cost ten live registers across the chunk loop)
             const mmq_item I = mmq_item_of(it, p);
             float *  dstp = a.dst;
@@ -963,9 +1088,9 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
 // persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
                                  const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
-    auto kern = k_mmq_p<MMQ_EPI_DEFAULT>;
+    auto kern = k_mmq_p<MMQ_EPI_DEFAULT, false>;
     B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
-    mmq_pargs p;
+    mmq_pargs p = {};
     p.ntn = (a.n + 255) / 256;
     p.mtiles = mtiles;
     p.raster = env_flag("B200_MMQ_RASTER", 0);
@@ -995,7 +1120,8 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
 }
 
 static int launch_quantize_x8(int nxp, const float * x, int64_t x_stride, int8_t * Q, float * Tt, int64_t n, int64_t k,
-                              int64_t kp, int64_t npad, const mmq_zero & z, cudaStream_t stream) {
+                              int64_t kp, int64_t npad, const mmq_zero & z, cudaStream_t stream, const mmq_gather & gt = {},
+                              bool vec_ok = true) {
     const int64_t warps = n * (kp / MMQ_KC);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim  = dim3((unsigned) ((warps + 7) / 8), 1, 1);
@@ -1005,9 +1131,9 @@ static int launch_quantize_x8(int nxp, const float * x, int64_t x_stride, int8_t
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    const bool vec = (uintptr_t) x % 16 == 0 && x_stride % 4 == 0;
-    if (nxp == 2) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<2>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
-    else          B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<1>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec));
+    const bool vec = vec_ok && (uintptr_t) x % 16 == 0 && x_stride % 4 == 0;
+    if (nxp == 2) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<2>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec, gt));
+    else          B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_quantize_x8<1>, x, x_stride, Q, Tt, n, k, kp, npad, z, vec, gt));
     note_launch();
     return B200_OK;
 }
@@ -1095,6 +1221,85 @@ int launch_mmq_multi(int type, int nmat, const void * const * planes, const floa
 int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
     return launch_mmq_multi(type, 1, &plane, x, x_stride, &dst, &dst_stride, &m, n, k, workspace, stream);
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT_ID on tensor cores
+// workspace = [plan: hdr | sorted | items][Q: maxpos x (nxp * kpad) int8][t: (nxp * nchunks) x npad f32]
+static inline size_t mmidq_plan_bytes(int64_t npairs, int64_t n_expert, int64_t mt) {
+    return align256(16 + (size_t) mmidq_maxpos(npairs, n_expert) * 4) + align256((size_t) mmidq_max_items(npairs, n_expert, mt) * 16);
+}
+size_t mmid_mmq_workspace_bytes(int64_t m, int64_t k, int64_t n_expert, int64_t npairs) {
+    if (m <= 0 || m % MMQ_BM != 0 || n_expert <= 0 || n_expert > MMIDQ_MAX_EXPERTS || npairs <= 0) return 0;
+    const int64_t maxpos = mmidq_maxpos(npairs, n_expert), kp = mmq_kpad(k);
+    return mmidq_plan_bytes(npairs, n_expert, m / MMQ_BM) + align256((size_t) maxpos * 2 * kp) +
+           align256((size_t) 2 * (kp / MMQ_KC) * (((maxpos + 3) & ~(int64_t) 3) + 256) * 4) + 2048;
+}
+int launch_mmid_mmq(int type, const void * plane, const float * b, int64_t b_token_stride, int64_t b_slot_stride, int64_t ne11,
+                    const int32_t * ids, int64_t ids_row_stride, float * dst, int64_t dst_token_stride, int64_t dst_slot_stride,
+                    int64_t m, int64_t k, int64_t n_expert, int64_t n_used, int64_t n_tokens, void * workspace,
+                    cudaStream_t stream) {
+    const int sm_count = sm_count_current_device();
+    if (!sm_count) return B200_ERR_CUDA;
+    const int64_t npairs = n_tokens * n_used, mt = m / MMQ_BM;
+    if (m % MMQ_BM != 0 || n_expert > MMIDQ_MAX_EXPERTS || npairs > INT32_MAX / 2 || n_expert * m > INT32_MAX) return B200_ERR_UNSUPPORTED;
+    const int     nwp = mmq_nplanes(type), nxp = mmq_xplanes(type);
+    const int64_t kp = mmq_kpad(k), nch = kp / MMQ_KC, maxpos = mmidq_maxpos(npairs, n_expert),
+                  npad = ((maxpos + 3) & ~(int64_t) 3) + 256;   // pitch of the scale rows: a multiple of 16 bytes (bulk copies)
+    const int64_t max_items = mmidq_max_items(npairs, n_expert, mt), M = n_expert * m;
+    uint8_t * w      = (uint8_t *) workspace;
+    int32_t * hdr    = (int32_t *) w;
+    int32_t * sorted = hdr + 4;
+    int4 *    items  = (int4 *) (w + align256(16 + (size_t) maxpos * 4));
+    int8_t *  Q      = (int8_t *) (w + mmidq_plan_bytes(npairs, n_expert, mt));
+    float *   Tt     = (float *) ((uint8_t *) Q + align256((size_t) maxpos * nxp * kp));
+    {   // 1. the plan: pairs sorted by expert, work items
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(1, 1, 1), cfg.blockDim = dim3(1024, 1, 1), cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr, cfg.numAttrs = 1;
+        B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_mmid_sort, ids, ids_row_stride, (int) npairs, (int) n_used, (int) n_expert, (int) mt,
+                                         (int) maxpos, hdr, sorted, items));
+        note_launch();
+    }
+    {   // 2. activation rows gathered in sorted order while they are quantized
+        mmq_gather gt = {};
+        gt.sorted = sorted, gt.n_used = (int) n_used, gt.ne11 = (int) ne11;
+        gt.x_token_stride = b_token_stride, gt.x_slot_stride = b_slot_stride;
+        const bool vec_ok = b_token_stride % 4 == 0 && b_slot_stride % 4 == 0;
+        const int st = launch_quantize_x8(nxp, b, 0, Q, Tt, maxpos, k, kp, npad, mmq_zero{}, stream, gt, vec_ok);
+        if (st != B200_OK) return st;
+    }
+    // 3. the GEMM over the stacked expert planes
+    CUtensorMap mapA, mapB;
+    int st = make_map(&mapB, Q, maxpos, nxp * kp, 128);
+    if (st != B200_OK) return st;
+    st = make_map(&mapA, plane, M, nwp * kp, MMQ_BM);
+    if (st != B200_OK) return st;
+    mmq_kargs a = {};
+    a.S = (const float *) ((const uint8_t *) plane + align256((size_t) M * nwp * kp));
+    a.Tt = Tt, a.dst = dst, a.dst_stride = m, a.m = (int) M, a.n = (int) maxpos, a.nch = (int) nch, a.npad = (int) npad;
+    a.mpad = (int) mmq_mpad(M), a.nmat = 1, a.ksplit = 1, a.nseg = 1;
+    if (nxp == 2) a.seg_a[a.nseg] = 0, a.seg_b[a.nseg] = (int) nch, a.nseg++;
+    if (nwp == 2) a.seg_a[a.nseg] = (int) nch, a.seg_b[a.nseg] = 0, a.nseg++;
+    mmq_pargs p = {};
+    p.items = items, p.hdr = hdr, p.sorted = sorted, p.n_used = (int) n_used, p.mt_expert = (int) mt, p.m_expert = (int) m;
+    p.dst_token_stride = dst_token_stride, p.dst_slot_stride = dst_slot_stride;
+    auto kern = k_mmq_p<MMQ_EPI_DEFAULT, true>;
+    B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
+    const int64_t grid = max_items < sm_count ? max_items : sm_count;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) grid, 1, 1), cfg.blockDim = dim3(mmq_pshape::THREADS, 1, 1);
+    cfg.dynamicSmemBytes = mmq_pshape::SMEM, cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    static const mmq_maps3 none = {};
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, mapA, mapB, a, none, p));
+    note_launch();
+    return B200_OK;
 }
 
 }  // namespace b200

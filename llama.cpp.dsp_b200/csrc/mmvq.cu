@@ -449,6 +449,10 @@ static bool make_plan(int type, int64_t k, int ncols, bool contiguous, int64_t r
         int vfirst = 8;
         while (vfirst > 2 && (rows_per_cta < (int64_t) P.nteams * vfirst || (size_t) vfirst * P.row_pitch * 3 > budget))
             vfirst >>= 1;
+        // long rows (k >= 6144: four or more warps per row, at most four teams): 4 rows per stage.  8-row stages leave each
+        // team a single ring slot, 2-row stages pay the per-stage costs twice; measured 10-17 % faster on the 70B row
+        // lengths (k = 8192, 28672) for Q4_K and Q6_K alike, equal at worst (profiles/r02/gemv_sweep_70b.log)
+        if (T >= 4 && (size_t) 4 * P.row_pitch * 2 + 64 <= budget) vfirst = 4;
         vfirst = env_int("B200_GEMV_V", vfirst);
         for (int V = vfirst; V >= 2; V >>= 1) {
             // payload + 15 bytes of leading misalignment + 16 so word reads of a 2-byte-aligned tail stay inside

@@ -774,6 +774,22 @@ static void b200_compute_mul_mat_id(b200_backend_context * ctx, ggml_tensor * ds
     const int64_t n_tokens = ids->ne[1];
     if (ggml_nelements(dst) == 0) return;
 
+    // batches: the tensor cores over the stacked int8 plane of all experts (cached with the weight buffer like the
+    // MUL_MAT planes); the GEMV would stream an expert once per 4 pairs
+    if (b200_mul_mat_id_prefers_mmq(m, n_expert, n_used, n_tokens) && nb02 == (size_t) m * ggml_row_size(src0->type, k)) {
+        ggml_backend_buffer_t wbuf = src0->view_src ? src0->view_src->buffer : src0->buffer;
+        b200_plane_key key = {src0->data, (int64_t) nb01, n_expert * m, k, type};
+        const void * plane = ((b200_buffer_context *) wbuf->context)->get_plane(key, wbuf->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS,
+                                                                              ctx->stream);
+        if (plane) {
+            const size_t wsb = b200_mul_mat_id_mmq_workspace_size(type, m, k, n_expert, n_used, n_tokens);
+            void *       wsp = ctx->scratch(wsb);
+            B200_CHECK(b200_mul_mat_id_mmq(type, plane, (const float *) src1->data, nb12 / 4, nb11 / 4, ne11,
+                                           (const int32_t *) ids->data, ids->nb[1] / 4, (float *) dst->data, nb2 / 4, nb1 / 4, m, k,
+                                           n_expert, n_used, n_tokens, wsp, ctx->workspace_bytes, ctx->stream));
+            return;
+        }
+    }
     const size_t ws_bytes = b200_mul_mat_id_workspace_size(type, m, k, n_expert, n_used, n_tokens);
     void *       ws       = ws_bytes ? ctx->scratch(ws_bytes) : nullptr;
     B200_CHECK(b200_mul_mat_id(type, src0->data, nb02, (const float *) src1->data, nb12 / 4, nb11 / 4, ne11,

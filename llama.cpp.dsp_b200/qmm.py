@@ -30,6 +30,7 @@ EXPORTS = [
     "b200_noalloc_scratch_size", "b200_mul_mat_noalloc",
     "b200_sequence_plan_size", "b200_sequence_plan_build", "b200_sequence_run", "b200_sequence_status",
     "b200_debug_sequence_trace",
+    "b200_mul_mat_id_prefers_mmq", "b200_mul_mat_id_mmq_workspace_size", "b200_mul_mat_id_mmq",
 ]
 
 
@@ -112,6 +113,10 @@ def lib():
     L.b200_sequence_run.argtypes = [vp, vp]
     L.b200_sequence_status.argtypes = [vp, C.POINTER(i32), vp]
     L.b200_debug_sequence_trace.argtypes = [vp, vp, vp]
+    L.b200_mul_mat_id_prefers_mmq.argtypes = [i64, i64, i64, i64]
+    L.b200_mul_mat_id_mmq_workspace_size.restype = sz
+    L.b200_mul_mat_id_mmq_workspace_size.argtypes = [i32, i64, i64, i64, i64, i64]
+    L.b200_mul_mat_id_mmq.argtypes = [i32, vp, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp, sz, vp]
     L.b200_reload_env.restype = None
     L.b200_debug_gemv_trace.restype = None
     L.b200_debug_gemv_trace.argtypes = [vp, i64]
@@ -404,4 +409,21 @@ def mul_mat_id(t, w, b, ids, m, k, n_expert, out=None, stream=None):
     check(lib().b200_mul_mat_id(t, w.data_ptr(), 0, b.data_ptr(), b.stride(0), b.stride(1), ne11, ids.data_ptr(),
                                 ids.stride(0), dst.data_ptr(), dst.stride(0), dst.stride(1), m, k, n_expert, n_used,
                                 n_tokens, ws, wsz, _stream_ptr(stream)))
+    return dst
+
+
+def mul_mat_id_mmq(t, plane, b, ids, m, k, n_expert, out=None, stream=None):
+    """MUL_MAT_ID on the tensor cores: plane = build_plane(t, w, n_expert * m, k) of the stacked experts; b, ids, dst as in
+    mul_mat_id.  Rows of dst whose id is invalid are left untouched."""
+    import torch
+    _require_cuda(plane, b, ids)
+    assert b.dtype == torch.float32 and b.dim() == 3 and b.stride(2) == 1
+    assert ids.dtype == torch.int32 and ids.dim() == 2 and ids.stride(1) == 1
+    n_tokens, ne11, _ = b.shape
+    n_used = ids.shape[1]
+    dst = out if out is not None else torch.empty((n_tokens, n_used, m), dtype=torch.float32, device=b.device)
+    ws, wsz = _workspace(b.device, lib().b200_mul_mat_id_mmq_workspace_size(t, m, k, n_expert, n_used, n_tokens))
+    check(lib().b200_mul_mat_id_mmq(t, plane.data_ptr(), b.data_ptr(), b.stride(0), b.stride(1), ne11, ids.data_ptr(),
+                                    ids.stride(0), dst.data_ptr(), dst.stride(0), dst.stride(1), m, k, n_expert, n_used,
+                                    n_tokens, ws, wsz, _stream_ptr(stream)))
     return dst

@@ -590,3 +590,42 @@ def test_sequence_many_independent_groups_and_limits(qmm):
     assert L.b200_sequence_plan_size(0) == 0
     grp = (qmm.qmm.SeqGroup * 1)()
     assert L.b200_sequence_plan_build(grp, 1, None, 0, None) != 0
+
+
+# ------------------------------------------------------------------------------------------------ MUL_MAT_ID on tensor cores
+@pytest.mark.parametrize("name,t", TYPES)
+@pytest.mark.parametrize("n_expert,n_used,n_tokens,bcast,m", [(8, 2, 32, True, 256), (4, 2, 129, False, 128), (8, 4, 600, True, 384),
+                                                              (16, 1, 40, True, 128), (4, 4, 9, False, 256)])
+def test_mul_mat_id_tensor_cores(qmm, name, t, n_expert, n_used, n_tokens, bcast, m):
+    """batched MUL_MAT_ID through b200_mul_mat_id_mmq: device-side sort of the pairs by expert (ranges of 1 .. >256 pairs:
+    several 256-column items per expert, narrow UMMA N for short ranges, experts nobody chose), gather in the quantizer,
+    scatter in the epilogue.  Tight vs the restatement of the tensor-core arithmetic per pair, harness bound vs ggml-cpu
+    semantics, bit-identical from run to run, and rows of dst that belong to no valid pair stay untouched."""
+    rng = np.random.default_rng(n_expert * 1000 + n_used * 10 + n_tokens)
+    k = 512
+    ne11 = 1 if bcast else n_used
+    w = qref.random_blocks(t, n_expert * m, k, rng)
+    b = rng.uniform(-1, 1, (n_tokens, ne11, k)).astype(np.float32)
+    # a skewed router (expert 0 is hot), distinct experts per token (ggml's top-k), one expert nobody chooses when >= 8
+    E = n_expert - (1 if n_expert >= 8 else 0)
+    probs = np.array([0.5] + [0.5 / (E - 1)] * (E - 1))
+    ids_full = np.zeros((n_tokens, n_expert), dtype=np.int32)
+    for r in range(n_tokens):
+        ids_full[r, :n_used] = rng.choice(E, n_used, replace=False, p=probs)
+    ids = np.ascontiguousarray(ids_full[:, :n_used])
+    ids_dev = dev(ids_full)[:, :n_used]                          # a strided view, like the harness passes
+    plane = qmm.build_plane(t, dev(w), n_expert * m, k)
+    out = torch.full((n_tokens, n_used, m), 7.5, device="cuda")
+    got = qmm.mul_mat_id_mmq(t, plane, dev(b), ids_dev, m, k, n_expert, out=out).clone()
+    out.fill_(-2.0)
+    assert torch.equal(qmm.mul_mat_id_mmq(t, plane, dev(b), ids_dev, m, k, n_expert, out=out), got)
+    g = got.cpu().numpy()
+    assert np.isfinite(g).all() and not (g == 7.5).any()
+    want = np.zeros_like(g)
+    for tok in range(n_tokens):
+        for s_ in range(n_used):
+            e = ids[tok, s_]
+            want[tok, s_] = qref.mul_mat_plane(t, w[e * m:(e + 1) * m], b[tok, s_ % ne11][None], m, k)[0]
+    assert qref.nmse(want, g) < NMSE_TIGHT
+    assert qref.nmse(qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "cpu"), g) < NMSE_HARNESS
+    assert qmm.lib().b200_mul_mat_id_prefers_mmq(m, n_expert, n_used, n_tokens) in (0, 1)

@@ -65,7 +65,14 @@ def main():
     if "--big" in args:      # ring geometry on the shapes that carry the bytes of a decode token
         shapes = [(28672, 4096), (14336, 4096), (4096, 14336), (6144, 4096), (4096, 4096)]
         ns = (1,)
+    if "--70b" in args:      # the row lengths of the Llama-3-70B-shaped token (bench.py headline)
+        shapes = [(10240, 8192), (8192, 8192), (57344, 8192), (8192, 28672)]
+        ns = (1,)
     configs = [{}] if quick else [
+        {}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 2}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 12}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 16},
+        {"B200_GEMV_V": 2, "B200_GEMV_STAGES": 16}, {"B200_GEMV_V": 2, "B200_GEMV_STAGES": 24}, {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 3},
+        {"B200_GEMV_V": 4, "B200_GEMV_TEAMS": 3, "B200_GEMV_STAGES": 9}, {"B200_GEMV_V": 4, "B200_GEMV_TEAMS": 2, "B200_GEMV_STAGES": 8},
+    ] if "--70b" in args else [
         {}, {"B200_GEMV_V": 4}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 24}, {"B200_GEMV_V": 4, "B200_GEMV_STAGES": 32},
         {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 6}, {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 4},
         {"B200_GEMV_V": 8, "B200_GEMV_TEAMS": 4, "B200_GEMV_STAGES": 12}, {"B200_GEMV_V": 2, "B200_GEMV_STAGES": 32},
