@@ -250,6 +250,19 @@ typedef struct {
 B200_API size_t b200_sequence_plan_size(int ngroups);
 B200_API int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes,
                                       b200_stream_t stream);
+/*
+ * The plan of ONE RANK of a split-mode-row sequence over `world` GPUs (one process per GPU) -- replaces the row-split
+ * choreography of ggml_cuda_op_mul_mat for a whole decode token (ggml/src/ggml-cuda/ggml-cuda.cu:1560-1700: per matmul a
+ * broadcast of the activations, peer copies of the result slices, events).  `groups` describe this rank's row slices
+ * (W = its rows, m = their count, dst = full result + row_low; b200_row_split gives the ranges).  Every dst lies inside
+ * this rank's symmetric allocation [peer_base[rank], + span_bytes); peer_base[r] and peer_sync[r] are rank r's allocation
+ * and counter array (>= 2 * ngroups ints, zeroed once) mapped into this process (b200_ipc_*).  The kernel's epilogue
+ * stores every row into all ranks' allocations over NVLink and publishes groups with system-scope counters, so each rank
+ * holds the whole dst when its b200_sequence_run returns.  All ranks run their plans the same number of times.
+ */
+B200_API int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, int ngroups, void * plan_device,
+                                               size_t plan_bytes, int world, int rank, void * const * peer_base,
+                                               size_t span_bytes, int32_t * const * peer_sync, b200_stream_t stream);
 B200_API int b200_sequence_run(void * plan_device, b200_stream_t stream);
 /* *error_group = 0: fine; g > 0: dependent group g timed out waiting for earlier groups (synchronizes the stream) */
 B200_API int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t stream);

@@ -10,8 +10,9 @@
 // 226 KB of shared memory).  Here one CTA per SM stays resident for the whole sequence:
 //  * a "group" = up to 4 weight matrices that read the same activation vector (q/k/v, gate/up), exactly the unit of
 //    b200_mul_mat_multi; groups are executed in list order;
-//  * warp 16 walks the (group, stage) list of its CTA and keeps issuing bulk TMA copies of weight rows into ONE ring of
-//    uniform slots shared by all groups (stage number q -> slot q % NS, mbarrier phase q / NS), so the next group's first
+//  * warp 16 walks the (group, stage) list of its CTA and keeps issuing bulk TMA copies of weight rows into ONE byte ring
+//    shared by all groups (stage number q -> mbarrier q % 32, phase q / 32; its bytes are allocated circularly, each group
+//    with the stage size that suits its row length), so the next group's first
 //    stages are requested while the compute warps finish the current one, wait for the other CTAs and quantize the next
 //    activations: weights never depend on earlier results.  Consumers look at a stage's barrier only after the issue
 //    warp has published "stage q issued" -- the slot's previous phase is then known to be complete, which is what makes
@@ -44,9 +45,9 @@ namespace b200 {
 
 constexpr int SEQ_NW       = 16;                 // compute warps; warp SEQ_NW issues the TMA copies
 constexpr int SEQ_THREADS  = (SEQ_NW + 1) * 32;
-constexpr int SEQ_MAXSLOTS = 32;                 // ring slots
+constexpr int SEQ_MAXSLOTS = 32;                 // stages in flight at most (barriers); a power of two
 constexpr int SEQ_SMEM     = 226 * 1024;
-constexpr int SEQ_CTRL     = 1280;               // barriers, counters, three staged group descriptors
+constexpr int SEQ_CTRL     = 1664;               // barriers, counters, three staged group descriptors, peer tables, stage offsets
 constexpr int SEQ_PART     = 256;                // bytes of partial sums per slot: V * T <= 64 floats
 constexpr int SEQ_MAXSEG   = 4;
 
@@ -68,9 +69,18 @@ struct seq_group {
 static_assert(sizeof(seq_group) == 176, "seq_group layout");
 struct seq_header {         // first bytes of the plan (device memory)
     int ngroups, exitc, error, act_bytes;   // act_bytes: shared memory reserved for the quantized activations
-    int nslots, slot_bytes, pad[2];          // ring geometry, the same for every group of the sequence
+    int ring_bytes, pad[3];                  // bytes of the weight ring (the rest of shared memory)
     unsigned long long * trace;              // profiling aid (tools/seq_trace.py): 8 globaltimer stamps per (group, CTA)
     unsigned long long   pad2;
+    // ---- split-mode row over `world` GPUs (one process and one plan per GPU; world == 1: everything below is unused)
+    // Every rank's result buffers live at the same offsets of a "symmetric" allocation; a row this rank computes is stored
+    // at that offset in EVERY rank's allocation (peer_delta[r] = rank r's base - this rank's base, NVLink-mapped), so each
+    // rank ends up with the whole dst -- the next group's activations.  done[] lives in a sync block that every rank maps:
+    // a CTA publishes a group with one system-scope release add per rank, consumers wait for world * gridDim.x arrivals.
+    int       world, rank;
+    int       epoch, pad3;                   // launches of this plan so far: the counters are never reset, targets grow
+    long long peer_delta[16];
+    int *     peer_done[16];                 // every rank's counter array (2 * ngroups ints); [rank] = the local one
 };
 // plan = [seq_header][done: ngroups ints, padded to 16][seq_group x ngroups]
 __host__ __device__ static inline size_t seq_done_bytes(int ng) { return ((size_t) ng * 4 + 15) & ~(size_t) 15; }
@@ -90,6 +100,14 @@ __device__ __forceinline__ void seq_stamp(unsigned long long * tr, int g, int nc
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         tr[((size_t) g * ncta + cta) * 8 + i] = t;
     }
+}
+__device__ __forceinline__ int ld_acquire_sys(const int * p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_relaxed_sys_add(int * p, int v) {
+    asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void red_release_gpu_add(int * p, int v) {
     asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -154,18 +172,23 @@ __device__ __forceinline__ int ld_acquire_cta_shared(uint32_t addr) {
 __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restrict__ plan, int evict_first) {
     extern __shared__ __align__(128) uint8_t smem[];
     seq_header *      H      = reinterpret_cast<seq_header *>(plan);
-    const int         ng     = H->ngroups;
-    int *             done   = reinterpret_cast<int *>(plan + sizeof(seq_header));
+    const int         ng     = H->ngroups, world = H->world, rank = H->rank;
+    int *             done   = world > 1 ? H->peer_done[rank] : reinterpret_cast<int *>(plan + sizeof(seq_header));
     const seq_group * groups = reinterpret_cast<const seq_group *>(plan + sizeof(seq_header) + seq_done_bytes(ng));
-    const int         act_bytes = H->act_bytes, NS = H->nslots, S = H->slot_bytes;
+    const int         act_bytes = H->act_bytes;
+    const uint32_t    R = (uint32_t) H->ring_bytes;
+    constexpr int     NB = SEQ_MAXSLOTS;
     unsigned long long * const trace = H->trace;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int G = gridDim.x, cta = blockIdx.x;
 
-    // shared memory: [control][partial sums: 256 B per slot][q8 activations: act_bytes][ring: NS slots of S bytes]
-    //   control: full[32], empty[32] mbarriers; arrived[32] ints; issued (stages the producer has issued so far)
-    // Stage number q (this CTA's stages of all groups, in order) lives in slot q % NS, barrier phase q / NS.
+    // shared memory: [control][partial sums: 256 B per barrier][q8 activations: act_bytes][ring: R bytes]
+    //   control: full[32], empty[32] mbarriers; arrived[32] ints; issued (stages the producer has issued so far);
+    //   st_off[32]: where in the ring a stage's bytes start
+    // Stage number q (this CTA's stages of all groups, in order) uses barrier q % 32, phase q / 32, and a piece of the ring
+    // allocated circularly by the producer: stages of different groups have different sizes (rows per stage x row bytes),
+    // so every group fills the ring with a stage size that suits its row length.
     const uint32_t ctrl      = smem_u32(smem);
     const uint32_t bar_full  = ctrl, bar_empty = ctrl + 8 * SEQ_MAXSLOTS;
     int * const    arrived   = reinterpret_cast<int *>(smem + 16 * SEQ_MAXSLOTS);
@@ -173,6 +196,10 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
     // With 226 KB of shared memory carved out, L1 is a few KB: a descriptor field read from global memory is an L2 round
     // trip.  The group in work is therefore staged in shared memory, one copy for the compute warps (written at the group
     // boundary) and one for the producer (which runs ahead).
+    // split mode: where a result row goes in every peer, and every peer's counters (staged: read per stored row / per group)
+    long long * const pdelta = reinterpret_cast<long long *>(smem + 1280);
+    int ** const      pdone  = reinterpret_cast<int **>(smem + 1408);
+    volatile uint32_t * const st_off = reinterpret_cast<volatile uint32_t *>(smem + 1536);
     seq_group * const Gc  = reinterpret_cast<seq_group *>(smem + 704);
     seq_group * const Gq2 = reinterpret_cast<seq_group *>(smem + 704 + sizeof(seq_group));   // [2]: this group / the next one
     float * const  partials  = reinterpret_cast<float *>(smem + SEQ_CTRL);
@@ -188,6 +215,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
         *reinterpret_cast<volatile int *>(smem + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS) = 0;
         mbar_fence_init();
     }
+    if (threadIdx.x < 16) pdelta[threadIdx.x] = H->peer_delta[threadIdx.x], pdone[threadIdx.x] = H->peer_done[threadIdx.x];
     __syncthreads();
     pdl_launch_dependents();
 
@@ -201,7 +229,8 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
         // ---------------------------------------------------------------------------------------- TMA issue warp (lane 0)
         if (lane == 0) {
             const uint64_t policy = evict_first ? l2_policy_evict_first() : 0;
-            int q = 0, slot = 0, eph = 1;                       // stages issued; slot = q % NS; parity of empty[slot]'s LAST phase
+            int      q = 0, freed = 0;                          // stages issued / stages known to be consumed (in order)
+            uint32_t head = 0, tail = 0;                        // ring: in-flight bytes lie from tail to head, circularly
             // descriptors come through cp.async, one group ahead, so that a group switch costs no L2 round trip
             auto fetch = [&](int g) {
                 const uint32_t d = smem_u32(&Gq2[g & 1]);
@@ -239,18 +268,33 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                     uint64_t  ga = (uint64_t) (Gq->seg[seg].W + (int64_t) r0 * row_bytes);
                     const uint32_t step = (uint32_t) V * (uint32_t) row_bytes;
                     for (; st < end; st++, q++) {
-                        if (q >= NS) mbar_wait(bar_empty + 8 * slot, (uint32_t) eph);   // stage q - NS is consumed
                         const int      nr   = V < m - r0 ? V : m - r0;
                         const uint64_t g0   = ga & ~(uint64_t) 15;
                         const uint32_t span = (uint32_t) (((ga + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
-                        const uint32_t bar  = bar_full + 8 * slot;
+                        const uint32_t sz   = (span + 127) & ~127u;
+                        // room for sz bytes: at head, or at 0 when the end of the ring is too short; otherwise wait for the
+                        // oldest stage in flight (this thread is the only waiter on the empty barriers and takes them in order)
+                        for (;;) {
+                            if (freed == q) { head = tail = 0; break; }
+                            if (q - freed < NB) {
+                                if (head > tail) {
+                                    if (head + sz <= R) break;
+                                    if (sz <= tail) { head = 0; break; }
+                                } else if (head + sz <= tail) break;
+                            }
+                            mbar_wait(bar_empty + 8 * (freed & (NB - 1)), (uint32_t) ((freed / NB) & 1));
+                            freed++;
+                            tail = st_off[freed & (NB - 1)];   // (meaningless when nothing is in flight: handled above)
+                        }
+                        st_off[q & (NB - 1)] = head;
+                        const uint32_t bar  = bar_full + 8 * (q & (NB - 1));
                         mbar_expect_tx(bar, span);
-                        if (evict_first) tma_load_1d_hint(ring + slot * S, (const void *) g0, span, bar, policy);
-                        else tma_load_1d(ring + slot * S, (const void *) g0, span, bar);
+                        if (evict_first) tma_load_1d_hint(ring + head, (const void *) g0, span, bar, policy);
+                        else tma_load_1d(ring + head, (const void *) g0, span, bar);
+                        head += sz;
                         // consumers look at a stage's barrier only once it has been issued: the slot's previous phase is
                         // then known to be complete, so a parity wait cannot be satisfied by the phase before it
                         st_release_cta_shared(issued_a, q + 1);
-                        if (++slot == NS) slot = 0, eph ^= 1;
                         ga += step, r0 += V;
                     }
                 }
@@ -259,18 +303,36 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
     } else {
         // -------------------------------------------------------------------------------------------- compute warps
         pdl_wait();                                             // x and dst may still be in use by the previous kernel
+        // arrivals a group's counter must have reached in THIS launch: the counters only ever grow (no reset to race with)
+        const int target = (H->epoch + 1) * world * G;
         int qbase = 0;                                          // this CTA's stages in earlier groups
         for (int g = 0; g <= ng; g++) {
             // ---- group boundary: every compute warp is done with the previous group's stages, activations and descriptor
             named_bar_sync(1, SEQ_NW * 32);
             if (threadIdx.x == 0 && g > 0) {
-                // the barrier ordered every warp's dst stores of group g - 1 before this thread: one gpu-scope release
-                // publishes this CTA's rows of it.  Every CTA arrives for every group, in order (with or without rows in it),
-                // so done[g - 1] == gridDim.x means that ALL groups <= g - 1 are complete everywhere.
-                __threadfence();
-                red_release_gpu_add(&done[g - 1], 1);
+                // the barrier ordered every warp's dst stores of group g - 1 before this thread: one release publishes this
+                // CTA's rows of it (system scope and one add per rank when the rows were mirrored into the peers).  Every CTA
+                // arrives for every group, in order (with or without rows in it), so "done[g - 1] has all its arrivals" means
+                // that ALL groups <= g - 1 are complete everywhere.
+                if (world > 1) {
+                    __threadfence_system();
+                    for (int r = 0; r < world; r++) red_relaxed_sys_add(pdone[r] + (g - 1), 1);   // (the fence above releases)
+                } else {
+                    __threadfence();
+                    red_release_gpu_add(&done[g - 1], 1);
+                }
             }
-            if (g == ng) break;
+            if (g == ng) {
+                // split mode: leave only when every rank's rows of the last group have landed here -- whatever runs next on
+                // this stream reads the whole dst
+                if (world > 1 && threadIdx.x == 0) {
+                    const long long t0 = clock64();
+                    while (ld_acquire_sys(&done[ng - 1]) - target < 0) {
+                        if (clock64() - t0 > (1ll << 31)) { atomicExch(&H->error, ng); break; }
+                    }
+                }
+                break;
+            }
             int       s0;
             const int nloc = nloc_of(g, s0);
             if (nloc == 0) continue;
@@ -278,9 +340,9 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
             if (warp == 0) {
                 const int dep = lane == 0 ? __ldcg(&groups[g].dep) : 0;
                 if (lane < 11) reinterpret_cast<uint4 *>(Gc)[lane] = __ldcg(reinterpret_cast<const uint4 *>(&groups[g]) + lane);
-                if (lane == 0 && dep && g > 0) {                // all CTAs have published every earlier group
+                if (lane == 0 && dep && g > 0) {                // all CTAs (of all ranks) have published every earlier group
                     const long long t0 = clock64();
-                    while (ld_acquire_gpu(&done[g - 1]) < G) {
+                    while ((world > 1 ? ld_acquire_sys(&done[g - 1]) : ld_acquire_gpu(&done[g - 1])) - target < 0) {
                         if (clock64() - t0 > (1ll << 31)) {     // ~1 s: leave a mark instead of hanging the GPU
                             atomicExch(&H->error, g);
                             break;
@@ -310,7 +372,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                            st3 = nseg > 3 ? Gc->seg[3].stage0 : INT32_MAX;
                 q8_unit u;
                 int     cur_q6 = -1;                            // register layout of u: 1 = Q6_K grouping, 0 = two 32-blocks
-                int     q = qbase + team, slot = q % NS, ph = (q / NS) & 1;
+                int     q = qbase + team;
                 for (int li = team; li < nloc; li += nteams) {
                     const int st = s0 + li;
                     const int s  = st >= st3 ? 3 : st >= st2 ? 2 : st >= st1 ? 1 : 0;
@@ -323,10 +385,11 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                         else    make_unit_q8<B200_TYPE_Q4_K, true>(u, act, L, k, ugc);
                         cur_q6 = q6;
                     }
+                    const int slot = q & (NB - 1);
                     while (ld_acquire_cta_shared(issued_a) <= q) {}
-                    mbar_wait(bar_full + 8 * slot, (uint32_t) ph);
+                    mbar_wait(bar_full + 8 * slot, (uint32_t) ((q / NB) & 1));
                     if (threadIdx.x == 0 && li == team) seq_stamp(trace, g, G, cta, 3);   // first weights of the group in hand
-                    const uint32_t base = ring + slot * S;
+                    const uint32_t base = ring + st_off[slot];
                     const uint32_t c0   = (uint32_t) ((uint64_t) (sg->W + (int64_t) r0 * row_bytes) & 15);
                     float * p = partials + slot * (SEQ_PART / 4);
                     switch (type) {
@@ -352,25 +415,28 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                             const volatile float * pq = p + lane * T;
                             float v = 0.f;
                             for (int w = 0; w < T; w++) v += pq[w];
-                            sg->dst[r0 + lane] = v;
+                            float * d = sg->dst + r0 + lane;
+                            *d = v;
+                            for (int r = 0; r < world; r++)     // (world == 1: no iterations; peer_delta[rank] == 0 is skipped)
+                                if (r != rank && world > 1)
+                                    *reinterpret_cast<float *>(reinterpret_cast<char *>(d) + pdelta[r]) = v;
                         }
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar_empty + 8 * slot);
                     }
-                    q += nteams, slot += nteams;
-                    while (slot >= NS) slot -= NS, ph ^= 1;
+                    q += nteams;
                 }
                 if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 4);   // team 0's share of the group done
             }
             qbase += nloc;
         }
     }
-    // ---- exit: the last CTA to leave re-arms the plan's counters for the next launch
+    // ---- exit: the last CTA to leave advances the plan's epoch for the next launch
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         if (atomicAdd(&H->exitc, 1) == G - 1) {
-            for (int g = 0; g < ng; g++) done[g] = 0;
+            H->epoch = H->epoch + 1;                            // every CTA has read it; the next launch's targets move on
             __threadfence();
             atomicExch(&H->exitc, 0);
         }
@@ -385,9 +451,11 @@ using namespace b200;
 static int seq_block_elems(int type) { return type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 ? 32 : 256; }
 static int seq_align(int type) { return type == B200_TYPE_Q4_K ? 16 : type == B200_TYPE_IQ4_XS ? 8 : 2; }
 
-// per-group geometry inside ring slots of `slot_bytes`: rows per stage V (as many as fit, but few enough that every
-// team of the CTA gets a stage) and the team layout; false if one row does not fit or the row is too long for a CTA
-static bool seq_geometry(seq_group & g, int slot_bytes, int ncta) {
+// per-group geometry: the team layout and the rows per stage V.  V is the largest of 8 / 4 / 2 / 1 (4 for rows of four or
+// more warps: shorter stages, more of them in flight -- the measured optimum of the per-call planner, mmvq.cu make_plan)
+// such that the ring holds a stage for every team plus one (two at least), the team's partial sums fit and every team of
+// the CTA gets a stage; false if two stages of one row do not fit or the row is too long for a CTA
+static bool seq_geometry(seq_group & g, int ring_bytes, int ncta) {
     const int upr = (g.k + 63) / 64;
     g.T = (upr + 31) / 32;
     if (g.T > SEQ_NW) return false;
@@ -396,10 +464,13 @@ static bool seq_geometry(seq_group & g, int slot_bytes, int ncta) {
     int64_t rows = 0;
     for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax, rows += g.seg[i].m;
     const int64_t rows_per_cta = (rows + ncta - 1) / ncta;
-    int V = 8;
-    while (V > 1 && (V * rowmax + 15 + 16 > slot_bytes || V * g.T > SEQ_PART / 4 || rows_per_cta < (int64_t) g.nteams * V)) V >>= 1;
-    if (V * rowmax + 15 + 16 > slot_bytes) return false;
+    auto stage_bytes = [&](int v) { return (v * rowmax + 15 + 16 + 127) & ~127; };
+    const int want = g.nteams + 1 > 2 ? g.nteams + 1 : 2;
+    int V = g.T >= 4 ? env_knob("B200_SEQ_V_LONG", 4) : 8;
+    while (V > 1 && (ring_bytes / stage_bytes(V) < want || V * g.T > SEQ_PART / 4 || rows_per_cta < (int64_t) g.nteams * V)) V >>= 1;
+    if (ring_bytes / stage_bytes(V) < 2) return false;
     g.V = V;
+    if (g.nseg == 0) g.nteams = 1;
     int st = 0;
     for (int i = 0; i < g.nseg; i++) g.seg[i].stage0 = st, st += (g.seg[i].m + V - 1) / V;
     g.nstages = st;
@@ -432,10 +503,13 @@ int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * 
         for (int cls = 0; cls < 2; cls++) {                     // 0: plain q8 layout, 1: IQ4_XS (pair-interleaved)
             seq_group g = {};
             g.x = in.x_device, g.k = (int) in.k, g.dep = in.dependent ? 1 : 0, g.interleave = cls;
+            bool has_class = false;   // a group is kept even when this rank owns no rows of it (m == 0 everywhere): in a row
+                                      // split every rank must publish every group, so the group list is the same on all ranks
             for (int i = 0; i < in.nmat; i++) {
                 const int type = in.type[i];
                 if (!b200_type_supported(type)) return B200_ERR_TYPE;
                 if ((type == B200_TYPE_IQ4_XS) != (cls == 1)) continue;
+                has_class = true;
                 if (in.k % seq_block_elems(type) != 0 || in.m[i] < 0 || in.m[i] > INT32_MAX) return B200_ERR_SHAPE;
                 if (in.m[i] == 0) continue;
                 if (!in.W_device[i] || !in.dst_device[i]) return B200_ERR_SHAPE;
@@ -444,32 +518,56 @@ int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * 
                 s.W = (const uint8_t *) in.W_device[i], s.dst = in.dst_device[i], s.m = (int) in.m[i], s.type = type;
                 s.row_bytes = (int) b200_row_size(type, in.k);
             }
-            if (g.nseg) out.push_back(g);
+            if (has_class) out.push_back(g);
         }
     }
     if (out.empty()) return B200_ERR_SHAPE;
     seq_header H = {};
+    H.world      = 1;
     H.ngroups    = (int) out.size();
     H.act_bytes  = (int) ((q8_soa_layout(kmax).bytes + 127) & ~127u);
-    // one slot size for the whole sequence: room for the longest row, at least 24 KB by default (8 rows of a k = 4096 Q4_K matrix: measured best, profiles/r02/seq_bench_*.log)
-    int rowmax = 0;
+    H.ring_bytes = (SEQ_SMEM - SEQ_CTRL - SEQ_PART * SEQ_MAXSLOTS - H.act_bytes) & ~127;
     for (auto & g : out)
-        for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax;
-    const int ring_bytes = SEQ_SMEM - SEQ_CTRL - SEQ_PART * SEQ_MAXSLOTS - H.act_bytes;
-    int slot = (rowmax + 15 + 16 + 127) & ~127;
-    const int want = env_knob("B200_SEQ_SLOT_BYTES", 24576);
-    if (slot < want) slot = (want + 127) & ~127;
-    H.slot_bytes = slot;
-    H.nslots     = ring_bytes / slot < SEQ_MAXSLOTS ? ring_bytes / slot : SEQ_MAXSLOTS;
-    if (H.nslots < 2) return B200_ERR_UNSUPPORTED;
-    for (auto & g : out)
-        if (!seq_geometry(g, H.slot_bytes, ncta)) return B200_ERR_UNSUPPORTED;
+        if (!seq_geometry(g, H.ring_bytes, ncta)) return B200_ERR_UNSUPPORTED;
     const size_t done_b = seq_done_bytes(H.ngroups);
     std::vector<uint8_t> host(sizeof(H) + done_b + out.size() * sizeof(seq_group), 0);
     memcpy(host.data(), &H, sizeof(H));
     memcpy(host.data() + sizeof(H) + done_b, out.data(), out.size() * sizeof(seq_group));
     // pageable source: cudaMemcpyAsync returns once the bytes are staged, so `host` may go out of scope
     B200_CUDA_TRY(cudaMemcpyAsync(plan_device, host.data(), host.size(), cudaMemcpyHostToDevice, stream));
+    return B200_OK;
+}
+
+// The same plan for ONE RANK of a row split over `world` GPUs (one process per GPU): `groups` describe this rank's row
+// slices (W = its rows, m = their count, dst = the full result + row_low), every dst lies inside this rank's symmetric
+// allocation [peer_base[rank], + span_bytes), peer_base[r] / peer_sync[r] are rank r's allocation and counter array
+// (>= 2 * ngroups ints, zeroed once) as mapped into THIS process (b200_ipc_open_handle).  Every rank must run its plan
+// the same number of times; b200_sequence_run returns only after all ranks' rows have landed in this rank's dst.
+int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes, int world,
+                                      int rank, void * const * peer_base, size_t span_bytes, int32_t * const * peer_sync,
+                                      b200_stream_t stream_) {
+    if (world < 1 || world > 16 || rank < 0 || rank >= world || !peer_base || !peer_sync) return B200_ERR_SHAPE;
+    for (int r = 0; r < world; r++)
+        if (!peer_base[r] || !peer_sync[r] || (uintptr_t) peer_base[r] % 4 != 0) return B200_ERR_ALIGNMENT;
+    for (int g = 0; g < ngroups; g++)
+        for (int i = 0; groups && i < groups[g].nmat && i < SEQ_MAXSEG; i++) {
+            const char * d = (const char *) groups[g].dst_device[i];
+            if (groups[g].m[i] > 0 && (d < (const char *) peer_base[rank] || d + groups[g].m[i] * 4 > (const char *) peer_base[rank] + span_bytes))
+                return B200_ERR_SHAPE;   // a result outside the symmetric allocation cannot be mirrored
+        }
+    int st = b200_sequence_plan_build(groups, ngroups, plan_device, plan_bytes, stream_);
+    if (st != B200_OK) return st;
+    seq_header H = {};
+    cudaStream_t stream = (cudaStream_t) stream_;
+    B200_CUDA_TRY(cudaMemcpyAsync(&H, plan_device, sizeof(H), cudaMemcpyDeviceToHost, stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(stream));
+    H.world = world, H.rank = rank, H.epoch = 0;
+    for (int r = 0; r < world; r++) {
+        H.peer_delta[r] = (long long) ((const char *) peer_base[r] - (const char *) peer_base[rank]);
+        H.peer_done[r]  = peer_sync[r];
+    }
+    B200_CUDA_TRY(cudaMemcpyAsync(plan_device, &H, sizeof(H), cudaMemcpyHostToDevice, stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(stream));
     return B200_OK;
 }
 

@@ -29,7 +29,7 @@ EXPORTS = [
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
     "b200_noalloc_scratch_size", "b200_mul_mat_noalloc",
     "b200_sequence_plan_size", "b200_sequence_plan_build", "b200_sequence_run", "b200_sequence_status",
-    "b200_debug_sequence_trace",
+    "b200_debug_sequence_trace", "b200_sequence_plan_build_rowsplit",
     "b200_mul_mat_id_prefers_mmq", "b200_mul_mat_id_mmq_workspace_size", "b200_mul_mat_id_mmq",
 ]
 
@@ -111,6 +111,7 @@ def lib():
     L.b200_sequence_plan_size.argtypes = [i32]
     L.b200_sequence_plan_build.argtypes = [vp, i32, vp, sz, vp]
     L.b200_sequence_run.argtypes = [vp, vp]
+    L.b200_sequence_plan_build_rowsplit.argtypes = [vp, i32, vp, sz, i32, i32, vp, sz, vp, vp]
     L.b200_sequence_status.argtypes = [vp, C.POINTER(i32), vp]
     L.b200_debug_sequence_trace.argtypes = [vp, vp, vp]
     L.b200_mul_mat_id_prefers_mmq.argtypes = [i64, i64, i64, i64]
@@ -320,7 +321,9 @@ class Sequence:
     """b200_sequence_*: a list of MUL_MAT groups at batch 1 run as ONE persistent launch.
     groups: [(x [1, k] or [k] f32 cuda, k, [(type, w, m, out [m] or [1, m] f32 cuda), ...], dependent)]"""
 
-    def __init__(self, groups, stream=None):
+    def __init__(self, groups, stream=None, split=None):
+        """split = (world, rank, peer_base (ctypes array of `world` pointers), span_bytes, peer_sync (same)): this rank's
+        part of a row split; every `out` must lie inside this rank's symmetric allocation"""
         import torch
         n = len(groups)
         arr = (SeqGroup * n)()
@@ -337,7 +340,12 @@ class Sequence:
                 self.keep += [w, out]
         nbytes = lib().b200_sequence_plan_size(n)
         self.plan = torch.zeros(nbytes, dtype=torch.uint8, device=self.keep[0].device)
-        check(lib().b200_sequence_plan_build(arr, n, self.plan.data_ptr(), nbytes, _stream_ptr(stream)))
+        if split is None:
+            check(lib().b200_sequence_plan_build(arr, n, self.plan.data_ptr(), nbytes, _stream_ptr(stream)))
+        else:
+            world, rank, peer_base, span, peer_sync = split
+            check(lib().b200_sequence_plan_build_rowsplit(arr, n, self.plan.data_ptr(), nbytes, world, rank, peer_base, span,
+                                                          peer_sync, _stream_ptr(stream)))
 
     def __call__(self, stream=None):
         check(lib().b200_sequence_run(self.plan.data_ptr(), _stream_ptr(stream)))

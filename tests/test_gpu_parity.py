@@ -629,3 +629,21 @@ def test_mul_mat_id_tensor_cores(qmm, name, t, n_expert, n_used, n_tokens, bcast
     assert qref.nmse(want, g) < NMSE_TIGHT
     assert qref.nmse(qref.mul_mat_id(t, w, b, ids, m, k, n_expert, "cpu"), g) < NMSE_HARNESS
     assert qmm.lib().b200_mul_mat_id_prefers_mmq(m, n_expert, n_used, n_tokens) in (0, 1)
+
+
+@pytest.mark.gpu
+def test_sequence_row_split_two_gpus_bit_identical():
+    """b200_sequence_plan_build_rowsplit on 2 GPUs (one process per GPU, torchrun): every rank's result buffer equals the
+    whole matmuls computed locally, over repeated runs of the plan (tests/seq_rowsplit_check.py).  Skipped on a 1-GPU box."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "tests", "seq_rowsplit_check.py")]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.count("OK") >= 2, r.stdout[-3000:]

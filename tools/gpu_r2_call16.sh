@@ -1,0 +1,25 @@
+#!/bin/bash
+# 2 GPUs: sequence kernel (byte ring) regression + single-GPU timing, row-split sequence check, bench --gpus 2
+mkdir -p gpurun_out
+nvidia-smi -L > gpurun_out/c16_gpus.txt
+timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "sequence" > gpurun_out/c16_pytest_seq.log 2>&1
+echo "pytest seq rc=$?"; tail -5 gpurun_out/c16_pytest_seq.log
+for m in llama3-8b-q4_k_m llama3-70b-q4_k_m; do
+  timeout 600 python tools/seq_bench.py $m 30 > gpurun_out/c16_seq_bench_$m.log 2>&1; echo "seq_bench $m rc=$?"; tail -4 gpurun_out/c16_seq_bench_$m.log
+done
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/seq_rowsplit_check.py > gpurun_out/c16_seqsplit.log 2>&1
+echo "seqsplit rc=$?"; grep "rank" gpurun_out/c16_seqsplit.log | grep -v "^\[rank\|^W" | tail -12
+timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 20 --warmup 3 > gpurun_out/c16_bench_n2.json 2> gpurun_out/c16_bench_n2.err
+echo "bench n2 rc=$?"; python - <<'PY'
+import json
+try:
+    r = json.loads([l for l in open("gpurun_out/c16_bench_n2.json") if l.startswith("{")][-1])
+    print("value", r["value"], r["config"]["workload"])
+    print("seq_split", r.get("sequence_row_split"))
+    print("single", r.get("single_gpu_same_workload"))
+    print("nccl", r.get("nccl_all_gather_baseline"))
+    print("pp512", r.get("pp512"))
+except Exception as e:
+    print("no json", e)
+PY
+tail -5 gpurun_out/c16_bench_n2.err
