@@ -696,7 +696,11 @@ def main():
         def token_step_host_split():
             for k in ks:
                 xs[k].copy_(hx[k], non_blocking=True)
-            if collective == "fused_peer_store":
+            if collective == "sequence_peer_store":
+                seqs()
+                for m, (o0, _) in seq_last_of_m.items():
+                    hfull[m].copy_(sym.dst[:, o0:o0 + m], non_blocking=True)
+            elif collective == "fused_peer_store":
                 token_step_fused()
                 for m in maxrows:
                     hfull[m].copy_(peers[m].dst, non_blocking=True)
@@ -706,8 +710,10 @@ def main():
                     hout[m].copy_(out_full[m][0], non_blocking=True)
             torch.cuda.current_stream().synchronize()
         hfull = {m: torch.zeros((n, m)).pin_memory() for m in maxrows}
+        if collective == "sequence_peer_store":
+            seq_last_of_m = {m: (bases[b_][0], b_) for b_, (_, m, _, _, _, _) in last.items()}
         ms_e2e = timed(token_step_host_split, max(8, args.steps // 4), 3)
-        fusedp = collective == "fused_peer_store"
+        fusedp = collective in ("fused_peer_store", "sequence_peer_store")
         e2e = {"value": 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": sum(n * k * 4 for k in ks),
                "d2h_bytes_per_step": sum(n * (m if fusedp else maxrows[m]) * 4 for m in maxrows), "ms_per_step": ms_e2e,
                "api": "pinned host activations -> H2D once per token -> row-split matmuls (%s) -> D2H of the last "

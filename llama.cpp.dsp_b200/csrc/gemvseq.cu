@@ -14,9 +14,8 @@
 //    shared by all groups (stage number q -> mbarrier q % 32, phase q / 32; its bytes are allocated circularly, each group
 //    with the stage size that suits its row length), so the next group's first
 //    stages are requested while the compute warps finish the current one, wait for the other CTAs and quantize the next
-//    activations: weights never depend on earlier results.  Consumers look at a stage's barrier only after the issue
-//    warp has published "stage q issued" -- the slot's previous phase is then known to be complete, which is what makes
-//    parity waits safe although teams of different groups share slots;
+//    activations: weights never depend on earlier results.  32 stage barriers are shared by all groups; a parity wait
+//    is safe because the stage that used the barrier before was consumed by the same team or by an earlier group;
 //  * every CTA quantizes the group's activation vector itself into shared memory (16 warps, one pass over <= 56 KB from
 //    L2, the arithmetic of quantize_row_q8_1_ref -- actquant.cuh), so there is no quantizer kernel and no q8 scratch;
 //  * a group marked DEPENDENT starts only after every CTA has finished all earlier groups (a release/acquire counter per
@@ -141,11 +140,20 @@ __device__ __forceinline__ void seq_stage(uint32_t base, uint32_t row_bytes, uin
         if (lane == 0) p[wt] = v;
     } else {
         float acc[V];
+        if (nr == V) {                                          // full stage: one basic block, the V dot products interleave
 #pragma unroll
-        for (int v = 0; v < V; v++) {
-            float out[1] = {0.f};
-            if (v < nr) unit_dot<TYPE, 1>(base + v * row_bytes + c0, ugc, k32, &u, out);   // warp-uniform branch
-            acc[v] = have ? out[0] : 0.f;
+            for (int v = 0; v < V; v++) {
+                float out[1];
+                unit_dot<TYPE, 1>(base + v * row_bytes + c0, ugc, k32, &u, out);
+                acc[v] = have ? out[0] : 0.f;
+            }
+        } else {
+#pragma unroll
+            for (int v = 0; v < V; v++) {
+                float out[1] = {0.f};
+                if (v < nr) unit_dot<TYPE, 1>(base + v * row_bytes + c0, ugc, k32, &u, out);   // warp-uniform branch
+                acc[v] = have ? out[0] : 0.f;
+            }
         }
         butterfly_rows<V>(acc, lane);
         if ((lane & (32 / V - 1)) == 0) p[butterfly_row<V>(lane) * T + wt] = acc[0];
@@ -169,7 +177,12 @@ __device__ __forceinline__ int ld_acquire_cta_shared(uint32_t addr) {
     return v;
 }
 
-__global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restrict__ plan, int evict_first) {
+__global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restrict__ plan, int flags) {
+    // flags: bit 0 = evict-first L2 policy for the weights; bits 8..15 = how a group is published (0: fence.sc + release,
+    // 1: release only, 3: relaxed -- measurement only); bits 16..23 = how many stages of a group the producer may issue
+    // before the compute warps have that group's activations (0: no limit)
+    const int evict_first = flags & 1, pub_mode = (flags >> 8) & 255, lookahead = (flags >> 16) & 255;
+    const int dbg = (flags >> 24) & 255;   // experiments (wrong results): 1 = quantize the activations of the first group only
     extern __shared__ __align__(128) uint8_t smem[];
     seq_header *      H      = reinterpret_cast<seq_header *>(plan);
     const int         ng     = H->ngroups, world = H->world, rank = H->rank;
@@ -193,6 +206,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
     const uint32_t bar_full  = ctrl, bar_empty = ctrl + 8 * SEQ_MAXSLOTS;
     int * const    arrived   = reinterpret_cast<int *>(smem + 16 * SEQ_MAXSLOTS);
     const uint32_t issued_a  = ctrl + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS;
+    const uint32_t cons_a    = issued_a + 4;                    // groups whose activations the compute warps have quantized
     // With 226 KB of shared memory carved out, L1 is a few KB: a descriptor field read from global memory is an L2 round
     // trip.  The group in work is therefore staged in shared memory, one copy for the compute warps (written at the group
     // boundary) and one for the producer (which runs ahead).
@@ -213,6 +227,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
             arrived[i] = 0;
         }
         *reinterpret_cast<volatile int *>(smem + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS) = 0;
+        *reinterpret_cast<volatile int *>(smem + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS + 4) = 0;
         mbar_fence_init();
     }
     if (threadIdx.x < 16) pdelta[threadIdx.x] = H->peer_delta[threadIdx.x], pdone[threadIdx.x] = H->peer_done[threadIdx.x];
@@ -268,6 +283,8 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                     uint64_t  ga = (uint64_t) (Gq->seg[seg].W + (int64_t) r0 * row_bytes);
                     const uint32_t step = (uint32_t) V * (uint32_t) row_bytes;
                     for (; st < end; st++, q++) {
+                        if (lookahead && st - s0 >= lookahead)
+                            while (ld_acquire_cta_shared(cons_a) <= g) {}
                         const int      nr   = V < m - r0 ? V : m - r0;
                         const uint64_t g0   = ga & ~(uint64_t) 15;
                         const uint32_t span = (uint32_t) (((ga + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
@@ -292,9 +309,6 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                         if (evict_first) tma_load_1d_hint(ring + head, (const void *) g0, span, bar, policy);
                         else tma_load_1d(ring + head, (const void *) g0, span, bar);
                         head += sz;
-                        // consumers look at a stage's barrier only once it has been issued: the slot's previous phase is
-                        // then known to be complete, so a parity wait cannot be satisfied by the phase before it
-                        st_release_cta_shared(issued_a, q + 1);
                         ga += step, r0 += V;
                     }
                 }
@@ -309,18 +323,24 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
         for (int g = 0; g <= ng; g++) {
             // ---- group boundary: every compute warp is done with the previous group's stages, activations and descriptor
             named_bar_sync(1, SEQ_NW * 32);
+            if (threadIdx.x == 0 && g > 0) seq_stamp(trace, g - 1, G, cta, 6);   // every warp of this CTA is done with group g - 1
             if (threadIdx.x == 0 && g > 0) {
                 // the barrier ordered every warp's dst stores of group g - 1 before this thread: one release publishes this
                 // CTA's rows of it (system scope and one add per rank when the rows were mirrored into the peers).  Every CTA
                 // arrives for every group, in order (with or without rows in it), so "done[g - 1] has all its arrivals" means
                 // that ALL groups <= g - 1 are complete everywhere.
                 if (world > 1) {
-                    __threadfence_system();
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");   // (not __threadfence_system: that is fence.sc, far dearer)
                     for (int r = 0; r < world; r++) red_relaxed_sys_add(pdone[r] + (g - 1), 1);   // (the fence above releases)
-                } else {
+                } else if (pub_mode == 0) {
                     __threadfence();
                     red_release_gpu_add(&done[g - 1], 1);
+                } else if (pub_mode == 1) {
+                    red_release_gpu_add(&done[g - 1], 1);
+                } else {
+                    asm volatile("red.relaxed.gpu.global.add.s32 [%0], %1;" ::"l"(&done[g - 1]), "r"(1) : "memory");
                 }
+                seq_stamp(trace, g - 1, G, cta, 7);             // published
             }
             if (g == ng) {
                 // split mode: leave only when every rank's rows of the last group have landed here -- whatever runs next on
@@ -357,10 +377,16 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
             const q8_layout L = q8_soa_layout(k);
             const float *   x = Gc->x;
             const bool      vec = ((uintptr_t) x & 15) == 0;
-            if (Gc->interleave) quantize_row_q8_soa<true, 4, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
-            else                quantize_row_q8_soa<false, 4, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            // (8 loads per lane in flight: k <= 16384 is ONE L2 round trip per CTA -- under the weight prefetch a round trip
+            //  costs 1-2 us, profiles/r02/seq_trace_*.log)
+            if ((dbg & 1) && g > 0) {
+            } else if (Gc->interleave) quantize_row_q8_soa<true, 8, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            else                quantize_row_q8_soa<false, 8, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
             named_bar_sync(1, SEQ_NW * 32);
-            if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 2);   // activations quantized
+            if (threadIdx.x == 0) {
+                if (lookahead) st_release_cta_shared(cons_a, g + 1);
+                seq_stamp(trace, g, G, cta, 2);                 // activations quantized
+            }
 
             const int team = warp / T, wt = warp - team * T;
             if (team < nteams) {                                // (spare warps of this group's team layout skip the stages)
@@ -386,7 +412,11 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                         cur_q6 = q6;
                     }
                     const int slot = q & (NB - 1);
-                    while (ld_acquire_cta_shared(issued_a) <= q) {}
+                    if (threadIdx.x == 0 && li == team) seq_stamp(trace, g, G, cta, 5);   // activations in registers
+                    // parity wait on a barrier shared by stages q, q - 32, ...: safe because stage q - 32 was consumed by this
+                    // same team (nteams divides 32) or belongs to an earlier group (complete before the boundary barrier),
+                    // so the barrier cannot still be in the phase before the one waited for.  (An "issued" counter published
+                    // by the producer with a release store per stage made the producer the bottleneck: MEMBAR.CTA per stage.)
                     mbar_wait(bar_full + 8 * slot, (uint32_t) ((q / NB) & 1));
                     if (threadIdx.x == 0 && li == team) seq_stamp(trace, g, G, cta, 3);   // first weights of the group in hand
                     const uint32_t base = ring + st_off[slot];
@@ -459,7 +489,8 @@ static bool seq_geometry(seq_group & g, int ring_bytes, int ncta) {
     const int upr = (g.k + 63) / 64;
     g.T = (upr + 31) / 32;
     if (g.T > SEQ_NW) return false;
-    g.nteams = SEQ_NW / g.T;
+    g.nteams = 1;
+    while (g.nteams * 2 * g.T <= SEQ_NW) g.nteams *= 2;       // a power of two: the kernel's barrier-parity argument needs nteams | 32
     int     rowmax = 0;
     int64_t rows = 0;
     for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax, rows += g.seg[i].m;
@@ -586,7 +617,8 @@ int b200_sequence_run(void * plan_device, b200_stream_t stream_) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = env_knob("B200_PDL", 1);
     cfg.attrs = attr, cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_gemv_seq, (uint8_t *) plan_device, env_knob("B200_GEMV_EVICT_FIRST", 1)));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_gemv_seq, (uint8_t *) plan_device, (env_knob("B200_GEMV_EVICT_FIRST", 1) & 1) | (env_knob("B200_SEQ_PUBLISH", 1) & 255) << 8 |
+                                                                   (env_knob("B200_SEQ_LOOKAHEAD", 0) & 255) << 16 | (env_knob("B200_SEQ_DEBUG", 0) & 255) << 24));
     note_launch();
     return B200_OK;
 }

@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 // every rank's arrival counter and the last one tops the launch up to B200_ARRIVAL_UNIT, so a rank's
                 // launch always counts UNIT whatever its grid size; the consumer side is the next call's quantizer
                 // (wait_sync) or a stream wait-value (b200_rowsplit_wait).
-                __threadfence_system();
+                asm volatile("fence.acq_rel.sys;" ::: "memory");   // (__threadfence_system is fence.sc.sys: MEMBAR.SC + ERRBAR + CCTL.IVALL)
                 const int total = (int) (gridDim.x * gridDim.y);
                 int add = 1;
                 if (atomicAdd(peers.local, 1) == total - 1) {
@@ -323,17 +323,31 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         gemv_locate(mm, rl, Wl, dl, dcs);
         const uint32_t c0   = (uint32_t) ((uint64_t) (Wl + (int64_t) rl * a.w_row_stride) & 15);
         float acc[NCOLS][V];
+        if (nr == V && !(a.dbg & 8)) {
+            // full stage (all but a CTA's last one): no per-row branch, so the V independent dot products are one
+            // basic block and their shared-memory loads and integer chains interleave (the kernel is bound by the
+            // issue latency of its 4 warps per scheduler, profiles/r02/ncu_gemv_seq_70b_*)
 #pragma unroll
-        for (int v = 0; v < V; v++) {
-            float out[NCOLS];
-#pragma unroll
-            for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
-            if (v < nr && !(a.dbg & 8)) {                       // warp-uniform (dbg 8: loads only)
+            for (int v = 0; v < V; v++) {
+                float out[NCOLS];
                 const uint32_t ra = base + v * row_step + ((c0 + v * c1) & 15u);
                 unit_dot<TYPE, NCOLS>(ra, ugc, k32, u, out);
-            }
 #pragma unroll
-            for (int c = 0; c < NCOLS; c++) acc[c][v] = have ? out[c] : 0.f;
+                for (int c = 0; c < NCOLS; c++) acc[c][v] = have ? out[c] : 0.f;
+            }
+        } else {
+#pragma unroll
+            for (int v = 0; v < V; v++) {
+                float out[NCOLS];
+#pragma unroll
+                for (int c = 0; c < NCOLS; c++) out[c] = 0.f;
+                if (v < nr && !(a.dbg & 8)) {                   // warp-uniform (dbg 8: loads only)
+                    const uint32_t ra = base + v * row_step + ((c0 + v * c1) & 15u);
+                    unit_dot<TYPE, NCOLS>(ra, ugc, k32, u, out);
+                }
+#pragma unroll
+                for (int c = 0; c < NCOLS; c++) acc[c][v] = have ? out[c] : 0.f;
+            }
         }
         float * p = partial + (size_t) (slot * 2 + par) * part_sz;
 #pragma unroll

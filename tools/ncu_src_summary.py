@@ -33,3 +33,7 @@ for r in sorted(data, key=lambda r: -I(r, "# Samples"))[:ntop]:
     top = sorted(((I(r, h), h) for h in stalls), reverse=True)[:2]
     print("  %5d smp %8d exec  %-60s %s" % (I(r, "# Samples"), I(r, "Instructions Executed"), r[ix["Source"]].strip()[:60],
                                           ", ".join("%s=%d" % (h[6:], v) for v, h in top if v)))
+if len(sys.argv) > 3:   # full per-line listing (address order): exec count, samples, instruction
+    with open(sys.argv[3], "w") as f:
+        for r in data:
+            f.write("%s %9d %6d  %s\n" % (r[0][-5:], I(r, "Instructions Executed"), I(r, "# Samples"), r[ix["Source"]].strip()[:90]))

@@ -41,7 +41,7 @@ for _, k, members in groups:
         oa.append(out_a[base]), ob.append(out_b[base])
     calls.append((qmm.MultiMatMul([t for _, t, _, _ in members], [w for _, _, _, w in members],
                                   [m for _, _, m, _ in members], k, oa, 1), xs[k]))
-    seq_groups.append((xs[k], k, [(t, w, m, o) for (_, t, m, w), o in zip(members, ob)], True))
+    seq_groups.append((xs[k], k, [(t, w, m, o) for (_, t, m, w), o in zip(members, ob)], os.environ.get("SEQ_INDEPENDENT") is None))
 seq = qmm.Sequence(seq_groups)
 step_bytes = sum(bench.gemv_bytes(t, m, k, 1) for _, t, m, k in mms)
 
