@@ -581,9 +581,11 @@ def main():
             mats = []
             for b_, t, w, lo, hi in members:
                 o0 = bases[b_][0]
-                mats.append((t, w if w is not None else fws, hi - lo, sym.dst[0, o0 + lo:o0 + hi]))
+                mats.append((t, w if w is not None else fws, bases[b_][1], sym.dst[0, o0:o0 + bases[b_][1]]))   # whole matrix, w = own rows
             sgroups.append((xs[k], k, mats, True))
-        seqs = qmm.Sequence(sgroups, split=(world, rank, sym.ptr_dst, off * 4, sym.ptr_sync[0]))
+        use_ll = os.environ.get("B200_SEQ_SPLIT_LL", "1") != "0"
+        sym_ll = PeerBuffers(1, 2 * off, 1, world, rank, dev) if use_ll else None
+        seqs = qmm.Sequence(sgroups, split=(world, rank, sym.ptr_dst, off * 4, sym.ptr_sync[0], sym_ll.ptr_dst if use_ll else None))
         dist.barrier()
         seqs()
         torch.cuda.synchronize()
@@ -618,9 +620,32 @@ def main():
             ms_sq = timed(gq.replay, args.steps, args.warmup)
             seq_split = {"value": 1e3 / ms_sq, "unit": "tok/s", "ms_per_step": ms_sq, "launches_per_step": 1,
                          "bit_identical_to_per_rank_results": True, "groups": len(sgroups),
+                         "exchange": "flag in the data: 8-byte {value, tag} peer stores, local collection + local counters" if use_ll
+                                     else "mirrored stores + system-scope fence + remote counters",
                          "hbm_gbs_per_gpu": step_bytes / ms_sq / 1e6,
                          "api": "b200_sequence_plan_build_rowsplit + b200_sequence_run per rank: one persistent kernel per GPU, rows "
                                 "mirrored into every rank's dst over NVLink from the epilogue, system-scope arrival counters"}
+            if os.environ.get("B200_BENCH_SEQ_TRACE"):
+                # in-kernel globaltimer stamps of one token (b200_debug_sequence_trace): where a group's time goes on this rank
+                import numpy as np
+                ngp, ncta = len(sgroups), qmm.lib().b200_sm_count(local_rank)
+                trace = torch.zeros((2 * ngp, ncta, 8), dtype=torch.int64, device=dev)
+                qmm.check(qmm.lib().b200_debug_sequence_trace(seqs.plan.data_ptr(), trace.data_ptr(), None))
+                dist.barrier()
+                seqs()
+                seqs()
+                torch.cuda.synchronize()
+                qmm.check(qmm.lib().b200_debug_sequence_trace(seqs.plan.data_ptr(), None, None))
+                tr = trace.cpu().numpy()[:ngp]
+                ok = (tr[:-1, :, 0] > 0) & (tr[1:, :, 0] > 0) & (tr[:-1, :, 6] > 0)
+                a, b = tr[:-1], tr[1:]
+                med = lambda v: float(np.median(v[ok])) / 1e3
+                seq_split["trace_us_median"] = {
+                    "wait_for_all_ranks": med(a[:, :, 1] - a[:, :, 0]), "quantize": med(a[:, :, 2] - a[:, :, 1]),
+                    "first_weights": med(a[:, :, 3] - a[:, :, 2]), "dot_products": med(a[:, :, 4] - a[:, :, 3]),
+                    "team0_done_to_cta_done": med(a[:, :, 6] - a[:, :, 4]), "publish_fence_and_adds": med(a[:, :, 7] - a[:, :, 6]),
+                    "to_next_boundary": med(b[:, :, 0] - a[:, :, 7]),
+                    "group_period": float(np.median((b[:, :, 0] - a[:, :, 0])[ok])) / 1e3}
             if ms_sq < ms_step:
                 fused_leg = {"value": 1e3 / ms_step, "unit": "tok/s", "ms_per_step": ms_step}
                 ms_step, collective = ms_sq, "sequence_peer_store"

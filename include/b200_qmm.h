@@ -253,16 +253,25 @@ B200_API int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups
 /*
  * The plan of ONE RANK of a split-mode-row sequence over `world` GPUs (one process per GPU) -- replaces the row-split
  * choreography of ggml_cuda_op_mul_mat for a whole decode token (ggml/src/ggml-cuda/ggml-cuda.cu:1560-1700: per matmul a
- * broadcast of the activations, peer copies of the result slices, events).  `groups` describe this rank's row slices
- * (W = its rows, m = their count, dst = full result + row_low; b200_row_split gives the ranges).  Every dst lies inside
- * this rank's symmetric allocation [peer_base[rank], + span_bytes); peer_base[r] and peer_sync[r] are rank r's allocation
- * and counter array (>= 2 * ngroups ints, zeroed once) mapped into this process (b200_ipc_*).  The kernel's epilogue
- * stores every row into all ranks' allocations over NVLink and publishes groups with system-scope counters, so each rank
- * holds the whole dst when its b200_sequence_run returns.  All ranks run their plans the same number of times.
+ * broadcast of the activations, peer copies of the result slices, events).  `groups` describe the WHOLE matrices (m = all
+ * rows, dst = where row 0 goes) except that W points at THIS RANK's rows: rows [lo, hi) = b200_row_split(m, world, rank),
+ * the reference's get_row_split rule.  Every dst lies inside this rank's symmetric allocation [peer_base[rank],
+ * + span_bytes); peer_base[r], peer_sync[r] (>= 2 * ngroups ints, zeroed once) and peer_ll[r] are rank r's buffers mapped
+ * into this process (b200_ipc_*).  Every group is ordered after the one before it.
+ *   peer_ll != NULL ("flag in the data"): every rank has an exchange buffer of 2 * span_bytes, zeroed before the plans are
+ *     built and used by one plan at a time.  A computed row is stored in the peers as 8 bytes {value, tag of (launch,
+ *     group)}; each rank polls the tags of the rows it expects, copies the values into its dst and publishes the group on a
+ *     local counter -- one NVLink store latency per group, no system-scope fence, no remote atomics.  Consecutive groups
+ *     may not write the same dst rows (B200_ERR_SHAPE).
+ *   peer_ll == NULL: rows are stored straight into the peers' dst, groups are published with a system-scope fence and one
+ *     remote atomic per rank (a round trip per group).
+ * Either way each rank holds the whole dst when its b200_sequence_run returns.  All ranks run their plans the same number
+ * of times.
  */
 B200_API int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, int ngroups, void * plan_device,
                                                size_t plan_bytes, int world, int rank, void * const * peer_base,
-                                               size_t span_bytes, int32_t * const * peer_sync, b200_stream_t stream);
+                                               size_t span_bytes, int32_t * const * peer_sync, void * const * peer_ll,
+                                               b200_stream_t stream);
 B200_API int b200_sequence_run(void * plan_device, b200_stream_t stream);
 /* *error_group = 0: fine; g > 0: dependent group g timed out waiting for earlier groups (synchronizes the stream) */
 B200_API int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t stream);

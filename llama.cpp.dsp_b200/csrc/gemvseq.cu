@@ -46,7 +46,7 @@ constexpr int SEQ_NW       = 16;                 // compute warps; warp SEQ_NW i
 constexpr int SEQ_THREADS  = (SEQ_NW + 1) * 32;
 constexpr int SEQ_MAXSLOTS = 32;                 // stages in flight at most (barriers); a power of two
 constexpr int SEQ_SMEM     = 226 * 1024;
-constexpr int SEQ_CTRL     = 1664;               // barriers, counters, three staged group descriptors, peer tables, stage offsets
+constexpr int SEQ_CTRL     = 1920;               // barriers, counters, three staged group descriptors, peer tables, stage offsets
 constexpr int SEQ_PART     = 256;                // bytes of partial sums per slot: V * T <= 64 floats
 constexpr int SEQ_MAXSEG   = 4;
 
@@ -63,9 +63,14 @@ struct seq_group {
     int           interleave;   // activation layout class: 1 = IQ4_XS (pair-interleaved q8), 0 = everything else
     int           T, nteams, V, nstages;
     seq_seg       seg[SEQ_MAXSEG];
-    int           pad[2];   // sizeof = 176: copied to shared memory as 11 x 16 bytes
-};
-static_assert(sizeof(seq_group) == 176, "seq_group layout");
+    int           nseg_all, pad;
+    // split mode, per matrix of the group (also those this rank owns no rows of): this rank computes rows
+    // [row_low, row_low + m_own) of m_full; dst_full = where row 0 goes
+    int           row_low[SEQ_MAXSEG], m_full[SEQ_MAXSEG], m_own[SEQ_MAXSEG];
+    float *       dst_full[SEQ_MAXSEG];
+};                          // sizeof = 256: copied to shared memory as 16 x 16 bytes
+static_assert(sizeof(seq_group) == 256, "seq_group layout");
+constexpr int SEQ_GROUP_U4 = sizeof(seq_group) / 16;
 struct seq_header {         // first bytes of the plan (device memory)
     int ngroups, exitc, error, act_bytes;   // act_bytes: shared memory reserved for the quantized activations
     int ring_bytes, pad[3];                  // bytes of the weight ring (the rest of shared memory)
@@ -80,6 +85,13 @@ struct seq_header {         // first bytes of the plan (device memory)
     int       epoch, pad3;                   // launches of this plan so far: the counters are never reset, targets grow
     long long peer_delta[16];
     int *     peer_done[16];                 // every rank's counter array (2 * ngroups ints); [rank] = the local one
+    // "flag in the data" exchange (peer_ll[0] != null): a row computed here is stored in the peers as 8 bytes {value, tag}
+    // into their exchange buffers (2 x span bytes, slot of the float at byte offset o of the span = 2 * o); every rank
+    // polls the tags of the rows it expects, copies the values into its dst and publishes the group on its LOCAL counter.
+    // No system-scope fence and no remote atomics on the critical path: one NVLink store latency instead of a round trip.
+    char *    peer_ll[16];
+    char *    base_local;                    // peer_base[rank]
+    unsigned long long pad4;
 };
 // plan = [seq_header][done: ngroups ints, padded to 16][seq_group x ngroups]
 __host__ __device__ static inline size_t seq_done_bytes(int ng) { return ((size_t) ng * 4 + 15) & ~(size_t) 15; }
@@ -211,11 +223,13 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
     // trip.  The group in work is therefore staged in shared memory, one copy for the compute warps (written at the group
     // boundary) and one for the producer (which runs ahead).
     // split mode: where a result row goes in every peer, and every peer's counters (staged: read per stored row / per group)
-    long long * const pdelta = reinterpret_cast<long long *>(smem + 1280);
-    int ** const      pdone  = reinterpret_cast<int **>(smem + 1408);
-    volatile uint32_t * const st_off = reinterpret_cast<volatile uint32_t *>(smem + 1536);
     seq_group * const Gc  = reinterpret_cast<seq_group *>(smem + 704);
     seq_group * const Gq2 = reinterpret_cast<seq_group *>(smem + 704 + sizeof(seq_group));   // [2]: this group / the next one
+    static_assert(704 + 3 * sizeof(seq_group) <= 1472, "control block layout");
+    long long * const pdelta = reinterpret_cast<long long *>(smem + 1472);     // split: peer_delta, or peer_ll in LL mode
+    int ** const      pdone  = reinterpret_cast<int **>(smem + 1600);
+    volatile uint32_t * const st_off = reinterpret_cast<volatile uint32_t *>(smem + 1728);
+    static_assert(1728 + 4 * SEQ_MAXSLOTS <= SEQ_CTRL, "control block layout");
     float * const  partials  = reinterpret_cast<float *>(smem + SEQ_CTRL);
     uint8_t * const act      = smem + SEQ_CTRL + SEQ_PART * SEQ_MAXSLOTS;
     const uint32_t  ring     = ctrl + SEQ_CTRL + SEQ_PART * SEQ_MAXSLOTS + act_bytes;
@@ -230,7 +244,12 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
         *reinterpret_cast<volatile int *>(smem + 16 * SEQ_MAXSLOTS + 4 * SEQ_MAXSLOTS + 4) = 0;
         mbar_fence_init();
     }
-    if (threadIdx.x < 16) pdelta[threadIdx.x] = H->peer_delta[threadIdx.x], pdone[threadIdx.x] = H->peer_done[threadIdx.x];
+    const bool   ll         = world > 1 && H->peer_ll[0] != nullptr;
+    char * const base_local = H->base_local;
+    if (threadIdx.x < 16) {
+        pdelta[threadIdx.x] = ll ? (long long) H->peer_ll[threadIdx.x] : H->peer_delta[threadIdx.x];
+        pdone[threadIdx.x]  = H->peer_done[threadIdx.x];
+    }
     __syncthreads();
     pdl_launch_dependents();
 
@@ -251,7 +270,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                 const uint32_t d = smem_u32(&Gq2[g & 1]);
                 const uint8_t * src = reinterpret_cast<const uint8_t *>(&groups[g]);
 #pragma unroll
-                for (int i = 0; i < 11; i++)
+                for (int i = 0; i < SEQ_GROUP_U4; i++)
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 16 * i), "l"(src + 16 * i) : "memory");
                 asm volatile("cp.async.commit_group;" ::: "memory");
             };
@@ -288,7 +307,9 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                         const int      nr   = V < m - r0 ? V : m - r0;
                         const uint64_t g0   = ga & ~(uint64_t) 15;
                         const uint32_t span = (uint32_t) (((ga + (uint64_t) nr * row_bytes + 15) & ~(uint64_t) 15) - g0);
-                        const uint32_t sz   = (span + 127) & ~127u;
+                        // (+16: the 2-byte-aligned formats read whole words, up to 4 bytes past a row's end -- keep that
+                        //  inside the stage's own piece of the ring, the last piece ends where shared memory ends)
+                        const uint32_t sz   = (span + 16 + 127) & ~127u;
                         // room for sz bytes: at head, or at 0 when the end of the ring is too short; otherwise wait for the
                         // oldest stage in flight (this thread is the only waiter on the empty barriers and takes them in order)
                         for (;;) {
@@ -318,18 +339,47 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
         // -------------------------------------------------------------------------------------------- compute warps
         pdl_wait();                                             // x and dst may still be in use by the previous kernel
         // arrivals a group's counter must have reached in THIS launch: the counters only ever grow (no reset to race with)
-        const int target = (H->epoch + 1) * world * G;
+        const int epoch  = H->epoch;
+        const int target = (epoch + 1) * (ll ? 1 : world) * G;  // (LL mode: a rank's counters only count its own CTAs)
         int qbase = 0;                                          // this CTA's stages in earlier groups
         for (int g = 0; g <= ng; g++) {
             // ---- group boundary: every compute warp is done with the previous group's stages, activations and descriptor
             named_bar_sync(1, SEQ_NW * 32);
             if (threadIdx.x == 0 && g > 0) seq_stamp(trace, g - 1, G, cta, 6);   // every warp of this CTA is done with group g - 1
+            if (ll && g > 0) {
+                // LL exchange: collect this CTA's share of the rows of group g - 1 that OTHER ranks computed.  Gc still
+                // describes group g - 1 (every CTA stages every group).  Row r of matrix i is remote when it lies outside
+                // [row_low, row_low + m); its 8-byte slot in the local exchange buffer carries the value and the tag of
+                // (launch, group) -- poll until the tag is there, then the value goes into dst.
+                const uint32_t tag = (uint32_t) epoch * (uint32_t) ng + (uint32_t) g;    // = tag of group g - 1 (tags start at 1)
+                const int nsegp = Gc->nseg_all;
+                int total = 0;
+                for (int i = 0; i < nsegp; i++) total += Gc->m_full[i] - Gc->m_own[i];
+                for (int v = cta * (SEQ_NW * 32) + (int) threadIdx.x; v < total; v += G * SEQ_NW * 32) {
+                    int i = 0, w = v;
+                    while (i + 1 < nsegp && w >= Gc->m_full[i] - Gc->m_own[i]) w -= Gc->m_full[i] - Gc->m_own[i], i++;
+                    const int row = w < Gc->row_low[i] ? w : w + Gc->m_own[i];
+                    float * d = Gc->dst_full[i] + row;
+                    const char * slot = reinterpret_cast<const char *>(pdelta[rank]) + 2 * (reinterpret_cast<char *>(d) - base_local);
+                    uint32_t val, tg;
+                    const long long t0 = clock64();
+                    for (;;) {
+                        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(val), "=r"(tg) : "l"(slot) : "memory");
+                        if (tg == tag) break;
+                        if (clock64() - t0 > (1ll << 31)) { atomicExch(&H->error, g); break; }
+                    }
+                    *d = __uint_as_float(val);
+                }
+                named_bar_sync(1, SEQ_NW * 32);                 // this CTA's share of the remote rows is in dst
+            }
             if (threadIdx.x == 0 && g > 0) {
                 // the barrier ordered every warp's dst stores of group g - 1 before this thread: one release publishes this
                 // CTA's rows of it (system scope and one add per rank when the rows were mirrored into the peers).  Every CTA
                 // arrives for every group, in order (with or without rows in it), so "done[g - 1] has all its arrivals" means
                 // that ALL groups <= g - 1 are complete everywhere.
-                if (world > 1) {
+                if (ll) {
+                    red_release_gpu_add(&done[g - 1], 1);       // own rows + collected rows: a LOCAL release is all it takes
+                } else if (world > 1) {
                     asm volatile("fence.acq_rel.sys;" ::: "memory");   // (not __threadfence_system: that is fence.sc, far dearer)
                     for (int r = 0; r < world; r++) red_relaxed_sys_add(pdone[r] + (g - 1), 1);   // (the fence above releases)
                 } else if (pub_mode == 0) {
@@ -355,12 +405,12 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
             }
             int       s0;
             const int nloc = nloc_of(g, s0);
-            if (nloc == 0) continue;
+            if (nloc == 0 && !ll) continue;
             if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 0);   // boundary reached: previous group done on this CTA
             if (warp == 0) {
                 const int dep = lane == 0 ? __ldcg(&groups[g].dep) : 0;
-                if (lane < 11) reinterpret_cast<uint4 *>(Gc)[lane] = __ldcg(reinterpret_cast<const uint4 *>(&groups[g]) + lane);
-                if (lane == 0 && dep && g > 0) {                // all CTAs (of all ranks) have published every earlier group
+                if (lane < SEQ_GROUP_U4) reinterpret_cast<uint4 *>(Gc)[lane] = __ldcg(reinterpret_cast<const uint4 *>(&groups[g]) + lane);
+                if (lane == 0 && dep && g > 0 && nloc > 0) {    // all CTAs (of all ranks) have published every earlier group
                     const long long t0 = clock64();
                     while ((world > 1 ? ld_acquire_sys(&done[g - 1]) : ld_acquire_gpu(&done[g - 1])) - target < 0) {
                         if (clock64() - t0 > (1ll << 31)) {     // ~1 s: leave a mark instead of hanging the GPU
@@ -371,6 +421,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                 }
             }
             named_bar_sync(1, SEQ_NW * 32);
+            if (nloc == 0) continue;                            // (LL mode: staged the descriptor for the collection above)
             if (threadIdx.x == 0) seq_stamp(trace, g, G, cta, 1);   // earlier groups complete everywhere
             const int k = Gc->k, T = Gc->T, nteams = Gc->nteams, V = Gc->V, nseg = Gc->nseg;
             // ---- quantize x into shared memory (every CTA for itself; L2-coherent loads: x may be an earlier group's dst)
@@ -447,9 +498,18 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                             for (int w = 0; w < T; w++) v += pq[w];
                             float * d = sg->dst + r0 + lane;
                             *d = v;
-                            for (int r = 0; r < world; r++)     // (world == 1: no iterations; peer_delta[rank] == 0 is skipped)
-                                if (r != rank && world > 1)
-                                    *reinterpret_cast<float *>(reinterpret_cast<char *>(d) + pdelta[r]) = v;
+                            if (ll) {
+                                const long long o2 = 2 * (reinterpret_cast<char *>(d) - base_local);
+                                const uint32_t  tg = (uint32_t) epoch * (uint32_t) ng + (uint32_t) g + 1u;
+                                for (int r = 0; r < world; r++)
+                                    if (r != rank)
+                                        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"((char *) pdelta[r] + o2),
+                                                     "r"(__float_as_uint(v)), "r"(tg) : "memory");
+                            } else {
+                                for (int r = 0; r < world; r++)     // (world == 1: no iterations; peer_delta[rank] == 0 is skipped)
+                                    if (r != rank && world > 1)
+                                        *reinterpret_cast<float *>(reinterpret_cast<char *>(d) + pdelta[r]) = v;
+                            }
                         }
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar_empty + 8 * slot);
@@ -495,7 +555,7 @@ static bool seq_geometry(seq_group & g, int ring_bytes, int ncta) {
     int64_t rows = 0;
     for (int i = 0; i < g.nseg; i++) rowmax = g.seg[i].row_bytes > rowmax ? g.seg[i].row_bytes : rowmax, rows += g.seg[i].m;
     const int64_t rows_per_cta = (rows + ncta - 1) / ncta;
-    auto stage_bytes = [&](int v) { return (v * rowmax + 15 + 16 + 127) & ~127; };
+    auto stage_bytes = [&](int v) { return (v * rowmax + 15 + 16 + 16 + 127) & ~127; };   // = the kernel's worst-case `sz`
     const int want = g.nteams + 1 > 2 ? g.nteams + 1 : 2;
     int V = g.T >= 4 ? env_knob("B200_SEQ_V_LONG", 4) : 8;
     while (V > 1 && (ring_bytes / stage_bytes(V) < want || V * g.T > SEQ_PART / 4 || rows_per_cta < (int64_t) g.nteams * V)) V >>= 1;
@@ -516,9 +576,16 @@ size_t b200_sequence_plan_size(int ngroups) {
     return sizeof(seq_header) + seq_done_bytes(ng) + (size_t) ng * sizeof(seq_group);
 }
 
-int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes,
-                             b200_stream_t stream_) {
-    cudaStream_t stream = (cudaStream_t) stream_;
+struct seq_split_info {     // row split: which rows of every matrix this rank computes, and the exchange set-up
+    int world, rank;
+    void * const *    peer_base;
+    size_t            span_bytes;
+    int32_t * const * peer_sync;
+    void * const *    peer_ll;   // null: plain mirrored stores + system-scope counters
+};
+
+static int seq_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes, const seq_split_info * sp,
+                     cudaStream_t stream) {
     if (!groups || ngroups <= 0) return B200_ERR_SHAPE;
     if (!plan_device || plan_bytes < b200_sequence_plan_size(ngroups)) return B200_ERR_WORKSPACE;
     if ((uintptr_t) plan_device % 16 != 0) return B200_ERR_ALIGNMENT;
@@ -533,26 +600,46 @@ int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * 
         kmax = in.k > kmax ? in.k : kmax;
         for (int cls = 0; cls < 2; cls++) {                     // 0: plain q8 layout, 1: IQ4_XS (pair-interleaved)
             seq_group g = {};
-            g.x = in.x_device, g.k = (int) in.k, g.dep = in.dependent ? 1 : 0, g.interleave = cls;
-            bool has_class = false;   // a group is kept even when this rank owns no rows of it (m == 0 everywhere): in a row
-                                      // split every rank must publish every group, so the group list is the same on all ranks
+            g.x = in.x_device, g.k = (int) in.k, g.interleave = cls;
+            g.dep = (in.dependent || sp) ? 1 : 0;               // row split: every group waits for the exchange of the one before
+            bool has_class = false;   // a group is kept even when this rank owns no rows of it: in a row split every rank
+                                      // publishes every group, so the group list is the same on all ranks
             for (int i = 0; i < in.nmat; i++) {
                 const int type = in.type[i];
                 if (!b200_type_supported(type)) return B200_ERR_TYPE;
                 if ((type == B200_TYPE_IQ4_XS) != (cls == 1)) continue;
                 has_class = true;
                 if (in.k % seq_block_elems(type) != 0 || in.m[i] < 0 || in.m[i] > INT32_MAX) return B200_ERR_SHAPE;
-                if (in.m[i] == 0) continue;
+                int64_t lo = 0, hi = in.m[i];
+                if (sp) {                                       // in.m = the whole matrix; W = this rank's rows, dst = row 0
+                    int st = b200_row_split(in.m[i], sp->world, sp->rank, nullptr, &lo, &hi);
+                    if (st != B200_OK) return st;
+                    const char * d = (const char *) in.dst_device[i];
+                    if (in.m[i] > 0 && (!d || d < (const char *) sp->peer_base[sp->rank] ||
+                                        d + in.m[i] * 4 > (const char *) sp->peer_base[sp->rank] + sp->span_bytes))
+                        return B200_ERR_SHAPE;                  // a result outside the symmetric allocation cannot be exchanged
+                    const int j = g.nseg_all++;
+                    g.row_low[j] = (int) lo, g.m_full[j] = (int) in.m[i], g.m_own[j] = (int) (hi - lo), g.dst_full[j] = in.dst_device[i];
+                }
+                if (hi == lo) continue;
                 if (!in.W_device[i] || !in.dst_device[i]) return B200_ERR_SHAPE;
                 if ((uintptr_t) in.W_device[i] % seq_align(type) != 0 || (uintptr_t) in.dst_device[i] % 4 != 0) return B200_ERR_ALIGNMENT;
                 seq_seg & s = g.seg[g.nseg++];
-                s.W = (const uint8_t *) in.W_device[i], s.dst = in.dst_device[i], s.m = (int) in.m[i], s.type = type;
+                s.W = (const uint8_t *) in.W_device[i], s.dst = in.dst_device[i] + lo, s.m = (int) (hi - lo), s.type = type;
                 s.row_bytes = (int) b200_row_size(type, in.k);
             }
             if (has_class) out.push_back(g);
         }
     }
     if (out.empty()) return B200_ERR_SHAPE;
+    if (sp && sp->peer_ll)                                      // an exchange slot must not be rewritten before it was collected:
+        for (size_t a = 0; a + 1 < out.size(); a++)             // consecutive groups may not share result rows
+            for (int i = 0; i < out[a].nseg_all; i++)
+                for (int j = 0; j < out[a + 1].nseg_all; j++) {
+                    const float *p0 = out[a].dst_full[i], *p1 = p0 + out[a].m_full[i];
+                    const float *q0 = out[a + 1].dst_full[j], *q1 = q0 + out[a + 1].m_full[j];
+                    if (p0 < q1 && q0 < p1) return B200_ERR_SHAPE;
+                }
     seq_header H = {};
     H.world      = 1;
     H.ngroups    = (int) out.size();
@@ -560,6 +647,15 @@ int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * 
     H.ring_bytes = (SEQ_SMEM - SEQ_CTRL - SEQ_PART * SEQ_MAXSLOTS - H.act_bytes) & ~127;
     for (auto & g : out)
         if (!seq_geometry(g, H.ring_bytes, ncta)) return B200_ERR_UNSUPPORTED;
+    if (sp) {
+        H.world = sp->world, H.rank = sp->rank, H.epoch = 0;
+        H.base_local = (char *) sp->peer_base[sp->rank];
+        for (int r = 0; r < sp->world; r++) {
+            H.peer_delta[r] = (long long) ((const char *) sp->peer_base[r] - (const char *) sp->peer_base[sp->rank]);
+            H.peer_done[r]  = sp->peer_sync[r];
+            H.peer_ll[r]    = sp->peer_ll ? (char *) sp->peer_ll[r] : nullptr;
+        }
+    }
     const size_t done_b = seq_done_bytes(H.ngroups);
     std::vector<uint8_t> host(sizeof(H) + done_b + out.size() * sizeof(seq_group), 0);
     memcpy(host.data(), &H, sizeof(H));
@@ -569,37 +665,27 @@ int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * 
     return B200_OK;
 }
 
-// The same plan for ONE RANK of a row split over `world` GPUs (one process per GPU): `groups` describe this rank's row
-// slices (W = its rows, m = their count, dst = the full result + row_low), every dst lies inside this rank's symmetric
-// allocation [peer_base[rank], + span_bytes), peer_base[r] / peer_sync[r] are rank r's allocation and counter array
-// (>= 2 * ngroups ints, zeroed once) as mapped into THIS process (b200_ipc_open_handle).  Every rank must run its plan
-// the same number of times; b200_sequence_run returns only after all ranks' rows have landed in this rank's dst.
+int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes,
+                             b200_stream_t stream_) {
+    return seq_build(groups, ngroups, plan_device, plan_bytes, nullptr, (cudaStream_t) stream_);
+}
+
+// The plan of ONE RANK of a row split over `world` GPUs (one process per GPU).  `groups` describe the WHOLE matrices (m = all
+// rows, dst = where row 0 goes) except that W points at THIS RANK's rows, which are rows [lo, hi) = b200_row_split(m, world,
+// rank).  Every dst lies inside this rank's symmetric allocation [peer_base[rank], + span_bytes); peer_base[r], peer_sync[r]
+// (>= 2 * ngroups ints, zeroed once) and peer_ll[r] (2 * span_bytes, zeroed, or peer_ll = NULL) are rank r's buffers as
+// mapped into THIS process (b200_ipc_open_handle).  Every rank runs its plan the same number of times;
+// b200_sequence_run returns only after all ranks' rows have landed in this rank's dst.
 int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, int ngroups, void * plan_device, size_t plan_bytes, int world,
                                       int rank, void * const * peer_base, size_t span_bytes, int32_t * const * peer_sync,
-                                      b200_stream_t stream_) {
+                                      void * const * peer_ll, b200_stream_t stream_) {
     if (world < 1 || world > 16 || rank < 0 || rank >= world || !peer_base || !peer_sync) return B200_ERR_SHAPE;
-    for (int r = 0; r < world; r++)
-        if (!peer_base[r] || !peer_sync[r] || (uintptr_t) peer_base[r] % 4 != 0) return B200_ERR_ALIGNMENT;
-    for (int g = 0; g < ngroups; g++)
-        for (int i = 0; groups && i < groups[g].nmat && i < SEQ_MAXSEG; i++) {
-            const char * d = (const char *) groups[g].dst_device[i];
-            if (groups[g].m[i] > 0 && (d < (const char *) peer_base[rank] || d + groups[g].m[i] * 4 > (const char *) peer_base[rank] + span_bytes))
-                return B200_ERR_SHAPE;   // a result outside the symmetric allocation cannot be mirrored
-        }
-    int st = b200_sequence_plan_build(groups, ngroups, plan_device, plan_bytes, stream_);
-    if (st != B200_OK) return st;
-    seq_header H = {};
-    cudaStream_t stream = (cudaStream_t) stream_;
-    B200_CUDA_TRY(cudaMemcpyAsync(&H, plan_device, sizeof(H), cudaMemcpyDeviceToHost, stream));
-    B200_CUDA_TRY(cudaStreamSynchronize(stream));
-    H.world = world, H.rank = rank, H.epoch = 0;
     for (int r = 0; r < world; r++) {
-        H.peer_delta[r] = (long long) ((const char *) peer_base[r] - (const char *) peer_base[rank]);
-        H.peer_done[r]  = peer_sync[r];
+        if (!peer_base[r] || !peer_sync[r] || (uintptr_t) peer_base[r] % 8 != 0) return B200_ERR_ALIGNMENT;
+        if (peer_ll && (!peer_ll[r] || (uintptr_t) peer_ll[r] % 8 != 0)) return B200_ERR_ALIGNMENT;
     }
-    B200_CUDA_TRY(cudaMemcpyAsync(plan_device, &H, sizeof(H), cudaMemcpyHostToDevice, stream));
-    B200_CUDA_TRY(cudaStreamSynchronize(stream));
-    return B200_OK;
+    seq_split_info sp = {world, rank, peer_base, span_bytes, peer_sync, world > 1 ? peer_ll : nullptr};
+    return seq_build(groups, ngroups, plan_device, plan_bytes, &sp, (cudaStream_t) stream_);
 }
 
 int b200_sequence_run(void * plan_device, b200_stream_t stream_) {

@@ -111,7 +111,7 @@ def lib():
     L.b200_sequence_plan_size.argtypes = [i32]
     L.b200_sequence_plan_build.argtypes = [vp, i32, vp, sz, vp]
     L.b200_sequence_run.argtypes = [vp, vp]
-    L.b200_sequence_plan_build_rowsplit.argtypes = [vp, i32, vp, sz, i32, i32, vp, sz, vp, vp]
+    L.b200_sequence_plan_build_rowsplit.argtypes = [vp, i32, vp, sz, i32, i32, vp, sz, vp, vp, vp]
     L.b200_sequence_status.argtypes = [vp, C.POINTER(i32), vp]
     L.b200_debug_sequence_trace.argtypes = [vp, vp, vp]
     L.b200_mul_mat_id_prefers_mmq.argtypes = [i64, i64, i64, i64]
@@ -322,8 +322,9 @@ class Sequence:
     groups: [(x [1, k] or [k] f32 cuda, k, [(type, w, m, out [m] or [1, m] f32 cuda), ...], dependent)]"""
 
     def __init__(self, groups, stream=None, split=None):
-        """split = (world, rank, peer_base (ctypes array of `world` pointers), span_bytes, peer_sync (same)): this rank's
-        part of a row split; every `out` must lie inside this rank's symmetric allocation"""
+        """split = (world, rank, peer_base (ctypes array of `world` pointers), span_bytes, peer_sync (same), peer_ll (same, or
+        None)): this rank's plan of a row split.  The groups then describe the WHOLE matrices (m, out = all rows) with w = this
+        rank's rows (qmm.row_split); every `out` must lie inside this rank's symmetric allocation"""
         import torch
         n = len(groups)
         arr = (SeqGroup * n)()
@@ -343,9 +344,9 @@ class Sequence:
         if split is None:
             check(lib().b200_sequence_plan_build(arr, n, self.plan.data_ptr(), nbytes, _stream_ptr(stream)))
         else:
-            world, rank, peer_base, span, peer_sync = split
+            world, rank, peer_base, span, peer_sync, peer_ll = split
             check(lib().b200_sequence_plan_build_rowsplit(arr, n, self.plan.data_ptr(), nbytes, world, rank, peer_base, span,
-                                                          peer_sync, _stream_ptr(stream)))
+                                                          peer_sync, peer_ll, _stream_ptr(stream)))
 
     def __call__(self, stream=None):
         check(lib().b200_sequence_run(self.plan.data_ptr(), _stream_ptr(stream)))

@@ -69,10 +69,12 @@ def main():
             lo, hi = qmm.row_split(m, world, rank)
             wl = w[lo:hi].contiguous() if hi > lo else w[:1].contiguous()
             keep.append(wl)
-            ms.append((t, wl, hi - lo, sym.dst[0, o + lo:o + hi]))
+            ms.append((t, wl, m, sym.dst[0, o:o + m]))         # the whole matrix; w = this rank's rows
         groups.append((x.view(1, k), k, ms, True))
         x = sym.dst[0, os_[0]:os_[0] + mats[0][1]]
-    seq = qmm.Sequence(groups, split=(world, rank, sym.ptr_dst, total * 4, sym.ptr_sync[0]))
+    use_ll = os.environ.get("SEQ_SPLIT_LL", "1") != "0"           # exchange protocol: flag-in-data (default) or counters
+    llb = PeerBuffers(1, 2 * total, 1, world, rank, dev) if use_ll else None
+    seq = qmm.Sequence(groups, split=(world, rank, sym.ptr_dst, total * 4, sym.ptr_sync[0], llb.ptr_dst if use_ll else None))
     dist.barrier()
     bad = 0
     for it in range(6):
@@ -110,7 +112,7 @@ def main():
     s.synchronize()
     same = torch.equal(sym.dst[0], ref) and seq.status() == 0
     bad += 0 if same else 1
-    print("rank %d/%d: %d groups, %s, %.1f us per run" % (rank, world, len(groups), "OK" if not bad else "MISMATCH",
+    print("rank %d/%d: %d groups, %s, %s, %.1f us per run" % (rank, world, len(groups), "ll" if use_ll else "counters", "OK" if not bad else "MISMATCH",
                                                         e0.elapsed_time(e1) * 1e3 / 20), flush=True)
     flag = torch.tensor([bad], device=dev)
     dist.all_reduce(flag)

@@ -644,6 +644,8 @@ def test_sequence_row_split_two_gpus_bit_identical():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29533", os.path.join(root, "tests", "seq_rowsplit_check.py")]
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
-    assert r.returncode == 0, r.stdout[-3000:]
-    assert r.stdout.count("OK") >= 2, r.stdout[-3000:]
+    for ll in ("1", "0"):          # both exchange protocols: flag-in-data, and mirrored stores + system-scope counters
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300,
+                           env=dict(os.environ, SEQ_SPLIT_LL=ll))
+        assert r.returncode == 0, r.stdout[-3000:]
+        assert r.stdout.count("OK") >= 2, r.stdout[-3000:]
