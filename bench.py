@@ -624,7 +624,7 @@ def main():
                                      else "mirrored stores + system-scope fence + remote counters",
                          "hbm_gbs_per_gpu": step_bytes / ms_sq / 1e6,
                          "api": "b200_sequence_plan_build_rowsplit + b200_sequence_run per rank: one persistent kernel per GPU, rows "
-                                "mirrored into every rank's dst over NVLink from the epilogue, system-scope arrival counters"}
+                                "stored into every rank over NVLink from the epilogue"}
             if os.environ.get("B200_BENCH_SEQ_TRACE"):
                 # in-kernel globaltimer stamps of one token (b200_debug_sequence_trace): where a group's time goes on this rank
                 import numpy as np
@@ -878,20 +878,63 @@ def main():
         sel = [(i, mm) for i, mm in enumerate(mms[:-1])]
         planes = [qmm.build_plane(mms[i][1], weights[i], slices[i][1] - slices[i][0], mms[i][3]) if weights[i] is not None else None
                   for i, _ in sel]
-        opp_l = {m: torch.empty((npp, maxrows[m]), device=dev) for _, (_, _, m, _) in sel}
-        opp_f = {m: torch.empty((world, npp, maxrows[m]), device=dev) for _, (_, _, m, _) in sel}
+        # one local slice buffer and one gathered buffer per kind of matrix (attn_q, ffn_up, ...), as in the decode legs
+        opp_l, opp_f = {}, {}
+        for _, (name, _, m, _) in sel:
+            b_ = name.split(".")[0]
+            if b_ not in opp_l:
+                opp_l[b_] = torch.empty((npp, maxrows[m]), device=dev)
+                opp_f[b_] = torch.empty((world, npp, maxrows[m]), device=dev)
+
+        def pgroup2(name):
+            base = name.split(".")[0]
+            return {"attn_q": "qkv", "attn_k": "qkv", "attn_v": "qkv", "ffn_gate": "gu", "ffn_up": "gu"}.get(base, base)
+        # matmuls that read the same activations share one b200_mul_mat_mmq_multi call (activations quantized once); the
+        # group's result slices are then all-gathered, and the next group starts after that (it needs the whole result)
+        pg = []
+        for (i, (name, t, m, k)), pl in zip(sel, planes):
+            key = (pgroup2(name), name.split(".")[-1])
+            if not pg or pg[-1][0] != key:
+                pg.append((key, k, []))
+            lo, hi, _ = slices[i]
+            pg[-1][2].append((name.split(".")[0], t, hi - lo, pl))
+        pcalls2 = []
+        for _, k, members in pg:
+            own = [(b_, t, rows, pl) for b_, t, rows, pl in members if pl is not None and rows > 0]
+            call = None
+            if own:
+                call = qmm.MultiMatMulMMQ([t for _, t, _, _ in own], [pl for _, _, _, pl in own], [rows for _, _, rows, _ in own], k,
+                                          [opp_l[b_][:, :rows] for b_, _, rows, _ in own], npp)
+            pcalls2.append((call, xpp[k], [b_ for b_, _, _, _ in members]))
 
         def prefill_step_split():
-            for (i, (name, t, m, k)), pl in zip(sel, planes):
-                lo, hi, _ = slices[i]
-                if pl is not None:
-                    qmm.mul_mat_mmq(t, pl, xpp[k], hi - lo, k, out=opp_l[m][:, :hi - lo])   # (dst row stride = widest slice)
-                dist.all_gather_into_tensor(opp_f[m], opp_l[m])
+            for call, x, bs in pcalls2:
+                if call is not None:
+                    call(x)
+                for b_ in bs:
+                    dist.all_gather_into_tensor(opp_f[b_], opp_l[b_])
         for _ in range(2):
             prefill_step_split()
         torch.cuda.synchronize()
         dist.barrier()
-        ms_pp = timed(prefill_step_split, 6, 2)
+        ms_pp_eager = timed(prefill_step_split, 6, 2)
+        ms_pp, pp_launch = ms_pp_eager, "eager"
+        if use_graph:
+            try:
+                gpp = torch.cuda.CUDAGraph()
+                with torch.cuda.stream(stream):
+                    prefill_step_split()
+                    stream.synchronize()
+                    dist.barrier()
+                    with torch.cuda.graph(gpp, stream=stream):
+                        prefill_step_split()
+                dist.barrier()
+                ms_pp_graph = timed(gpp.replay, 6, 2)
+                if ms_pp_graph < ms_pp:
+                    ms_pp, pp_launch = ms_pp_graph, "cuda_graph_replay"
+                del gpp
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write("pp512 row-split graph capture failed: %s\n" % str(e)[:200])
         flops = sum(2.0 * m * k * npp for _, (_, _, m, k) in sel)
         try:
             mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -900,7 +943,9 @@ def main():
             bf16_burst = 1590.0
         tops = flops / ms_pp / 1e9
         pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 6,
-              "launch": "eager", "collective": "dist.all_gather_into_tensor per matmul (NCCL)",
+              "launch": pp_launch, "ms_per_step_eager": ms_pp_eager,
+              "collective": "dist.all_gather_into_tensor per matmul (NCCL); matmuls sharing activations in one b200_mul_mat_mmq_multi call",
+              "all_gather_bytes_per_step_per_rank": sum(4.0 * npp * maxrows[m] * (world - 1) for _, (_, _, m, _) in sel),
               "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),
               "roofline": {"bound": "tensor", "achieved": tops, "unit": "TOP/s (int8), all GPUs", "peak": world * 2 * bf16_burst,
                            "frac": tops / (world * 2 * bf16_burst),

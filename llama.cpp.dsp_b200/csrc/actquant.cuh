@@ -14,17 +14,26 @@ namespace b200 {
 //   int8   qs[k]            quantized values (for IQ4_XS weights: pair-interleaved inside each 32-block, see below)
 //   float2 ds[k/32]         {d, d * sum(qs)}   d = fp16-rounded scale as float; the product is exact integer * d
 //   short2 s16[k/32]        sums of qs over the two 16-element halves of the block (used by Q6_K)
-// All three sections start 16-byte aligned.
+// All three sections start 16-byte aligned; qs is padded to whole 64-byte units.
+// In SHARED memory (the GEMV kernels' fused quantizer) the 16-byte chunks of qs are rotated inside each 64-byte unit
+// (q8_swz): a lane of the GEMV loads the four chunks of ITS unit, lanes are 64 bytes apart, and without the rotation
+// every LDS.128 of a warp falls on two groups of four banks (16-way conflict, ~0.5 us per kernel with 16 warps loading at
+// once); rotated by (unit >> 1) the 32 lanes spread over all banks (4 wavefronts: the minimum for 512 bytes).
 struct q8_layout {
     uint32_t off_ds, off_s16, bytes;
 };
 __host__ __device__ __forceinline__ q8_layout q8_soa_layout(int64_t k) {
     q8_layout L;
     const uint32_t nb = (uint32_t) (k / 32);
-    L.off_ds  = (uint32_t) ((k + 15) & ~(int64_t) 15);
+    L.off_ds  = (uint32_t) ((k + 63) & ~(int64_t) 63);
     L.off_s16 = L.off_ds + ((nb * 8 + 15) & ~15u);
     L.bytes   = L.off_s16 + ((nb * 4 + 15) & ~15u);
     return L;
+}
+
+// byte offset o inside qs -> where it lives in the shared-memory copy
+__host__ __device__ __forceinline__ uint32_t q8_swz(uint32_t o) {
+    return (o & ~0x30u) | ((((o >> 4) + (o >> 7)) & 3u) << 4);
 }
 
 #ifdef __CUDACC__
@@ -76,7 +85,7 @@ __device__ __forceinline__ float4 load_f4_cg(const float * p, bool vec) {
 // IQ4_XS kernel's prmt codebook lookup emits weights.
 // UNROLL: how many of a warp's iterations issue their global loads back to back before any arithmetic (the GEMV's
 // fused prologue uses 4 so that a row costs one L2 round trip instead of one per iteration).
-template <bool INTERLEAVE, int UNROLL = 1, bool CG = false>
+template <bool INTERLEAVE, int UNROLL = 1, bool CG = false, bool SWZ = false>
 __device__ __forceinline__ void quantize_row_q8_soa(const float * __restrict__ x, int64_t k, uint8_t * out,
                                                     q8_layout L, int warp, int nwarps, int lane, bool vec) {
     const int nb   = (int) (k / 32);
@@ -111,7 +120,8 @@ __device__ __forceinline__ void quantize_row_q8_soa(const float * __restrict__ x
                 pos = 8 * (sub & 3) + (sub < 4 ? 0 : 4);
             }
             if (active) {
-                *reinterpret_cast<uint32_t *>(out + (int64_t) b * 32 + pos) = w;
+                const uint32_t o = (uint32_t) b * 32u + (uint32_t) pos;
+                *reinterpret_cast<uint32_t *>(out + (SWZ ? q8_swz(o) : o)) = w;
                 if (sub == 0) {
                     const float dh = __half2float(__float2half_rn(r.d));
                     ds[b]  = make_float2(dh, dh * (float) r.isum);

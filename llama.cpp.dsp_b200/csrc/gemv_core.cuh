@@ -130,7 +130,8 @@ __device__ __forceinline__ void make_unit_f32(q8_unit & u, const float * __restr
 // Build the unit from activations already quantized into the SoA layout (actquant.cuh) in global memory.
 template <int TYPE, bool SMEM = false>
 __device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __restrict__ xq, q8_layout L, int k, int ug) {
-    // SMEM: xq points into shared memory (filled by the CTA's cooperative quantizer): no read-only-cache loads
+    // SMEM: xq points into shared memory (filled by the CTA's cooperative quantizer with the chunk rotation q8_swz): no
+    // read-only-cache loads, rotated chunk addresses
     auto ld16 = [](const uint8_t * p) { return SMEM ? *reinterpret_cast<const uint4 *>(p) : __ldg(reinterpret_cast<const uint4 *>(p)); };
     auto ldf2 = [](const float2 * p) { return SMEM ? *p : __ldg(p); };
     auto lds2 = [](const short2 * p) { return SMEM ? *p : __ldg(p); };
@@ -140,7 +141,8 @@ __device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __rest
         const int b32 = (ug >> 2) * 8 + ((ug >> 1) & 1) * 4, l0 = (ug & 1) * 16;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const uint4 t = ld16(xq + (b32 + j) * 32 + l0);
+            const uint32_t o = (uint32_t) ((b32 + j) * 32 + l0);
+            const uint4 t = ld16(xq + (SMEM ? q8_swz(o) : o));
             u.q[4 * j] = t.x, u.q[4 * j + 1] = t.y, u.q[4 * j + 2] = t.z, u.q[4 * j + 3] = t.w;
             u.d[j] = ldf2(&ds[b32 + j]).x;
             const short2 ss = lds2(&s16[b32 + j]);
@@ -152,8 +154,8 @@ __device__ __forceinline__ void make_unit_q8(q8_unit & u, const uint8_t * __rest
         for (int h = 0; h < 2; h++) {
             const int b = 2 * ug + h;
             if (b < nblk) {
-                const uint4 t0 = ld16(xq + b * 32);
-                const uint4 t1 = ld16(xq + b * 32 + 16);
+                const uint4 t0 = ld16(xq + (SMEM ? q8_swz((uint32_t) b * 32u) : (uint32_t) b * 32u));
+                const uint4 t1 = ld16(xq + (SMEM ? q8_swz((uint32_t) b * 32u + 16u) : (uint32_t) b * 32u + 16u));
                 u.q[8 * h] = t0.x, u.q[8 * h + 1] = t0.y, u.q[8 * h + 2] = t0.z, u.q[8 * h + 3] = t0.w;
                 u.q[8 * h + 4] = t1.x, u.q[8 * h + 5] = t1.y, u.q[8 * h + 6] = t1.z, u.q[8 * h + 7] = t1.w;
                 const float2 dd = ldf2(&ds[b]);

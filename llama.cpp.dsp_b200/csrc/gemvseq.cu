@@ -431,8 +431,8 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
             // (8 loads per lane in flight: k <= 16384 is ONE L2 round trip per CTA -- under the weight prefetch a round trip
             //  costs 1-2 us, profiles/r02/seq_trace_*.log)
             if ((dbg & 1) && g > 0) {
-            } else if (Gc->interleave) quantize_row_q8_soa<true, 8, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
-            else                quantize_row_q8_soa<false, 8, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            } else if (Gc->interleave) quantize_row_q8_soa<true, 8, true, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
+            else                quantize_row_q8_soa<false, 8, true, true>(x, k, act, L, warp, SEQ_NW, lane, vec);
             named_bar_sync(1, SEQ_NW * 32);
             if (threadIdx.x == 0) {
                 if (lookahead) st_release_cta_shared(cons_a, g + 1);

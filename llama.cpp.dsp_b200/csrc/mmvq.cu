@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     if (a.act_bytes) {
         // fused quantizer: all NW compute warps (spare ones included) quantize the row into shared memory once,
         // eight lanes per 32-block, with exactly the arithmetic of the standalone kernel (actquant.cuh)
-        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS, 4>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
+        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS, 4, false, true>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
         asm volatile("bar.sync 1, %0;" ::"n"(NW * 32) : "memory");
     }
     const int team = warp / T, wt = warp - team * T;
