@@ -221,6 +221,73 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def config3_sweep(args):
+    """BASELINE config 3: MUL_MAT m=4096 k=14336, every weight type, n in {1,2,4,8,512} -- B200 (b200_mul_mat through the
+    C ABI, weights cycled over copies that exceed L2) beside the unmodified ggml-cpu (oracle/_ref/ref-mulmat-bench, all host
+    threads).  Prints one JSON line with the table; tools read it into BASELINE.md.  Not the bench contract line."""
+    import torch
+    import b200pkg
+    qmm = b200pkg.load()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(3)
+    m, k, copies = 4096, 14336, 8
+    threads = host_threads()
+    rows = []
+    for t in (Q4_0, Q8_0, Q4_K, Q6_K, IQ4_XS):
+        ws = [gen_weights(torch, t, m, k, gen, dev) for _ in range(copies)]       # 8 x 24..62 MB > 126 MB of L2
+        wbytes = m * (k // BLOCK[t]) * TSIZE[t]
+        planes = None
+        for n in (1, 2, 4, 8, 512):
+            x = torch.rand((n, k), device=dev, generator=gen) * 2 - 1
+            out = torch.empty((n, m), device=dev)
+            if n >= 512 and planes is None:
+                planes = [qmm.build_plane(t, w, m, k) for w in ws]      # what the plug-in caches beside the weights
+
+            def calls():
+                for i in range(copies):
+                    if n >= 512:
+                        qmm.mul_mat_mmq(t, planes[i], x, m, k, out=out)
+                    else:
+                        qmm.mul_mat(t, ws[i], x, m, k, out=out)
+            st = torch.cuda.Stream(device=dev)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(st):
+                calls()
+                st.synchronize()
+                with torch.cuda.graph(g, stream=st):
+                    calls()
+                for _ in range(2):
+                    g.replay()
+                st.synchronize()
+                reps = 10 if n < 512 else 5
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(st)
+                for _ in range(reps):
+                    g.replay()
+                e1.record(st)
+                st.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (reps * copies)
+            del g
+            cpu_us = None
+            try:
+                exe = os.path.join(ROOT, "oracle", "_ref", "ref-mulmat-bench")
+                cmd = [exe, "--threads", str(threads), "--steps", "4" if n < 512 else "2", "--warmup", "1", "--n", str(n),
+                       "--copies", "4", "%s:%d:%d:4" % (TNAME[t], m, k)]
+                r = json.loads([ln for ln in subprocess.run(cmd, check=True, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                                                            text=True, timeout=300).stdout.splitlines() if ln.startswith("{")][-1])
+                cpu_us = r["ms_per_step"] * 1e3 / 4
+            except Exception:  # noqa: BLE001
+                pass
+            rows.append({"type": TNAME[t], "n": n, "b200_us": us, "b200_gbs": (wbytes + n * k * 4 + n * m * 4) / us / 1e3,
+                         "b200_tops": 2.0 * m * k * n / us / 1e6, "ggml_cpu_us": cpu_us, "cpu_threads": threads,
+                         "path": "tensor cores (cached int8 plane)" if n >= 512 else "gemv"})
+        del ws, planes
+    print(json.dumps({"config3_sweep": rows, "m": m, "k": k, "note": "CUDA-graph replay of b200_mul_mat (n <= 8) / b200_mul_mat_mmq "
+                      "with cached planes (n = 512) over %d weight copies (> L2); activation quantizer included" % copies}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -230,6 +297,7 @@ def main():
     ap.add_argument("--workload", default=None, choices=list(MODELS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-pp", action="store_true", help="skip the pp512 leg")
+    ap.add_argument("--sweep", action="store_true", help="BASELINE config 3 table (MUL_MAT 4096x14336, all types, n=1..512) instead of the bench line")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: how the row slices come together (fused = peer stores from the GEMV epilogue)")
     ap.add_argument("--per-node", action="store_true",
@@ -250,6 +318,9 @@ def main():
     if with_sub:
         args.no_pp = True
 
+    if args.sweep:
+        config3_sweep(args)
+        return
     if args.impl == "reference":
         return reference_arm(args, model)
 
@@ -338,6 +409,17 @@ def main():
     for _ in range(2):
         token_step()
     torch.cuda.synchronize()
+
+    if os.environ.get("B200_BENCH_NVTX_STEP"):
+        # profiling aid (tools/gpu_r2_traffic.sh): ONE eager token inside an NVTX range, so that `ncu --nvtx --nvtx-include
+        # b200_step/` sees exactly the kernels of a step (DRAM bytes for roofline.traffic, the launch list); then stop
+        torch.cuda.nvtx.range_push("b200_step")
+        token_step()
+        torch.cuda.synchronize()
+        torch.cuda.nvtx.range_pop()
+        print(json.dumps({"nvtx_step": True, "launches_per_step": launches_per_step, "algorithmic_bytes_per_step": step_bytes,
+                          "workload": model}))
+        return
 
     stream = torch.cuda.Stream(device=dev)
     # one CUDA graph per token (NCCL collectives are capturable too); B200_BENCH_GRAPH_MULTI=0 keeps N>1 eager
@@ -1078,11 +1160,14 @@ def main():
         # DRAM bytes of all GEMV launches of one step, from the committed ncu pass over the same workload (None otherwise)
         traffic, traffic_src = None, None
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "decode_step_dram_traffic.json")))
-            if world == 1 and model == "llama3-8b-q4_k_m" and tj["algorithmic_bytes_per_step"] == step_bytes:
-                traffic = tj["gemv_dram_bytes_read"] + tj["gemv_dram_bytes_write"]
-                traffic_src = "ncu dram__bytes_read.sum + dram__bytes_write.sum over the step's GEMV launches " \
-                              "(profiles/r01/decode_step_dram_traffic.json)"
+            for tf in ("profiles/r02/decode_step_dram_traffic_%s.json" % model, "profiles/r01/decode_step_dram_traffic.json"):
+                if not os.path.exists(os.path.join(ROOT, tf)):
+                    continue
+                tj = json.load(open(os.path.join(ROOT, tf)))
+                if world == 1 and tj["algorithmic_bytes_per_step"] == step_bytes:
+                    traffic = tj["gemv_dram_bytes_read"] + tj["gemv_dram_bytes_write"]
+                    traffic_src = "ncu dram__bytes_read.sum + dram__bytes_write.sum over the step's GEMV launches (%s)" % tf
+                    break
         except Exception:  # noqa: BLE001
             pass
         achieved = step_bytes / ms_step / 1e6   # GB/s per GPU (rank 0's slice)
