@@ -411,7 +411,7 @@ def main():
     torch.cuda.synchronize()
 
     if os.environ.get("B200_BENCH_NVTX_STEP"):
-        # profiling aid (tools/gpu_r2_traffic.sh): ONE eager token inside an NVTX range, so that `ncu --nvtx --nvtx-include
+        # profiling aid (tools/gpu_scripts/final_1gpu.sh): ONE eager token inside an NVTX range, so that `ncu --nvtx --nvtx-include
         # b200_step/` sees exactly the kernels of a step (DRAM bytes for roofline.traffic, the launch list); then stop
         torch.cuda.nvtx.range_push("b200_step")
         token_step()

@@ -344,8 +344,8 @@ B200_API int b200_row_split(int64_t m, int world, int rank, const float * tensor
  *              number of arrivals that makes that result whole: the activation quantizer of this call then waits
  *              in-kernel (bounded spin on the arrival counter, the
  *              producers run on other GPUs) until that result is whole, and this call re-arms the block -- the chained
- *              form of b200_rowsplit_wait without a stream operation between the two matmuls.  A timeout (~2 s) leaves
- *              -1 in wait_sync[1] instead of hanging.
+ *              form of b200_rowsplit_wait without a stream operation between the two matmuls.  A wait that gives up
+ *              (~2 s) is counted per device instead of hanging the stream: b200_rowsplit_timeout_count.
  *   workspace  device scratch of b200_mul_mat_rowsplit_workspace_size(type, n, k) bytes
  *
  * Completion: every fused call of every rank counts one ARRIVAL on each rank's block, so dst on THIS rank is whole once
@@ -362,6 +362,10 @@ B200_API int b200_mul_mat_rowsplit_fused(int type, const void * W, const float *
                                          int wait_arrivals, void * workspace, size_t workspace_bytes,
                                          b200_stream_t stream);
 B200_API int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream);
+/* *count = in-kernel row-split waits on the current device that gave up since the last call (then reset to 0); the
+ * matmuls behind such a wait ran on incomplete activations.  Synchronizes the stream.  No counterpart in the reference,
+ * whose peer copies are ordered by events (ggml-cuda.cu:1676-1691). */
+B200_API int b200_rowsplit_timeout_count(int * count, b200_stream_t stream);
 
 /* CUDA IPC helpers so that one-process-per-GPU hosts (torchrun) can exchange peer buffers without torch types.
  * The handle names the allocation device_ptr lies in; *offset_out is device_ptr's offset inside it. */

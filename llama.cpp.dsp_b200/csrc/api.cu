@@ -330,7 +330,7 @@ int b200_mul_mat(int type, const void * W, int64_t w_row_stride, const float * x
     int st = check_weights(type, W, w_row_stride, k);
     if (st != B200_OK) return st;
     if (m < 0 || n < 0 || x_row_stride < k || dst_row_stride < m) return B200_ERR_SHAPE;
-    if (m > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
+    if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
     if ((uintptr_t) x % 4 != 0 || (uintptr_t) dst % 4 != 0) return B200_ERR_ALIGNMENT;
     if (m == 0 || n == 0) return B200_OK;
     if (k == 0) {
@@ -390,7 +390,10 @@ size_t b200_mul_mat_multi_workspace_size(int nmat, const int * types, const int6
         if (w > need) need = w;
     }
     // both activation layouts may be live at once (IQ4_XS wants its own)
-    if (k > 0 && n > 0 && n < mmq_min_batch()) need = 2 * ws_align((size_t) n * q8_soa_layout(k).bytes);
+    if (k > 0 && n > 0 && n < mmq_min_batch()) {
+        const size_t both = 2 * ws_align((size_t) n * q8_soa_layout(k).bytes);
+        if (both > need) need = both;   // (never less than what a per-matrix fall-back to b200_mul_mat needs)
+    }
     return need;
 }
 
@@ -610,6 +613,7 @@ int b200_mul_mat_id(int type, const void * as, int64_t expert_stride, const floa
     g.x = b, g.dst = dst, g.m = m, g.k = k, g.ncols = 1, g.world = 1;
     g.x_col_stride = k, g.dst_col_stride = m;
     g.ids = ids, g.ids_row_stride = ids_row_stride, g.n_used = (int) n_used, g.ne11 = (int) ne11;
+    g.n_expert = (int) n_expert;
     g.x_token_stride = b_token_stride, g.x_slot_stride = b_slot_stride;
     g.dst_token_stride = dst_token_stride, g.dst_slot_stride = dst_slot_stride;
     const bool      fused = k <= fused_quant_max_k();
@@ -798,6 +802,11 @@ int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream)
     if (write_fn((CUstream) stream, (CUdeviceptr) sync_local, 0, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS)
         return B200_ERR_CUDA;
     return B200_OK;
+}
+
+int b200_rowsplit_timeout_count(int * count, b200_stream_t stream) {
+    if (!count) return B200_ERR_SHAPE;
+    return rowsplit_timeouts_fetch(count, (cudaStream_t) stream);
 }
 
 int b200_ipc_get_handle(void * device_ptr, void * handle_out, int64_t * offset_out) {

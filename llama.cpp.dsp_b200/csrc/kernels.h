@@ -41,6 +41,7 @@ struct gemv_args {
     const int32_t * ids;
     int64_t        ids_row_stride;
     int            n_used, ne11;
+    int            n_expert;         // ids outside [0, n_expert) leave their dst row untouched (0 = no check)
     int64_t        npairs;
     int64_t        x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
     // grouped MUL_MAT_ID (it_hdr != nullptr, ids == nullptr): grid.y = npairs = upper bound of the item count,
@@ -67,6 +68,7 @@ struct gemv_args {
 // MUL_MAT_ID plan: group the (token, slot) pairs by the expert they chose, 4 pairs per work item (one GEMV column each)
 size_t  mmid_plan_bytes(int64_t npairs, int64_t n_expert);
 int64_t mmid_max_items(int64_t npairs, int64_t n_expert);
+int     rowsplit_timeouts_fetch(int * count, cudaStream_t stream);   // quantize.cu: waits that gave up since the last call
 int     launch_mmid_plan(const int32_t * ids, int64_t ids_row_stride, int64_t n_tokens, int64_t n_used, int64_t n_expert,
                          void * plan, cudaStream_t stream);
 void   gemv_trace_set(void * base, long long launches);   // profiling aid (tools/gemv_trace.py)

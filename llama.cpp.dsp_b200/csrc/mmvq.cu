@@ -51,7 +51,7 @@ struct gemv_kargs {
     int             act_bytes;    // > 0: the CTA quantizes x into this much shared memory (fused quantizer), 128-aligned
     const int32_t * ids;
     int64_t         ids_row_stride;
-    int             n_used, ne11;
+    int             n_used, ne11, n_expert;
     int64_t         x_token_stride, x_slot_stride, dst_token_stride, dst_slot_stride;
     // grouped MUL_MAT_ID (it_hdr != nullptr): blockIdx.y = work item = one expert x up to NCOLS (token, slot) pairs that
     // chose it (k_mmid_plan); it_hdr[0] = number of items, it_pairs[item][c] = pair index or -1
@@ -156,6 +156,9 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
         pdl_wait();
         const int64_t p = blockIdx.y, tok = p / a.n_used, slot = p % a.n_used;
         const int     e = a.ids[tok * a.ids_row_stride + slot];
+        // an id outside the expert range leaves its dst row untouched, as in the grouped plan (the reference asserts
+        // 0 <= id < n_as, ggml-cuda.cu:2071); CTA-uniform, taken before any barrier is initialised
+        if (a.n_expert > 0 && (e < 0 || e >= a.n_expert)) return;
         W   += (int64_t) e * a.w_expert_stride;
         x   += tok * a.x_token_stride + (slot % a.ne11) * a.x_slot_stride;
         dst += tok * a.dst_token_stride + slot * a.dst_slot_stride;
@@ -244,7 +247,12 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
                 int add = 1;
                 if (atomicAdd(peers.local, 1) == total - 1) {
                     atomicExch(peers.local, 0);
-                    if (peers.rearm) atomicExch(peers.rearm, 0);   // every CTA of this rank is past the wait on it
+                    if (peers.rearm) {
+                        atomicExch(peers.rearm, 0);             // every CTA of this rank is past the wait on it
+                        // ... and the re-arm must be in place before any peer can see this launch's signal and start
+                        // sending the next arrivals to that counter
+                        asm volatile("fence.acq_rel.sys;" ::: "memory");
+                    }
                     add += B200_ARRIVAL_UNIT - total;
                 }
                 for (int r = 0; r < a.world; r++)
@@ -508,6 +516,7 @@ static int launch_gemv_k(const gemv_args & g, const gemv_plan & P, int gx, cudaS
     a.nst = P.nst, a.T = P.T, a.nteams = P.nteams, a.row_pitch = P.row_pitch, a.stage_bytes = P.stage_bytes;
     a.act_bytes = P.act_bytes;
     a.ids = g.ids, a.ids_row_stride = g.ids_row_stride, a.n_used = g.n_used > 0 ? g.n_used : 1;
+    a.n_expert = g.n_expert;
     a.it_hdr = g.it_hdr, a.it_expert = g.it_expert, a.it_pairs = g.it_pairs;
     a.ne11 = g.ne11 > 0 ? g.ne11 : 1;
     a.x_token_stride = g.x_token_stride, a.x_slot_stride = g.x_slot_stride;

@@ -53,6 +53,9 @@ int launch_quantize_q8_1_ggml(const float * x, int64_t x_stride, void * y, int64
 // ---------------------------------------------------------------------------------------------- q8_1, SoA layout
 // grid (ceil(k/32 / 32), nrows), 8 warps: every 8-lane group quantizes one block; output rows are L.bytes apart.
 // Launched with programmatic stream serialization so the GEMV that consumes it can prefetch weights meanwhile.
+// row-split waits that gave up (per device; read and cleared by rowsplit_timeouts_fetch)
+__device__ int g_rowsplit_timeouts = 0;
+
 template <bool INTERLEAVE>
 __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restrict__ x, int64_t x_stride,
                                                          uint8_t * __restrict__ y, int64_t y_pitch, int64_t k, bool vec,
@@ -62,7 +65,9 @@ __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restric
     if (wait_sync) {
         // row-split: x is only whole once `wait_target` ranks' slices have landed (their GEMVs bump wait_sync[0] over
         // NVLink).  The producers are kernels on OTHER GPUs, so this cannot starve them; the spin is bounded anyway
-        // (~2 s) and leaves a mark in wait_sync[1] instead of hanging the stream.
+        // (~2 s) and counts a time-out in g_rowsplit_timeouts (b200_rowsplit_timeout_count) instead of hanging the
+        // stream.  (The mark used to go into wait_sync[1], which is the block's local CTA counter: one time-out broke
+        // every later use of the block.)  The kernel then quantizes whatever x holds: the caller must check the count.
         if (threadIdx.x == 0) {
             const long long t0 = clock64();
             int v;
@@ -70,7 +75,7 @@ __global__ void __launch_bounds__(256) k_quantize_q8_soa(const float * __restric
                 asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(wait_sync) : "memory");
                 if (v >= wait_target) break;
                 if (clock64() - t0 > (1ll << 32)) {
-                    atomicExch(wait_sync + 1, -1);
+                    atomicAdd(&g_rowsplit_timeouts, 1);
                     break;
                 }
             }
@@ -146,6 +151,14 @@ int launch_dequantize_f32(int type, const void * w, int64_t w_stride, float * y,
     }
     note_launch();
     return check_cuda(cudaGetLastError(), "k_dequantize");
+}
+
+int rowsplit_timeouts_fetch(int * count, cudaStream_t stream) {
+    int zero = 0;
+    B200_CUDA_TRY(cudaMemcpyFromSymbolAsync(count, g_rowsplit_timeouts, sizeof(int), 0, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(stream));
+    if (*count) B200_CUDA_TRY(cudaMemcpyToSymbolAsync(g_rowsplit_timeouts, &zero, sizeof(int), 0, cudaMemcpyHostToDevice, stream));
+    return B200_OK;
 }
 
 }  // namespace b200

@@ -157,7 +157,10 @@ def test_fused_peer_store_row_split_one_device(t, m, k, n, world, ts):
     torch.cuda.synchronize()
     for r in range(world):
         assert torch.equal(dsts[r], want), r
-        assert int(syncs[r].abs().sum()) == 0                                    # all re-armed, no timeout marks
+        assert int(syncs[r].abs().sum()) == 0                                    # all re-armed
+    gave_up = C.c_int(-1)
+    qmm.check(qmm.lib().b200_rowsplit_timeout_count(C.byref(gave_up), None))
+    assert gave_up.value == 0                                                    # no in-kernel wait timed out
 
 
 @pytest.mark.gpu

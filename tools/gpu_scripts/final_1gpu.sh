@@ -1,7 +1,7 @@
 #!/bin/bash
 # final 1-GPU measurements of the round
 mkdir -p gpurun_out
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/f1_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/f1_pytest_gpu.log
 timeout 900 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/f1_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/f1_smoke.log
 # DRAM traffic + launch list of one 70B step (plain run first, then the same command under ncu)

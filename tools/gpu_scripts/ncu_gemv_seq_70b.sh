@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu of the sequence kernel on the 70B token (one launch), after the same command ran clean
 mkdir -p gpurun_out
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 timeout 600 python tools/seq_bench.py llama3-70b-q4_k_m 3 > gpurun_out/c21_plain.log 2>&1; echo "plain rc=$?"; grep "graph replay" gpurun_out/c21_plain.log
 tag=c21_ncu_gemv_seq_70b
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_gemv_seq -s 2 -c 1 -f -o gpurun_out/$tag python tools/seq_bench.py llama3-70b-q4_k_m 3 > gpurun_out/${tag}_ncu.log 2>&1; echo "ncu rc=$?"

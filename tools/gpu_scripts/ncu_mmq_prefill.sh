@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, call 12: pipelined MMQ epilogue -- parity, per-shape time, pp512 via the 8B sub-run, ncu of k_mmq_p
 mkdir -p gpurun_out
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "mmq or realistic or gemv or sequence or mul_mat" > gpurun_out/c12_pytest_mmq.log 2>&1; echo "mmq tests rc=$?"; tail -3 gpurun_out/c12_pytest_mmq.log
 for shape in "28672 4096 512" "4096 14336 512" "6144 4096 512" "4096 4096 512"; do
   set -- $shape
