@@ -273,7 +273,8 @@ B200_API int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, in
                                                size_t span_bytes, int32_t * const * peer_sync, void * const * peer_ll,
                                                b200_stream_t stream);
 B200_API int b200_sequence_run(void * plan_device, b200_stream_t stream);
-/* *error_group = 0: fine; g > 0: dependent group g timed out waiting for earlier groups (synchronizes the stream) */
+/* *error_group = 0: fine; g > 0: group g gave up waiting (~1 s) for earlier groups or for another rank's rows; every later
+ * wait of such a launch gives up at once, so its results are invalid.  Synchronizes the stream and clears the mark. */
 B200_API int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t stream);
 /* profiling aid (tools/seq_trace.py): later runs write 8 globaltimer stamps per (group, CTA) to trace_device; NULL = off */
 B200_API int b200_debug_sequence_trace(void * plan_device, void * trace_device, b200_stream_t stream);
@@ -361,6 +362,17 @@ B200_API int b200_mul_mat_rowsplit_fused(int type, const void * W, const float *
                                          int64_t n, int64_t k, int world, int rank, int32_t * wait_sync,
                                          int wait_arrivals, void * workspace, size_t workspace_bytes,
                                          b200_stream_t stream);
+/*
+ * Stream-ordered copy of `bytes` between device memory and host memory (either direction, or device to device) --
+ * what ggml_backend_cuda_set_tensor_async / _get_tensor_async do with cudaMemcpyAsync (ggml-cuda.cu:2374-2405).  When the
+ * host side is pinned (mapped under UVA) and the copy is small (<= B200_COPY_KERNEL_MAX, default 1 MiB) a copy KERNEL does
+ * it with 16-byte accesses over PCIe, chained to its neighbours by programmatic dependent launch: ~2 us per copy in a
+ * stream of launches instead of ~8-10 us per copy node.  Anything else falls back to cudaMemcpyAsync.
+ */
+B200_API int b200_copy_async(void * dst, const void * src, size_t bytes, b200_stream_t stream);
+/* same for a caller that KNOWS both pointers are device-accessible as they are (device memory, or host memory from
+ * cudaHostAlloc under unified addressing): no pointer-attribute query per call */
+B200_API int b200_copy_mapped_async(void * dst, const void * src, size_t bytes, b200_stream_t stream);
 B200_API int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream);
 /* *count = in-kernel row-split waits on the current device that gave up since the last call (then reset to 0); the
  * matmuls behind such a wait ran on incomplete activations.  Synchronizes the stream.  No counterpart in the reference,

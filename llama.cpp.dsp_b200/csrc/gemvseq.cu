@@ -180,6 +180,13 @@ __device__ __forceinline__ void seq_stage_v(int V, uint32_t base, uint32_t row_b
     else seq_stage<TYPE, 1>(base, row_bytes, c0, nr, ugc, have, k32, u, p, T, wt, lane);
 }
 
+// a wait of this kernel gives up after ~1 s (2^31 clocks) and marks the plan; once the plan is marked every later wait
+// gives up at once, so a broken exchange costs one time-out per launch, not one per group
+__device__ __forceinline__ bool seq_give_up(const long long t0, const int * error_word, int spins) {
+    if ((spins & 1023) == 1023 && *reinterpret_cast<const volatile int *>(error_word) != 0) return true;
+    return clock64() - t0 > (1ll << 31);
+}
+
 __device__ __forceinline__ void st_release_cta_shared(uint32_t addr, int v) {
     asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -363,10 +370,10 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                     const char * slot = reinterpret_cast<const char *>(pdelta[rank]) + 2 * (reinterpret_cast<char *>(d) - base_local);
                     uint32_t val, tg;
                     const long long t0 = clock64();
-                    for (;;) {
+                    for (int spins = 0;; spins++) {
                         asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(val), "=r"(tg) : "l"(slot) : "memory");
                         if (tg == tag) break;
-                        if (clock64() - t0 > (1ll << 31)) { atomicExch(&H->error, g); break; }
+                        if (seq_give_up(t0, &H->error, spins)) { atomicExch(&H->error, g); break; }
                     }
                     *d = __uint_as_float(val);
                 }
@@ -397,9 +404,8 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                 // this stream reads the whole dst
                 if (world > 1 && threadIdx.x == 0) {
                     const long long t0 = clock64();
-                    while (ld_acquire_sys(&done[ng - 1]) - target < 0) {
-                        if (clock64() - t0 > (1ll << 31)) { atomicExch(&H->error, ng); break; }
-                    }
+                    for (int spins = 0; ld_acquire_sys(&done[ng - 1]) - target < 0; spins++)
+                        if (seq_give_up(t0, &H->error, spins)) { atomicExch(&H->error, ng); break; }
                 }
                 break;
             }
@@ -412,12 +418,11 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) k_gemv_seq(uint8_t * __restric
                 if (lane < SEQ_GROUP_U4) reinterpret_cast<uint4 *>(Gc)[lane] = __ldcg(reinterpret_cast<const uint4 *>(&groups[g]) + lane);
                 if (lane == 0 && dep && g > 0 && nloc > 0) {    // all CTAs (of all ranks) have published every earlier group
                     const long long t0 = clock64();
-                    while ((world > 1 ? ld_acquire_sys(&done[g - 1]) : ld_acquire_gpu(&done[g - 1])) - target < 0) {
-                        if (clock64() - t0 > (1ll << 31)) {     // ~1 s: leave a mark instead of hanging the GPU
+                    for (int spins = 0; (world > 1 ? ld_acquire_sys(&done[g - 1]) : ld_acquire_gpu(&done[g - 1])) - target < 0; spins++)
+                        if (seq_give_up(t0, &H->error, spins)) {   // ~1 s: leave a mark instead of hanging the GPU
                             atomicExch(&H->error, g);
                             break;
                         }
-                    }
                 }
             }
             named_bar_sync(1, SEQ_NW * 32);
@@ -727,6 +732,12 @@ int b200_sequence_status(void * plan_device, int * error_group, b200_stream_t st
     B200_CUDA_TRY(cudaMemcpyAsync(&H, plan_device, sizeof(H), cudaMemcpyDeviceToHost, (cudaStream_t) stream_));
     B200_CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream_));
     *error_group = H.error;
+    if (H.error) {   // reported once: clear the mark so that later launches wait normally again
+        const int zero = 0;
+        B200_CUDA_TRY(cudaMemcpyAsync((uint8_t *) plan_device + offsetof(seq_header, error), &zero, sizeof(int), cudaMemcpyHostToDevice,
+                                      (cudaStream_t) stream_));
+        B200_CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream_));
+    }
     return B200_OK;
 }
 

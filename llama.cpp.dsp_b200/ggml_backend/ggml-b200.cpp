@@ -292,7 +292,23 @@ static ggml_backend_reg_t b200_reg();
 // CPU buffer interface, so that the scheduler's input / output copies are asynchronous DMA and the batch <= 8 path can read
 // activations from it directly (b200_mul_mat_multi_host).  GGML_CUDA_NO_PINNED in the environment switches it off, as there.
 static const char * b200_host_buft_get_name(ggml_backend_buffer_type_t) { return "B200_Host"; }
-static void b200_host_buffer_free_buffer(ggml_backend_buffer_t buffer) { CUDA_CHECK(cudaFreeHost(buffer->context)); }
+// our pinned allocations, so that tensor_set / tensor_get can tell "mapped host memory" without a driver query per copy
+static std::mutex                 g_pinned_mutex;
+static std::map<uintptr_t, size_t> g_pinned;   // base -> size
+static bool b200_is_pinned(const void * p, size_t bytes) {
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    auto it = g_pinned.upper_bound((uintptr_t) p);
+    if (it == g_pinned.begin()) return false;
+    --it;
+    return (uintptr_t) p + bytes <= it->first + it->second;
+}
+static void b200_host_buffer_free_buffer(ggml_backend_buffer_t buffer) {
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned.erase((uintptr_t) buffer->context);
+    }
+    CUDA_CHECK(cudaFreeHost(buffer->context));
+}
 static ggml_backend_buffer_t b200_host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
     void * ptr = nullptr;
     if (getenv("GGML_CUDA_NO_PINNED") == nullptr) {
@@ -305,6 +321,10 @@ static ggml_backend_buffer_t b200_host_buft_alloc_buffer(ggml_backend_buffer_typ
         }
     }
     if (ptr == nullptr) return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);   // pageable fallback
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned[(uintptr_t) ptr] = size > 0 ? size : 1;
+    }
     ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
     buffer->buft              = buft;
     buffer->iface.free_buffer = b200_host_buffer_free_buffer;
@@ -601,7 +621,9 @@ static void b200_backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * 
     GGML_ASSERT(b200_buffer_is_ours(buf) && "unsupported buffer type");
     ((b200_buffer_context *) buf->context)->drop_planes(tensor->data, ggml_nbytes(tensor));
     set_device(ctx->device);
-    CUDA_CHECK(cudaMemcpyAsync((char *) tensor->data + offset, data, size, cudaMemcpyHostToDevice, ctx->stream));
+    // (small copies from pinned memory -- activations from the B200_Host buffer type -- go out as a copy kernel)
+    if (b200_is_pinned(data, size)) B200_CHECK(b200_copy_mapped_async((char *) tensor->data + offset, data, size, ctx->stream));
+    else B200_CHECK(b200_copy_async((char *) tensor->data + offset, data, size, ctx->stream));
 }
 
 static void b200_backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor, void * data, size_t offset,
@@ -610,7 +632,8 @@ static void b200_backend_get_tensor_async(ggml_backend_t backend, const ggml_ten
     ggml_backend_buffer_t buf = tensor->view_src ? tensor->view_src->buffer : tensor->buffer;
     GGML_ASSERT(b200_buffer_is_ours(buf) && "unsupported buffer type");
     set_device(ctx->device);
-    CUDA_CHECK(cudaMemcpyAsync(data, (const char *) tensor->data + offset, size, cudaMemcpyDeviceToHost, ctx->stream));
+    if (b200_is_pinned(data, size)) B200_CHECK(b200_copy_mapped_async(data, (const char *) tensor->data + offset, size, ctx->stream));
+    else B200_CHECK(b200_copy_async(data, (const char *) tensor->data + offset, size, ctx->stream));
 }
 
 static bool b200_backend_is_ours(ggml_backend_t backend);

@@ -649,3 +649,31 @@ def test_sequence_row_split_two_gpus_bit_identical():
                            env=dict(os.environ, SEQ_SPLIT_LL=ll))
         assert r.returncode == 0, r.stdout[-3000:]
         assert r.stdout.count("OK") >= 2, r.stdout[-3000:]
+
+
+@pytest.mark.gpu
+def test_copy_async_kernel_and_fallback(qmm):
+    """b200_copy_async / b200_copy_mapped_async: small copies between device memory and PINNED host memory run as a copy
+    kernel (any size and alignment, both directions), pageable memory and large copies fall back to cudaMemcpyAsync; the
+    bytes must arrive either way and the kernel path must show up in the launch counter."""
+    import ctypes as C
+    L = qmm.lib()
+    rng = np.random.default_rng(5)
+    for nbytes, off in [(16, 0), (4096, 0), (4099, 0), (70001, 1), (1 << 20, 4), ((1 << 20) + 64, 0)]:
+        src_h = torch.from_numpy(rng.integers(0, 256, nbytes + 16, dtype=np.uint8)).pin_memory()
+        dev_buf = torch.zeros(nbytes + 16, dtype=torch.uint8, device="cuda")
+        back_h = torch.zeros(nbytes + 16, dtype=torch.uint8).pin_memory()
+        b0 = qmm.launch_count()
+        qmm.check(L.b200_copy_async(C.c_void_p(dev_buf.data_ptr() + off), C.c_void_p(src_h.data_ptr() + off), nbytes, None))
+        qmm.check(L.b200_copy_mapped_async(C.c_void_p(back_h.data_ptr() + off), C.c_void_p(dev_buf.data_ptr() + off), nbytes, None))
+        torch.cuda.synchronize()
+        assert torch.equal(back_h[off:off + nbytes], src_h[off:off + nbytes])
+        assert int(back_h[:off].sum()) == 0 and int(back_h[off + nbytes:].sum()) == 0      # nothing outside the range
+        assert (qmm.launch_count() - b0 == 2) == (nbytes <= (1 << 20))                     # kernel path up to 1 MiB
+    # pageable host memory: the generic entry falls back to the copy engine
+    src_p = torch.from_numpy(rng.integers(0, 256, 5000, dtype=np.uint8))
+    dev_buf = torch.zeros(5000, dtype=torch.uint8, device="cuda")
+    b0 = qmm.launch_count()
+    qmm.check(L.b200_copy_async(C.c_void_p(dev_buf.data_ptr()), C.c_void_p(src_p.data_ptr()), 5000, None))
+    torch.cuda.synchronize()
+    assert torch.equal(dev_buf.cpu(), src_p) and qmm.launch_count() == b0
