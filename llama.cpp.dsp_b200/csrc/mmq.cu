@@ -58,6 +58,7 @@ static_assert(MMQ_KC == 256 || MMQ_KC == 512, "chunk");
 // epilogue flavour the chunk size allows: the magic-number conversion is exact for |D| < 2^22 = 256 * 127 * 127 + ...;
 // a 512-chunk can exceed that, so it converts with I2FP (half as many conversions per weight as at 256 anyway)
 constexpr int MMQ_EPI_DEFAULT = MMQ_KC > 256 ? 0 : 2;
+constexpr int MMQ_PEPI_DEFAULT = MMQ_KC > 256 ? 0 : 3;       // persistent kernel: conversion bias kept in TMEM (epi_accumulate)
 
 int mmq_chunk() { return MMQ_KC; }
 static inline int64_t mmq_kpad(int64_t k) { return (k + MMQ_KC - 1) / MMQ_KC * MMQ_KC; }
@@ -344,6 +345,11 @@ __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[8]) { tme
 __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld32(taddr, r); }
 __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld16(taddr, r); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// eight columns of this warp's 32 lanes <- one 32-bit value (EPI 3: the accumulator's conversion bias, see below)
+__device__ __forceinline__ void tmem_st8_fill(uint32_t taddr, uint32_t v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // int32 accumulator -> fp32 without the conversion unit.  I2FP issues to the XU pipe (4 lanes/clk per SM sub-partition,
 // 8 clocks per warp instruction): ncu showed it 64 % busy with the tensor pipe at 25 % -- the conversion, not the MMA,
@@ -374,11 +380,27 @@ __device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
     return r;
 }
-// acc[0..N) += float(r[0..N)) * (sic * t[0..N)); EPI 0 = I2FP, 1 = magic-number conversion, 2 = magic + packed fp32.
-// All three produce the same bits (every operation is a separately rounded fp32 op on the same operands).
+// acc[0..N) += float(r[0..N)) * (sic * t[0..N)); EPI 0 = I2FP, 1 = magic-number conversion, 2 = magic + packed fp32,
+// 3 = packed fp32 on accumulators that ALREADY carry the bias: the persistent kernel's epilogue warps refill every
+// accumulator column they have read with MAGIC_BITS (tcgen05.st, one instruction per 8 columns) and the tensor core always
+// accumulates onto it, so r = MAGIC_BITS + D arrives as the float 12582912 + D and the two integer adds per pair are gone
+// (2.5 -> 1.75 issue slots per accumulator element; the epilogue warps are issue-bound, profiles/r02/ncu_mmq_p_v2_*).
+// All four produce the same bits (every operation is a separately rounded fp32 op on the same operands).
 template <int EPI, int N>
 __device__ __forceinline__ void epi_accumulate(const uint32_t (&r)[N], const float4 * tp, float sic, float * acc) {
-    if (EPI == 2) {
+    if (EPI == 3) {
+        const uint64_t s2 = pack2(sic, sic), nm = pack2(-MAGIC_F, -MAGIC_F);
+        uint64_t * acc2 = reinterpret_cast<uint64_t *>(acc);
+#pragma unroll
+        for (int i4 = 0; i4 < N / 4; i4++) {
+            const float4 t = tp[i4];
+            const uint64_t st0 = mul2(s2, pack2(t.x, t.y)), st1 = mul2(s2, pack2(t.z, t.w));
+            const uint64_t f0 = add2(pack2(__uint_as_float(r[4 * i4 + 0]), __uint_as_float(r[4 * i4 + 1])), nm);
+            const uint64_t f1 = add2(pack2(__uint_as_float(r[4 * i4 + 2]), __uint_as_float(r[4 * i4 + 3])), nm);
+            acc2[2 * i4 + 0] = fma2(f0, st0, acc2[2 * i4 + 0]);
+            acc2[2 * i4 + 1] = fma2(f1, st1, acc2[2 * i4 + 1]);
+        }
+    } else if (EPI == 2) {
         const uint64_t s2 = pack2(sic, sic), nm = pack2(-MAGIC_F, -MAGIC_F);
         uint64_t * acc2 = reinterpret_cast<uint64_t *>(acc);
 #pragma unroll
@@ -451,9 +473,11 @@ __device__ __forceinline__ void epi_chunk8(uint32_t tbase, const float4 * tp, fl
 #pragma unroll
     for (int g = 0; g < NG8; g++) {
         tmem_ld_wait();
+        if (EPI == 3) tmem_st8_fill(tbase + g * 8, MAGIC_BITS);  // these columns are in registers: re-arm them for the next chunk
         if (g + 1 < NG8) {
             tmem_ldw(tbase + (g + 1) * 8, r[(g + 1) & 1]);
         } else {                                                 // accumulator fully read: hand it back to the tensor core
+            if (EPI == 3) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             release();
@@ -853,7 +877,9 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                 const uint32_t idesc = MMID ? idesc_i8(MMQ_BM, __ldg(p.items + it).w)
                                             : it < p.n_main ? idesc_i8(MMQ_BM, 256) : idesc_i8(MMQ_BM, 128);
                 for (int c = 0; c < nch; c++) {
-                    TW(0, mbar_wait(bar_tempty + 8 * buf, buf_ph ^ 1));   // epilogue has drained this accumulator
+                    // epilogue has drained this accumulator (EPI 3: and refilled it with the bias -- one more phase, the
+                    // first one being the initial fill)
+                    TW(0, mbar_wait(bar_tempty + 8 * buf, EPI == 3 ? buf_ph : buf_ph ^ 1));
                     tc_fence_after();
 #pragma unroll
                     for (int h = 0; h < MMQ_KBC; h++) {
@@ -863,7 +889,7 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
                         const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sb);
 #pragma unroll
                         for (int kk = 0; kk < MMQ_BK / 32; kk++)
-                            mma_i8(tmem + buf * 256, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) ((h | kk) != 0));
+                            mma_i8(tmem + buf * 256, da + 2 * kk, db + 2 * kk, idesc, EPI == 3 ? 1u : (uint32_t) ((h | kk) != 0));
                         mma_commit(bar_empty + 8 * st);
                         if (++st == NS) st = 0, st_ph ^= 1;
                     }
@@ -883,6 +909,20 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
         const int q = warp & 3, part = (warp - 2) >> 2;          // TMEM lane quarter (warp id % 4), column part 0..3
         const float * sring = reinterpret_cast<const float *>(mmq_smem_raw + (scales - smem_u32(mmq_smem_raw)));
         uint32_t sc = 0, sc_ph = 0, buf = 0, buf_ph = 0;
+        if (EPI == 3) {
+            // every accumulator column starts as the conversion bias; from here on a column is either freshly refilled by
+            // the warp that read it, or belongs to the chunk in flight (columns an item does not use stay untouched)
+#pragma unroll
+            for (int b = 0; b < NB; b++) {
+#pragma unroll
+                for (int g = 0; g < 8; g++) tmem_st8_fill(tmem + ((uint32_t) (q * 32) << 16) + b * 256 + part * 64 + g * 8, MAGIC_BITS);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0)
+                for (int b = 0; b < NB; b++) mbar_arrive(bar_tempty + 8 * b);
+        }
         for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
             const int ncw = (MMID ? __ldg(p.items + it).w : it < p.n_main ? 256 : 128) >> 2;   // columns per warp (8 .. 64)
             const int col0 = part * ncw;
@@ -1088,8 +1128,13 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
 // persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
                                  const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
-    auto kern = k_mmq_p<MMQ_EPI_DEFAULT, false>;
-    B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
+    // B200_MMQ_TMEM_BIAS=0: the epilogue that adds the conversion bias itself (EPI 2) instead of finding it in TMEM (EPI 3)
+    const bool bias  = MMQ_PEPI_DEFAULT == 3 && env_flag("B200_MMQ_TMEM_BIAS", 1);
+    auto kern3 = k_mmq_p<MMQ_PEPI_DEFAULT, false>;
+    auto kern2 = k_mmq_p<MMQ_EPI_DEFAULT, false>;
+    B200_SMEM_ATTR_ONCE(kern3, mmq_pshape::SMEM);
+    B200_SMEM_ATTR_ONCE(kern2, mmq_pshape::SMEM);
+    auto kern = bias ? kern3 : kern2;
     mmq_pargs p = {};
     p.ntn = (a.n + 255) / 256;
     p.mtiles = mtiles;
@@ -1286,8 +1331,12 @@ int launch_mmid_mmq(int type, const void * plane, const float * b, int64_t b_tok
     mmq_pargs p = {};
     p.items = items, p.hdr = hdr, p.sorted = sorted, p.n_used = (int) n_used, p.mt_expert = (int) mt, p.m_expert = (int) m;
     p.dst_token_stride = dst_token_stride, p.dst_slot_stride = dst_slot_stride;
-    auto kern = k_mmq_p<MMQ_EPI_DEFAULT, true>;
-    B200_SMEM_ATTR_ONCE(kern, mmq_pshape::SMEM);
+    const bool bias  = MMQ_PEPI_DEFAULT == 3 && env_flag("B200_MMQ_TMEM_BIAS", 1);
+    auto kern3 = k_mmq_p<MMQ_PEPI_DEFAULT, true>;
+    auto kern2 = k_mmq_p<MMQ_EPI_DEFAULT, true>;
+    B200_SMEM_ATTR_ONCE(kern3, mmq_pshape::SMEM);
+    B200_SMEM_ATTR_ONCE(kern2, mmq_pshape::SMEM);
+    auto kern = bias ? kern3 : kern2;
     const int64_t grid = max_items < sm_count ? max_items : sm_count;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) grid, 1, 1), cfg.blockDim = dim3(mmq_pshape::THREADS, 1, 1);
