@@ -189,6 +189,10 @@ B200_API int    b200_mul_mat_mmq_multi(int nmat, const int * types, const void *
                                        size_t workspace_bytes, b200_stream_t stream);
 /* smallest n that b200_mul_mat sends to the tensor-core path (MMVQ_MAX_BATCH_SIZE + 1, ggml-cuda/mmvq.cuh:3) */
 B200_API int    b200_mmq_min_batch(void);
+/* 1 when a caller that already HOLDS a prepared plane of this type should use it for a batch of n columns: from
+ * b200_mmq_min_batch() on for every type, and from 5 columns on for Q4_K / Q6_K / IQ4_XS (the GEMV needs two passes above
+ * 4 columns).  The reference switches kernels at a fixed batch of 8 (MMVQ_MAX_BATCH_SIZE, mmvq.cuh:3). */
+B200_API int    b200_mmq_use_cached_plane(int type, int64_t n);
 /* elements of k that share one scale on the tensor-core path (plane and activation quantization granularity; a
  * build-time constant, 256 or 512): what a restatement of the path's arithmetic has to use (tests/qref.py:mul_mat_plane) */
 B200_API int    b200_mmq_chunk(void);

@@ -352,6 +352,18 @@ size_t b200_mul_mat_mmq_workspace_size(int64_t m, int64_t n, int64_t k) {
     (void) m;
     return n > 0 && k > 0 ? mmq_workspace_bytes(n, k) : 0;
 }
+// 1 when a caller that HOLDS a prepared plane should use it at this batch: always from b200_mmq_min_batch() on, and from
+// 5 columns on for the types that need one weight plane and one activation plane (Q4_K, Q6_K, IQ4_XS): the GEMV takes two
+// passes above 4 columns (27-43 us for 4096 x 14336), one pass over the plane takes 24 us (tools/small_batch_mmq.py).
+// Building a plane for such a batch does not pay; B200_MMQ_SMALL_N=0 switches the rule off.
+int b200_mmq_use_cached_plane(int type, int64_t n) {
+    if (!weight_type(type) || n <= 0) return 0;
+    if (n >= mmq_min_batch()) return 1;
+    const int small = env_knob("B200_MMQ_SMALL_N", 5);
+    if (small <= 0 || n < small) return 0;
+    return mmq_nplanes(type) == 1 && mmq_xplanes(type) == 1;
+}
+
 int b200_mul_mat_mmq(int type, const void * plane, const float * x, int64_t x_row_stride, float * dst, int64_t dst_row_stride,
                      int64_t m, int64_t n, int64_t k, void * workspace, size_t workspace_bytes, b200_stream_t stream) {
     if (!weight_type(type)) return B200_ERR_TYPE;

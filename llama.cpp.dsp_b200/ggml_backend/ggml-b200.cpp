@@ -132,6 +132,12 @@ struct b200_buffer_context {
             it = planes.erase(it);
         }
     }
+    // the plane if one is cached already (never builds): batches of 5..8 columns use it when it is there
+    const void * peek_plane(const b200_plane_key & key) {
+        std::lock_guard<std::mutex> lock(mtx);
+        auto it = planes.find(key);
+        return it == planes.end() ? nullptr : it->second.ptr;
+    }
     // The int8 plane of a weight matrix for the tensor-core path, or NULL when this call should use a transient one:
     // matrices in a weights buffer get a plane at first use, anything else at its second use without a write between.
     const void * get_plane(const b200_plane_key & key, bool weights, cudaStream_t stream) {
@@ -714,6 +720,9 @@ static void b200_compute_mul_mat(b200_backend_context * ctx, ggml_tensor * dst) 
             if (mmq) {
                 b200_plane_key key = {W, (int64_t) nb01, m, k, type};
                 plane = ((b200_buffer_context *) wbuf->context)->get_plane(key, weights, ctx->stream);
+            } else if (b200_mmq_use_cached_plane(type, n)) {     // 5..8 columns: two GEMV passes, or one pass over a plane
+                b200_plane_key key = {W, (int64_t) nb01, m, k, type};   // that an earlier prefill left behind
+                plane = ((b200_buffer_context *) wbuf->context)->peek_plane(key);
             }
             if (plane) {
                 B200_CHECK(b200_mul_mat_mmq(type, plane, x, nb11 / 4, y, nb1 / 4, m, n, k, ws, ctx->workspace_bytes, ctx->stream));
@@ -852,15 +861,23 @@ static bool b200_compute_mul_mat_group(b200_backend_context * ctx, ggml_tensor *
         dstride[i] = (int64_t) (nodes[i]->nb[1] / sizeof(float)), m[i] = a->ne[1];
         mmax = std::max(mmax, m[i]);
     }
-    if (n < b200_mmq_min_batch()) {
+    const void * planes[8];
+    bool cached = n < b200_mmq_min_batch();                      // small batch: the planes only if all of them are there already
+    for (int i = 0; cached && i < count; i++) {
+        const ggml_tensor *   a    = nodes[i]->src[0];
+        ggml_backend_buffer_t wbuf = a->view_src ? a->view_src->buffer : a->buffer;
+        b200_plane_key key = {a->data, (int64_t) a->nb[1], m[i], k, types[i]};
+        planes[i] = b200_mmq_use_cached_plane(types[i], n) ? ((b200_buffer_context *) wbuf->context)->peek_plane(key) : nullptr;
+        cached = planes[i] != nullptr;
+    }
+    if (n < b200_mmq_min_batch() && !cached) {
         const size_t ws_bytes = b200_mul_mat_multi_workspace_size(count, types, m, n, k);
         void *       ws       = ws_bytes ? ctx->scratch(ws_bytes) : nullptr;
         B200_CHECK(b200_mul_mat_multi(count, types, W, (const float *) x->data, (int64_t) (x->nb[1] / sizeof(float)), dst, dstride,
                                       m, n, k, ws, ctx->workspace_bytes, ctx->stream));
         return true;
     }
-    const void * planes[8];
-    for (int i = 0; i < count; i++) {
+    for (int i = 0; !cached && i < count; i++) {
         const ggml_tensor *   a    = nodes[i]->src[0];
         ggml_backend_buffer_t wbuf = a->view_src ? a->view_src->buffer : a->buffer;
         b200_plane_key key = {a->data, (int64_t) a->nb[1], m[i], k, types[i]};

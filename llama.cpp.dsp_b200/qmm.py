@@ -23,7 +23,7 @@ EXPORTS = [
     "b200_launch_count", "b200_type_supported", "b200_block_size", "b200_type_size", "b200_row_size",
     "b200_weight_alloc_size", "b200_quantize_q8_1", "b200_dequantize_f32", "b200_mul_mat_workspace_size",
     "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
-    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mmq_chunk", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
+    "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mmq_use_cached_plane", "b200_mmq_chunk", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
     "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
     "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait", "b200_rowsplit_timeout_count", "b200_copy_async", "b200_copy_mapped_async",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
@@ -104,6 +104,7 @@ def lib():
     L.b200_rowsplit_wait.argtypes = [vp, i32, vp]
     L.b200_rowsplit_timeout_count.argtypes = [C.POINTER(C.c_int), vp]
     L.b200_copy_async.argtypes = [vp, vp, sz, vp]
+    L.b200_mmq_use_cached_plane.argtypes = [i32, i64]
     L.b200_copy_mapped_async.argtypes = [vp, vp, sz, vp]
     L.b200_ipc_get_handle.argtypes = [vp, vp, C.POINTER(i64)]
     L.b200_ipc_open_handle.argtypes = [vp, i64, C.POINTER(vp)]

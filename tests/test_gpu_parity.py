@@ -677,3 +677,26 @@ def test_copy_async_kernel_and_fallback(qmm):
     qmm.check(L.b200_copy_async(C.c_void_p(dev_buf.data_ptr()), C.c_void_p(src_p.data_ptr()), 5000, None))
     torch.cuda.synchronize()
     assert torch.equal(dev_buf.cpu(), src_p) and qmm.launch_count() == b0
+
+
+@pytest.mark.gpu
+def test_small_batches_on_a_cached_plane(qmm):
+    """5..8 columns: a caller that holds a plane is told to use it for the single-plane types (b200_mmq_use_cached_plane)
+    and the result stays inside the harness bound against ggml-cpu semantics, like the GEMV's."""
+    L = qmm.lib()
+    assert L.b200_mmq_use_cached_plane(qref.Q4_K, 4) == 0 and L.b200_mmq_use_cached_plane(qref.Q4_K, 5) == 1
+    assert L.b200_mmq_use_cached_plane(qref.Q8_0, 8) == 0 and L.b200_mmq_use_cached_plane(qref.Q4_0, 8) == 0
+    assert L.b200_mmq_use_cached_plane(qref.Q8_0, 9) == 1 and L.b200_mmq_use_cached_plane(99, 9) == 0
+    rng = np.random.default_rng(11)
+    m, k = 512, 2048
+    for t in (qref.Q4_K, qref.Q6_K, qref.IQ4_XS):
+        w = qref.random_blocks(t, m, k, rng)
+        wd = dev(w)
+        plane = qmm.build_plane(t, wd, m, k)
+        for n in (5, 8):
+            x = rng.uniform(-1, 1, (n, k)).astype(np.float32)
+            want = qref.mul_mat(t, w, x, m, k)                      # ggml-cpu semantics
+            got_p = qmm.mul_mat_mmq(t, plane, dev(x), m, k).cpu().numpy()
+            got_g = qmm.mul_mat(t, wd, dev(x), m, k).cpu().numpy()
+            assert qref.nmse(got_p, want) < 5e-4 and qref.nmse(got_g, want) < 5e-4
+            assert qref.nmse(got_p, got_g) < 5e-4
