@@ -979,15 +979,15 @@ def main():
             if not pg or pg[-1][0] != key:
                 pg.append((key, k, []))
             lo, hi, _ = slices[i]
-            pg[-1][2].append((name.split(".")[0], t, hi - lo, pl))
+            pg[-1][2].append((name.split(".")[0], t, hi - lo, pl, lo))
         pcalls2 = []
         for _, k, members in pg:
-            own = [(b_, t, rows, pl) for b_, t, rows, pl in members if pl is not None and rows > 0]
+            own = [(b_, t, rows, pl) for b_, t, rows, pl, _ in members if pl is not None and rows > 0]
             call = None
             if own:
                 call = qmm.MultiMatMulMMQ([t for _, t, _, _ in own], [pl for _, _, _, pl in own], [rows for _, _, rows, _ in own], k,
                                           [opp_l[b_][:, :rows] for b_, _, rows, _ in own], npp)
-            pcalls2.append((call, xpp[k], [b_ for b_, _, _, _ in members]))
+            pcalls2.append((call, xpp[k], [b_ for b_, _, _, _, _ in members]))
 
         def prefill_step_split():
             for call, x, bs in pcalls2:
@@ -1017,6 +1017,80 @@ def main():
                 del gpp
             except Exception as e:  # noqa: BLE001
                 sys.stderr.write("pp512 row-split graph capture failed: %s\n" % str(e)[:200])
+        # ---- the fused form: GEMM and exchange in ONE kernel (b200_mul_mat_mmq_multi_rowsplit): the persistent tensor-core
+        #      kernel's epilogue stores its tiles into every rank's dst over NVLink and counts an arrival; a stream wait-value
+        #      per group replaces the collective.  Checked against the all-gathered results of the NCCL leg above.
+        nccl_pp, pp_collective = None, "dist.all_gather_into_tensor per matmul (NCCL); matmuls sharing activations in one b200_mul_mat_mmq_multi call"
+        if args.collective == "fused":
+            from llama_cpp_dsp_b200.rowsplit import MultiMatMulMMQRowSplit
+            pbase, poff = {}, 0
+            for _, (name, _, m, _) in sel:
+                b_ = name.split(".")[0]
+                if b_ not in pbase:
+                    pbase[b_] = (poff, m)
+                    poff += npp * m
+            symp = PeerBuffers(1, poff, len(pg), world, rank, dev)
+            delta = [symp.ptr_dst[r] - symp.ptr_dst[rank] for r in range(world)]
+            fcalls = []
+            for gi, (_, k, members) in enumerate(pg):
+                ty, pls, msl, dl = [], [], [], []
+                for b_, t, rows, pl, lo in members:
+                    o0, mfull = pbase[b_]
+                    full = symp.dst[0, o0:o0 + npp * mfull].view(npp, mfull)
+                    ty.append(t), pls.append(pl), msl.append(rows)
+                    dl.append(full[:, lo:lo + rows] if rows > 0 else None)
+                fcalls.append((MultiMatMulMMQRowSplit(ty, pls, msl, k, dl, npp, world, rank, delta), xpp[k], symp.ptr_sync[gi]))
+
+            def prefill_step_fused():
+                for call, x, ps in fcalls:
+                    call(x, ps)
+                    row_split_wait(ps, rank, world)
+            dist.barrier()
+            prefill_step_fused()
+            torch.cuda.synchronize()
+            dist.barrier()
+            okp = True
+            lastp = {}
+            for (i, (name, t, m, k)) in sel:
+                lastp[name.split(".")[0]] = m
+            prefill_step_split()                                  # (the NCCL leg's buffers hold the last layer's results again)
+            torch.cuda.synchronize()
+            for b_, m in lastp.items():
+                o0, _ = pbase[b_]
+                full = torch.cat([opp_f[b_][r, :, :h - l] for r, (l, h) in enumerate(splits[m].ranges)], dim=1)
+                got = symp.dst[0, o0:o0 + npp * m].view(npp, m)
+                # same integer sums and scales; the all-gather leg may add two k halves (split-K) where the fused launch
+                # never splits, so the comparison allows fp32 summation-order differences and nothing more
+                okp = okp and bool(((full - got).abs().max() <= 2e-6 * full.abs().max()).item())
+            flags = [None] * world
+            dist.all_gather_object(flags, bool(okp))
+            if all(flags):
+                ms_f_eager = timed(prefill_step_fused, 6, 2)
+                ms_f, f_launch = ms_f_eager, "eager"
+                if use_graph:
+                    try:
+                        gpf = torch.cuda.CUDAGraph()
+                        with torch.cuda.stream(stream):
+                            prefill_step_fused()
+                            stream.synchronize()
+                            dist.barrier()
+                            with torch.cuda.graph(gpf, stream=stream):
+                                prefill_step_fused()
+                        dist.barrier()
+                        ms_f_graph = timed(gpf.replay, 6, 2)
+                        if ms_f_graph < ms_f:
+                            ms_f, f_launch = ms_f_graph, "cuda_graph_replay"
+                        del gpf
+                    except Exception as e:  # noqa: BLE001
+                        sys.stderr.write("pp512 fused row-split graph capture failed: %s\n" % str(e)[:200])
+                nccl_pp = {"value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "launch": pp_launch}
+                if ms_f < ms_pp:
+                    ms_pp, pp_launch, ms_pp_eager = ms_f, f_launch, ms_f_eager
+                    pp_collective = ("fused: b200_mul_mat_mmq_multi_rowsplit (the GEMM's epilogue stores its tiles into every rank over "
+                                     "NVLink and counts an arrival) + b200_rowsplit_wait per group; checked against the all-gathered results")
+            else:
+                sys.stderr.write("pp512 fused row split: results differ from the all-gathered ones on some rank: %s\n" % flags)
+            del symp, fcalls
         flops = sum(2.0 * m * k * npp for _, (_, _, m, k) in sel)
         try:
             mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -1025,8 +1099,8 @@ def main():
             bf16_burst = 1590.0
         tops = flops / ms_pp / 1e9
         pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 6,
-              "launch": pp_launch, "ms_per_step_eager": ms_pp_eager,
-              "collective": "dist.all_gather_into_tensor per matmul (NCCL); matmuls sharing activations in one b200_mul_mat_mmq_multi call",
+              "launch": pp_launch, "ms_per_step_eager": ms_pp_eager, "nccl_all_gather_baseline": nccl_pp,
+              "collective": pp_collective,
               "all_gather_bytes_per_step_per_rank": sum(4.0 * npp * maxrows[m] * (world - 1) for _, (_, _, m, _) in sel),
               "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),
               "roofline": {"bound": "tensor", "achieved": tops, "unit": "TOP/s (int8), all GPUs", "peak": world * 2 * bf16_burst,

@@ -367,6 +367,24 @@ B200_API int b200_mul_mat_rowsplit_fused(int type, const void * W, const float *
                                          int wait_arrivals, void * workspace, size_t workspace_bytes,
                                          b200_stream_t stream);
 /*
+ * Prefill under split-mode row, GEMM and exchange in ONE kernel -- replaces ggml_cuda_op_mul_mat's row-split choreography
+ * for batches (ggml-cuda.cu:1560-1700: GEMM per device, then 2-D peer copies of the result slices).  This rank multiplies
+ * its row slices (planes[i] = b200_mmq_build_plane over its rows, m_slice[i] of them) of up to four matrices that share
+ * the activations; the persistent tensor-core kernel's epilogue stores every result element into ALL ranks' dst:
+ * dst_local[i] = this rank's copy of dst + row_low (row stride dst_row_stride[i] floats, the full m), and rank r's copy
+ * lies peer_delta[r] bytes from it (symmetric allocations mapped with b200_ipc_*; peer_delta[rank] = 0).  When its last
+ * CTA is done the launch counts ONE arrival on every rank's sync block (peer_sync as in b200_mul_mat_rowsplit_fused), so
+ * b200_rowsplit_wait(peer_sync[rank], world, stream) orders later work behind the whole dst.  All matrices of a call
+ * must belong to one precision class (K-quants and IQ4_XS / Q4_0 / Q8_0): B200_ERR_UNSUPPORTED otherwise.
+ * workspace: b200_mul_mat_mmq_workspace_size(max m_slice, n, k).
+ */
+B200_API int b200_mul_mat_mmq_multi_rowsplit(int nmat, const int * types, const void * const * planes, const float * x,
+                                             int64_t x_row_stride, float * const * dst_local,
+                                             const int64_t * dst_row_stride, const int64_t * m_slice, int64_t n, int64_t k,
+                                             int world, int rank, const int64_t * peer_delta,
+                                             int32_t * const * peer_sync, void * workspace, size_t workspace_bytes,
+                                             b200_stream_t stream);
+/*
  * Stream-ordered copy of `bytes` between device memory and host memory (either direction, or device to device) --
  * what ggml_backend_cuda_set_tensor_async / _get_tensor_async do with cudaMemcpyAsync (ggml-cuda.cu:2374-2405).  When the
  * host side is pinned (mapped under UVA) and the copy is small (<= B200_COPY_KERNEL_MAX, default 1 MiB) a copy KERNEL does

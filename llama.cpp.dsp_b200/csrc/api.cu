@@ -866,6 +866,61 @@ int b200_mul_mat_rowsplit_fused(int type, const void * W, const float * x, int64
     return launch_gemv(g, stream);
 }
 
+// Prefill under split-mode row: this rank's row slices of up to four matrices that share the activations, ONE persistent
+// tensor-core launch whose epilogue stores every result element into all ranks' dst (peer_delta) and counts one arrival on
+// every rank's sync block -- GEMM and exchange in one kernel instead of GEMM + all-gather.
+int b200_mul_mat_mmq_multi_rowsplit(int nmat, const int * types, const void * const * planes, const float * x, int64_t x_row_stride,
+                                    float * const * dst_local, const int64_t * dst_row_stride, const int64_t * m_slice, int64_t n,
+                                    int64_t k, int world, int rank, const int64_t * peer_delta, int32_t * const * peer_sync,
+                                    void * workspace, size_t workspace_bytes, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (nmat < 1 || nmat > 4 || !types || !planes || !dst_local || !dst_row_stride || !m_slice) return B200_ERR_SHAPE;
+    if (world < 1 || world > 16 || rank < 0 || rank >= world || !peer_delta || !peer_sync) return B200_ERR_SHAPE;
+    if (n < 1 || k <= 0 || x_row_stride < k || n > INT32_MAX || k > INT32_MAX) return B200_ERR_SHAPE;
+    for (int r = 0; r < world; r++)
+        if (!peer_sync[r] || (uintptr_t) peer_sync[r] % 8 != 0 || peer_delta[r] % 4 != 0) return B200_ERR_ALIGNMENT;
+    if (peer_delta[rank] != 0) return B200_ERR_SHAPE;
+    const void * pl[4];
+    float *      ds[4];
+    int64_t      st_[4], ms[4];
+    int cnt = 0, cls_type = 0;
+    for (int i = 0; i < nmat; i++) {
+        if (!weight_type(types[i])) return B200_ERR_TYPE;
+        if (m_slice[i] < 0 || m_slice[i] > INT32_MAX || dst_row_stride[i] < m_slice[i]) return B200_ERR_SHAPE;
+        if (m_slice[i] == 0) continue;
+        if (!planes[i] || (uintptr_t) planes[i] % 256 != 0 || !dst_local[i] || (uintptr_t) dst_local[i] % 4 != 0) return B200_ERR_ALIGNMENT;
+        if (cnt && mmq_nplanes(types[i]) * 4 + mmq_xplanes(types[i]) != mmq_nplanes(cls_type) * 4 + mmq_xplanes(cls_type))
+            return B200_ERR_UNSUPPORTED;                          // one launch = one arrival: one precision class per call
+        cls_type = types[i];
+        pl[cnt] = planes[i], ds[cnt] = dst_local[i], st_[cnt] = dst_row_stride[i], ms[cnt] = m_slice[i], cnt++;
+    }
+    if (cnt == 0) {   // this rank owns no rows of the group: the peers still count its arrival
+        rowsplit_signal_args sa = {};
+        sa.world = world;
+        for (int r = 0; r < world; r++) sa.flag[r] = peer_sync[r];
+        k_rowsplit_signal<<<1, 32, 0, stream>>>(sa);
+        B200_CUDA_TRY(cudaGetLastError());
+        note_launch();
+        return B200_OK;
+    }
+    if (!workspace || workspace_bytes < mmq_workspace_bytes(n, k)) return B200_ERR_WORKSPACE;
+    if ((uintptr_t) workspace % 256 != 0) return B200_ERR_ALIGNMENT;
+    mmq_rowsplit rs = {};
+    rs.world = world, rs.rank = rank, rs.local_count = peer_sync[rank] + 1;
+    for (int r = 0; r < world; r++) rs.peer_delta[r] = (long long) peer_delta[r], rs.peer_flag[r] = peer_sync[r];
+    if (world == 1) {   // degenerate: a local matmul plus the arrival
+        int st = launch_mmq_multi(cls_type, cnt, pl, x, x_row_stride, ds, st_, ms, n, k, workspace, stream, nullptr);
+        if (st != B200_OK) return st;
+        rowsplit_signal_args sa = {};
+        sa.world = 1, sa.flag[0] = peer_sync[0];
+        k_rowsplit_signal<<<1, 32, 0, stream>>>(sa);
+        B200_CUDA_TRY(cudaGetLastError());
+        note_launch();
+        return B200_OK;
+    }
+    return launch_mmq_multi(cls_type, cnt, pl, x, x_row_stride, ds, st_, ms, n, k, workspace, stream, &rs);
+}
+
 size_t b200_mul_mat_rowsplit_workspace_size(int type, int64_t n, int64_t k) {
     if (!weight_type(type) || n <= 0 || k <= 0) return 0;
     return (size_t) n * q8_soa_layout(k).bytes;

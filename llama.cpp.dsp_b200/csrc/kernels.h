@@ -83,11 +83,19 @@ int    mmq_chunk();   // elements of k per scale (build-time: 256 or 512)
 size_t mmq_workspace_bytes(int64_t n, int64_t k);
 int    launch_plane_build(int type, const void * W, int64_t w_stride, void * plane, int64_t m, int64_t k,
                           cudaStream_t stream);
+// split-mode row for the tensor-core path: where the peers' copies of dst are and how the launch reports completion
+struct mmq_rowsplit {
+    int       world, rank;
+    long long peer_delta[16];   // bytes from this rank's symmetric dst allocation to rank r's, as mapped here ([rank] = 0)
+    int32_t * peer_flag[16];    // every rank's arrival counter
+    int32_t * local_count;      // this rank's CTA counter (its sync block + 1)
+};
 // several matrices of one precision class (mmq_nplanes, mmq_xplanes of `type`) and one k against the same activations:
-// one activation quantizer, shared GEMM launches
+// one activation quantizer, shared GEMM launches.  rs != null: the row-split form (<= 4 matrices, one persistent launch
+// whose epilogue stores into every rank and counts one arrival)
 int    launch_mmq_multi(int type, int nmat, const void * const * planes, const float * x, int64_t x_stride,
                         float * const * dst, const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k,
-                        void * workspace, cudaStream_t stream);
+                        void * workspace, cudaStream_t stream, const mmq_rowsplit * rs = nullptr);
 int    launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                   int64_t n, int64_t k, void * workspace, cudaStream_t stream);
 

@@ -739,6 +739,13 @@ struct mmq_pargs {
     const int32_t * sorted;
     int             n_used, mt_expert, m_expert;
     int64_t         dst_token_stride, dst_slot_stride;
+    // split-mode row (world > 1): every result element is stored at the same offset of every rank's symmetric dst allocation
+    // (peer_delta[r] bytes from this rank's, NVLink-mapped; [rank] = 0) straight from the epilogue, and the launch counts one
+    // ARRIVAL on every rank's sync block when all its CTAs are done (the protocol of the row-split GEMV, mmvq.cu)
+    int             world, rank;
+    long long       peer_delta[16];
+    int32_t *       peer_flag[16];
+    int32_t *       local_count;
 };
 struct mmq_pshape {
     static constexpr int NS      = 4;
@@ -997,10 +1004,21 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
             if (row < mrows) {
                 const int jn = min(ncw, a.n - (I.n0 + col0));    // columns of this warp inside the matrix
                 float *   d  = dstp + (int64_t) (I.n0 + col0) * dstride + row;
+                if (p.world > 1) {
+                    for (int r = 0; r < p.world; r++) {          // 128-byte warp stores, local or over NVLink
+                        float * dr = reinterpret_cast<float *>(reinterpret_cast<char *>(d) + p.peer_delta[r]);
 #pragma unroll
-                for (int i = 0; i < 64; i++) {                   // lanes = consecutive rows: coalesced
-                    if (i < jn) *d = acc[i];
-                    d += dstride;
+                        for (int i = 0; i < 64; i++) {
+                            if (i < jn) *dr = acc[i];
+                            dr += dstride;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 64; i++) {               // lanes = consecutive rows: coalesced
+                        if (i < jn) *d = acc[i];
+                        d += dstride;
+                    }
                 }
             }
 #ifdef B200_MMQ_TRACE
@@ -1020,6 +1038,18 @@ __global__ void __launch_bounds__(mmq_pshape::THREADS, 1) k_mmq_p(const __grid_c
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc<512>(tmem);
+    if (!MMID && p.world > 1 && threadIdx.x == 0) {
+        // the barrier ordered every warp's result stores before this thread: one system-scope fence publishes them, then
+        // the CTA counts itself on every rank; the last CTA of the grid tops the launch up to B200_ARRIVAL_UNIT
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        int add = 1;
+        if (atomicAdd(p.local_count, 1) == (int) gridDim.x - 1) {
+            atomicExch(p.local_count, 0);
+            add += B200_ARRIVAL_UNIT - (int) gridDim.x;
+        }
+        for (int r = 0; r < p.world; r++)
+            asm volatile("red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(p.peer_flag[r]), "r"(add) : "memory");
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -1127,7 +1157,8 @@ static int launch_mmq_bn(const CUtensorMap & mapA, const CUtensorMap & mapB, con
 
 // persistent launch: items = 128 x 256 tiles (+ 128 x 128 halves for a short last round), one CTA per SM
 static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & mapB128, const mmq_kargs & a,
-                                 const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream) {
+                                 const mmq_maps3 & mapAx, int mtiles, int sm_count, cudaStream_t stream,
+                                 const mmq_rowsplit * rs = nullptr) {
     // B200_MMQ_TMEM_BIAS=0: the epilogue that adds the conversion bias itself (EPI 2) instead of finding it in TMEM (EPI 3)
     const bool bias  = MMQ_PEPI_DEFAULT == 3 && env_flag("B200_MMQ_TMEM_BIAS", 1);
     auto kern3 = k_mmq_p<MMQ_PEPI_DEFAULT, false>;
@@ -1136,6 +1167,11 @@ static int launch_mmq_persistent(const CUtensorMap & mapA, const CUtensorMap & m
     B200_SMEM_ATTR_ONCE(kern2, mmq_pshape::SMEM);
     auto kern = bias ? kern3 : kern2;
     mmq_pargs p = {};
+    p.world = 1;
+    if (rs && rs->world > 1) {
+        p.world = rs->world, p.rank = rs->rank, p.local_count = rs->local_count;
+        for (int r = 0; r < rs->world; r++) p.peer_delta[r] = rs->peer_delta[r], p.peer_flag[r] = rs->peer_flag[r];
+    }
     p.ntn = (a.n + 255) / 256;
     p.mtiles = mtiles;
     p.raster = env_flag("B200_MMQ_RASTER", 0);
@@ -1198,8 +1234,9 @@ static int mmq_ksplit(int64_t tiles, int64_t nvc, int sm_count, bool allowed) {
 // launch's fixed costs are paid once per group.
 int launch_mmq_multi(int type, int nmat, const void * const * planes, const float * x, int64_t x_stride, float * const * dst,
                      const int64_t * dst_stride, const int64_t * m, int64_t n, int64_t k, void * workspace,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, const mmq_rowsplit * rs) {
     if (nmat == 0 || n == 0) return B200_OK;
+    if (rs && (nmat > 4 || MMQ_KC > 256)) return B200_ERR_UNSUPPORTED;   // row split: ONE persistent launch = one arrival
     const int sm_count = sm_count_current_device();
     if (!sm_count) return B200_ERR_CUDA;
     const int     nwp = mmq_nplanes(type), nxp = mmq_xplanes(type);
@@ -1218,8 +1255,8 @@ int launch_mmq_multi(int type, int nmat, const void * const * planes, const floa
     }
     // tile width: 256 columns (the tensor core takes ~120 clocks per instruction whether N is 128 or 256, see
     // profiles/r01/mmq_trace_v1.log) unless n is small; shapes with few tiles split the virtual k in two instead
-    const int bn     = env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
-    const int ksplit = mmq_ksplit(total_mt * ((n + bn - 1) / bn), nseg * nch, sm_count, can_split);
+    const int bn     = rs ? 256 : env_flag("B200_MMQ_BN", 0) > 0 ? env_flag("B200_MMQ_BN", 0) : (n <= 128 ? 128 : 256);
+    const int ksplit = rs ? 1 : mmq_ksplit(total_mt * ((n + bn - 1) / bn), nseg * nch, sm_count, can_split);
     {
         mmq_zero z = {};
         if (ksplit > 1)
@@ -1227,7 +1264,7 @@ int launch_mmq_multi(int type, int nmat, const void * const * planes, const floa
         const int st = launch_quantize_x8(nxp, x, x_stride, Q, Tt, n, k, kp, npad, z, stream);
         if (st != B200_OK) return st;
     }
-    const bool persist = ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1);
+    const bool persist = rs || (ksplit == 1 && bn == 256 && env_flag("B200_MMQ_PERSIST", 1));
     CUtensorMap mapB;
     int st = make_map(&mapB, Q, n, nxp * kp, persist ? 128 : bn);
     if (st != B200_OK) return st;
@@ -1255,7 +1292,7 @@ int launch_mmq_multi(int type, int nmat, const void * const * planes, const floa
             tiles += (int) ((mj + MMQ_BM - 1) / MMQ_BM);
         }
         if (tiles == 0) continue;
-        st = persist ? launch_mmq_persistent(mapA, mapB, a, mx, tiles, sm_count, stream)
+        st = persist ? launch_mmq_persistent(mapA, mapB, a, mx, tiles, sm_count, stream, rs)
            : bn == 256 ? launch_mmq_bn<256>(mapA, mapB, a, mx, tiles, stream)
                        : launch_mmq_bn<128>(mapA, mapB, a, mx, tiles, stream);
         if (st != B200_OK) return st;
@@ -1265,7 +1302,7 @@ int launch_mmq_multi(int type, int nmat, const void * const * planes, const floa
 
 int launch_mmq(int type, const void * plane, const float * x, int64_t x_stride, float * dst, int64_t dst_stride, int64_t m,
                int64_t n, int64_t k, void * workspace, cudaStream_t stream) {
-    return launch_mmq_multi(type, 1, &plane, x, x_stride, &dst, &dst_stride, &m, n, k, workspace, stream);
+    return launch_mmq_multi(type, 1, &plane, x, x_stride, &dst, &dst_stride, &m, n, k, workspace, stream, nullptr);
 }
 
 // ------------------------------------------------------------------------------------------------ MUL_MAT_ID on tensor cores

@@ -130,6 +130,34 @@ def mul_mat_row_split_fused(t, w_local, x, split, k, ptr_dst, ptr_sync, dst_row_
         qmm._stream_ptr(stream)))
 
 
+class MultiMatMulMMQRowSplit:
+    """Prepared arguments of b200_mul_mat_mmq_multi_rowsplit: this rank's row slices (prefill planes) of up to four matrices
+    that share the activations; the GEMM's epilogue stores the results into every rank's dst and counts one arrival.
+    dsts_local[i]: this rank's [n, rows_i] view of its own full dst (row stride = the full m); peer_delta: bytes from this
+    rank's symmetric allocation to rank r's."""
+
+    def __init__(self, types, planes, m_slices, k, dsts_local, n, world, rank, peer_delta):
+        import ctypes as C
+        nmat = len(types)
+        self.keep = (list(planes), list(dsts_local))
+        self.nmat, self.k, self.n, self.world, self.rank = nmat, k, n, world, rank
+        self.types = (C.c_int * nmat)(*types)
+        self.P = (C.c_void_p * nmat)(*[p.data_ptr() if p is not None else 0 for p in planes])
+        self.dst = (C.c_void_p * nmat)(*[d.data_ptr() if d is not None else 0 for d in dsts_local])
+        self.dstride = (C.c_int64 * nmat)(*[d.stride(0) if d is not None else 0 for d in dsts_local])
+        self.m = (C.c_int64 * nmat)(*m_slices)
+        self.delta = (C.c_int64 * world)(*peer_delta)
+        self.ws_bytes = qmm.lib().b200_mul_mat_mmq_workspace_size(max(max(m_slices), 1), n, k)
+        self.device = next(d for d in dsts_local if d is not None).device if any(d is not None for d in dsts_local) else None
+
+    def __call__(self, x, ptr_sync, stream=None):
+        import ctypes as C
+        ws, wsz = qmm._workspace(x.device, self.ws_bytes)
+        qmm.check(qmm.lib().b200_mul_mat_mmq_multi_rowsplit(
+            self.nmat, self.types, self.P, C.c_void_p(x.data_ptr()), x.stride(0), self.dst, self.dstride, self.m, self.n, self.k,
+            self.world, self.rank, self.delta, ptr_sync, ws, wsz, qmm._stream_ptr(stream)))
+
+
 def row_split_wait(ptr_sync, rank, world, stream=None, calls=1):
     """stream-ordered wait until the slices of all `world` ranks (x `calls` fused calls sharing the block) have landed
     in this rank's dst; re-arms the counter"""

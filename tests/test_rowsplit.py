@@ -196,3 +196,50 @@ def test_fused_row_split_groups_share_a_sync_block_one_device():
     for r in range(world):
         assert torch.equal(dsts[r], wants[1]), r     # the last group had 2 calls: weights index 1 wrote last
         assert int(syncs[r].abs().sum()) == 0
+
+
+@pytest.mark.gpu
+def test_fused_row_split_prefill_one_device():
+    """b200_mul_mat_mmq_multi_rowsplit with ONE device playing every rank (peer_delta between two dst buffers in one
+    allocation): each "rank" multiplies its row slices of q/k/v on the tensor cores, the epilogue stores them into both
+    copies, one arrival per rank; both copies must equal the unsplit b200_mul_mat_mmq result bit for bit."""
+    import ctypes as C
+    qmm = b200pkg.load()
+    from llama_cpp_dsp_b200.rowsplit import MultiMatMulMMQRowSplit, row_split_wait
+    rng = np.random.default_rng(21)
+    world, n, k = 2, 160, 1024
+    mats = [(qref.Q4_K, 1280), (qref.Q6_K, 256), (qref.Q4_K, 384)]
+    ws_ = [torch.from_numpy(qref.random_blocks(t, m, k, rng)).cuda() for t, m in mats]
+    x = torch.from_numpy(rng.uniform(-1, 1, (n, k)).astype(np.float32)).cuda()
+    # the row-split launch never splits k (one launch = one arrival), so the unsplit reference must not either: the two-half
+    # split-K adds its halves with red.add -- the same value up to fp32 summation order, not the same bits
+    qmm.setenv(B200_MMQ_KSPLIT=1)
+    try:
+        want = [qmm.mul_mat_mmq(t, qmm.build_plane(t, w, m, k), x, m, k) for (t, m), w in zip(mats, ws_)]
+        torch.cuda.synchronize()
+    finally:
+        qmm.setenv(B200_MMQ_KSPLIT=None)
+    total = sum(n * m for _, m in mats)
+    sym = torch.full((world, total), float("nan"), device="cuda")           # rank r's "symmetric allocation" = row r
+    syncs = torch.zeros((world, 2), dtype=torch.int32, device="cuda")
+    ptr_sync = (C.c_void_p * world)(*[syncs[r].data_ptr() for r in range(world)])
+    for rank in range(world):
+        delta = [(r - rank) * total * 4 for r in range(world)]
+        planes, msl, dl, off = [], [], [], 0
+        for (t, m), w in zip(mats, ws_):
+            lo, hi = qmm.row_split(m, world, rank)
+            planes.append(qmm.build_plane(t, w[lo:hi].contiguous(), hi - lo, k) if hi > lo else None)
+            msl.append(hi - lo)
+            full = sym[rank, off:off + n * m].view(n, m)
+            dl.append(full[:, lo:hi] if hi > lo else None)
+            off += n * m
+        MultiMatMulMMQRowSplit([t for t, _ in mats], planes, msl, k, dl, n, world, rank, delta)(x, ptr_sync)
+    for rank in range(world):
+        row_split_wait(ptr_sync, rank, world)
+    torch.cuda.synchronize()
+    assert int(syncs.abs().sum()) == 0
+    off = 0
+    for (t, m), w_ in zip(mats, want):
+        for rank in range(world):
+            assert torch.equal(sym[rank, off:off + n * m].view(n, m), w_), (m, rank)
+        off += n * m
