@@ -1020,6 +1020,7 @@ def main():
         # ---- the fused form: GEMM and exchange in ONE kernel (b200_mul_mat_mmq_multi_rowsplit): the persistent tensor-core
         #      kernel's epilogue stores its tiles into every rank's dst over NVLink and counts an arrival; a stream wait-value
         #      per group replaces the collective.  Checked against the all-gathered results of the NCCL leg above.
+        fused_pp = None
         nccl_pp, pp_collective = None, "dist.all_gather_into_tensor per matmul (NCCL); matmuls sharing activations in one b200_mul_mat_mmq_multi call"
         if args.collective == "fused":
             from llama_cpp_dsp_b200.rowsplit import MultiMatMulMMQRowSplit
@@ -1084,6 +1085,8 @@ def main():
                     except Exception as e:  # noqa: BLE001
                         sys.stderr.write("pp512 fused row-split graph capture failed: %s\n" % str(e)[:200])
                 nccl_pp = {"value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "launch": pp_launch}
+                fused_pp = {"value": npp * 1e3 / ms_f, "unit": "tok/s", "ms_per_step": ms_f, "launch": f_launch,
+                            "api": "b200_mul_mat_mmq_multi_rowsplit + b200_rowsplit_wait per group (GEMM epilogue stores into every rank)"}
                 if ms_f < ms_pp:
                     ms_pp, pp_launch, ms_pp_eager = ms_f, f_launch, ms_f_eager
                     pp_collective = ("fused: b200_mul_mat_mmq_multi_rowsplit (the GEMM's epilogue stores its tiles into every rank over "
@@ -1100,6 +1103,7 @@ def main():
         tops = flops / ms_pp / 1e9
         pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 6,
               "launch": pp_launch, "ms_per_step_eager": ms_pp_eager, "nccl_all_gather_baseline": nccl_pp,
+              "fused_peer_store": fused_pp,
               "collective": pp_collective,
               "all_gather_bytes_per_step_per_rank": sum(4.0 * npp * maxrows[m] * (world - 1) for _, (_, _, m, _) in sel),
               "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),
