@@ -1023,7 +1023,7 @@ def main():
         fused_pp = None
         nccl_pp, pp_collective = None, "dist.all_gather_into_tensor per matmul (NCCL); matmuls sharing activations in one b200_mul_mat_mmq_multi call"
         if args.collective == "fused":
-            from llama_cpp_dsp_b200.rowsplit import MultiMatMulMMQRowSplit
+            from llama_cpp_dsp_b200.rowsplit import MultiMatMulMMQRowSplit, RowSplitPush, row_split_push_join
             pbase, poff = {}, 0
             for _, (name, _, m, _) in sel:
                 b_ = name.split(".")[0]
@@ -1032,7 +1032,7 @@ def main():
                     poff += npp * m
             symp = PeerBuffers(1, poff, len(pg), world, rank, dev)
             delta = [symp.ptr_dst[r] - symp.ptr_dst[rank] for r in range(world)]
-            fcalls = []
+            fcalls, ccalls = [], []
             for gi, (_, k, members) in enumerate(pg):
                 ty, pls, msl, dl = [], [], [], []
                 for b_, t, rows, pl, lo in members:
@@ -1041,11 +1041,25 @@ def main():
                     ty.append(t), pls.append(pl), msl.append(rows)
                     dl.append(full[:, lo:lo + rows] if rows > 0 else None)
                 fcalls.append((MultiMatMulMMQRowSplit(ty, pls, msl, k, dl, npp, world, rank, delta), xpp[k], symp.ptr_sync[gi]))
+                own = [j for j in range(len(ty)) if msl[j] > 0 and pls[j] is not None]
+                lcall = qmm.MultiMatMulMMQ([ty[j] for j in own], [pls[j] for j in own], [msl[j] for j in own], k,
+                                           [dl[j] for j in own], npp) if own else None
+                ccalls.append((lcall, RowSplitPush([dl[j] for j in own], npp, world, rank, delta), xpp[k], symp.ptr_sync[gi]))
 
             def prefill_step_fused():
                 for call, x, ps in fcalls:
                     call(x, ps)
                     row_split_wait(ps, rank, world)
+
+            # the reference's own form, one process per GPU: local GEMM, then the slices go to the peers through the copy
+            # engines (b200_rowsplit_push: cudaMemcpy2DAsync per peer on side streams + arrival counters)
+            def prefill_step_copy_engines():
+                for lcall, push, x, ps in ccalls:
+                    if lcall is not None:
+                        lcall(x)
+                    push(ps)
+                    row_split_wait(ps, rank, world)
+                row_split_push_join()
             dist.barrier()
             prefill_step_fused()
             torch.cuda.synchronize()
@@ -1084,16 +1098,41 @@ def main():
                         del gpf
                     except Exception as e:  # noqa: BLE001
                         sys.stderr.write("pp512 fused row-split graph capture failed: %s\n" % str(e)[:200])
+                # copy-engine form: checked the same way, timed eagerly (side streams)
+                ce_pp = None
+                symp.dst.zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                prefill_step_copy_engines()
+                torch.cuda.synchronize()
+                dist.barrier()
+                okc = True
+                for b_, m in lastp.items():
+                    o0, _ = pbase[b_]
+                    full = torch.cat([opp_f[b_][r, :, :h - l] for r, (l, h) in enumerate(splits[m].ranges)], dim=1)
+                    got = symp.dst[0, o0:o0 + npp * m].view(npp, m)
+                    okc = okc and bool(((full - got).abs().max() <= 2e-6 * full.abs().max()).item())
+                dist.all_gather_object(flags, bool(okc))
+                if all(flags):
+                    ms_c = timed(prefill_step_copy_engines, 6, 2)
+                    ce_pp = {"value": npp * 1e3 / ms_c, "unit": "tok/s", "ms_per_step": ms_c, "launch": "eager",
+                             "api": "b200_mul_mat_mmq_multi (local slices) + b200_rowsplit_push (cudaMemcpy2DAsync to every peer on side "
+                                    "streams, arrival counters) + b200_rowsplit_wait per group"}
+                else:
+                    sys.stderr.write("pp512 copy-engine row split: results differ on some rank: %s\n" % flags)
                 nccl_pp = {"value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "launch": pp_launch}
                 fused_pp = {"value": npp * 1e3 / ms_f, "unit": "tok/s", "ms_per_step": ms_f, "launch": f_launch,
                             "api": "b200_mul_mat_mmq_multi_rowsplit + b200_rowsplit_wait per group (GEMM epilogue stores into every rank)"}
-                if ms_f < ms_pp:
+                if ce_pp and ce_pp["ms_per_step"] < min(ms_f, ms_pp):
+                    ms_pp, pp_launch, ms_pp_eager = ce_pp["ms_per_step"], "eager", ce_pp["ms_per_step"]
+                    pp_collective = "copy engines: local GEMM + b200_rowsplit_push + b200_rowsplit_wait per group"
+                elif ms_f < ms_pp:
                     ms_pp, pp_launch, ms_pp_eager = ms_f, f_launch, ms_f_eager
                     pp_collective = ("fused: b200_mul_mat_mmq_multi_rowsplit (the GEMM's epilogue stores its tiles into every rank over "
                                      "NVLink and counts an arrival) + b200_rowsplit_wait per group; checked against the all-gathered results")
             else:
                 sys.stderr.write("pp512 fused row split: results differ from the all-gathered ones on some rank: %s\n" % flags)
-            del symp, fcalls
+            del symp, fcalls, ccalls
         flops = sum(2.0 * m * k * npp for _, (_, _, m, k) in sel)
         try:
             mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -1103,7 +1142,7 @@ def main():
         tops = flops / ms_pp / 1e9
         pp = {"metric": "pp512 tok/s", "value": npp * 1e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "steps": 6,
               "launch": pp_launch, "ms_per_step_eager": ms_pp_eager, "nccl_all_gather_baseline": nccl_pp,
-              "fused_peer_store": fused_pp,
+              "fused_peer_store": fused_pp, "copy_engine_push": ce_pp if fused_pp else None,
               "collective": pp_collective,
               "all_gather_bytes_per_step_per_rank": sum(4.0 * npp * maxrows[m] * (world - 1) for _, (_, _, m, _) in sel),
               "scale_chunk_k": int(qmm.lib().b200_mmq_chunk()),

@@ -385,6 +385,21 @@ B200_API int b200_mul_mat_mmq_multi_rowsplit(int nmat, const int * types, const 
                                              int32_t * const * peer_sync, void * workspace, size_t workspace_bytes,
                                              b200_stream_t stream);
 /*
+ * The same exchange by the COPY ENGINES -- the reference's own way (cudaMemcpy2DAsync peer copies per device,
+ * ggml-cuda.cu:1626-1691), from one process per GPU: after a local batched matmul has written this rank's row slices
+ * (src_local[i] = its copy of dst + row_low, `cols[i]` result rows wide, `n` tokens high, row stride row_stride[i] floats),
+ * b200_rowsplit_push copies every slice to the same place in every peer's dst (peer_delta) on one side stream per peer,
+ * counts this rank's arrival on each rank's sync block behind the copies, and returns; b200_rowsplit_wait(peer_sync[rank],
+ * world, stream) orders later work behind the whole dst as usual.  At most one group of pushes per peer is in flight: the
+ * next push (or b200_rowsplit_push_join) makes `stream` wait for the previous one -- call the join before the slices are
+ * overwritten and before ending a stream capture.  Bytes leave the SMs untouched; measured against the fused epilogue
+ * stores in DESIGN.md 7.
+ */
+B200_API int b200_rowsplit_push(int nmat, float * const * src_local, const int64_t * row_stride, const int64_t * cols,
+                                int64_t n, int world, int rank, const int64_t * peer_delta,
+                                int32_t * const * peer_sync, b200_stream_t stream);
+B200_API int b200_rowsplit_push_join(b200_stream_t stream);
+/*
  * Stream-ordered copy of `bytes` between device memory and host memory (either direction, or device to device) --
  * what ggml_backend_cuda_set_tensor_async / _get_tensor_async do with cudaMemcpyAsync (ggml-cuda.cu:2374-2405).  When the
  * host side is pinned (mapped under UVA) and the copy is small (<= B200_COPY_KERNEL_MAX, default 1 MiB) a copy KERNEL does

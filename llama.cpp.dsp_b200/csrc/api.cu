@@ -948,6 +948,78 @@ int b200_rowsplit_wait(int32_t * sync_local, int arrivals, b200_stream_t stream)
     return B200_OK;
 }
 
+// ---- result slices pushed to the peers by the COPY ENGINES (prefill under row split): what the reference does with
+// cudaMemcpy2DAsync peer copies per device (ggml-cuda.cu:1626-1691), here from one process per GPU into IPC-mapped peers,
+// one side stream per peer so that the copies to different ranks run on different engines, arrivals counted like the fused
+// kernels do.  Per-device side streams / events are created on first use and live until the process ends.
+struct push_state {
+    cudaStream_t side[16] = {};
+    cudaEvent_t  fork = nullptr, done[16] = {};
+    bool         pending[16] = {};
+};
+static push_state g_push[MAX_DEVICES];
+
+static int push_state_get(push_state *& ps, int world) {
+    const int dev = current_device();
+    if (dev < 0 || dev >= MAX_DEVICES) return B200_ERR_CUDA;
+    ps = &g_push[dev];
+    if (!ps->fork) B200_CUDA_TRY(cudaEventCreateWithFlags(&ps->fork, cudaEventDisableTiming));
+    for (int r = 0; r < world; r++) {
+        if (!ps->side[r]) B200_CUDA_TRY(cudaStreamCreateWithFlags(&ps->side[r], cudaStreamNonBlocking));
+        if (!ps->done[r]) B200_CUDA_TRY(cudaEventCreateWithFlags(&ps->done[r], cudaEventDisableTiming));
+    }
+    return B200_OK;
+}
+
+int b200_rowsplit_push_join(b200_stream_t stream_) {
+    push_state * ps = nullptr;
+    int st = push_state_get(ps, 0);
+    if (st != B200_OK) return st;
+    for (int r = 0; r < 16; r++)
+        if (ps->pending[r]) {
+            B200_CUDA_TRY(cudaStreamWaitEvent((cudaStream_t) stream_, ps->done[r], 0));
+            ps->pending[r] = false;
+        }
+    return B200_OK;
+}
+
+int b200_rowsplit_push(int nmat, float * const * src_local, const int64_t * row_stride, const int64_t * cols, int64_t n, int world,
+                       int rank, const int64_t * peer_delta, int32_t * const * peer_sync, b200_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t) stream_;
+    if (nmat < 0 || world < 1 || world > 16 || rank < 0 || rank >= world || !peer_delta || !peer_sync || n < 0) return B200_ERR_SHAPE;
+    if (nmat > 0 && (!src_local || !row_stride || !cols)) return B200_ERR_SHAPE;
+    for (int r = 0; r < world; r++)
+        if (!peer_sync[r]) return B200_ERR_ALIGNMENT;
+    push_state * ps = nullptr;
+    int st = push_state_get(ps, world);
+    if (st != B200_OK) return st;
+    st = b200_rowsplit_push_join(stream_);                      // at most one group of pushes in flight per peer
+    if (st != B200_OK) return st;
+    B200_CUDA_TRY(cudaEventRecord(ps->fork, stream));           // the slices are complete from here on
+    for (int r = 0; r < world; r++) {
+        cudaStream_t s = r == rank ? stream : ps->side[r];
+        if (r != rank) {
+            B200_CUDA_TRY(cudaStreamWaitEvent(s, ps->fork, 0));
+            for (int i = 0; i < nmat; i++) {
+                if (cols[i] <= 0 || n == 0) continue;
+                if (!src_local[i] || row_stride[i] < cols[i]) return B200_ERR_SHAPE;
+                B200_CUDA_TRY(cudaMemcpy2DAsync((char *) src_local[i] + peer_delta[r], (size_t) row_stride[i] * 4, src_local[i],
+                                                (size_t) row_stride[i] * 4, (size_t) cols[i] * 4, (size_t) n, cudaMemcpyDefault, s));
+            }
+        }
+        rowsplit_signal_args sa = {};                           // this rank's arrival on rank r, behind its copies to r
+        sa.world = 1, sa.flag[0] = peer_sync[r];
+        k_rowsplit_signal<<<1, 32, 0, s>>>(sa);
+        B200_CUDA_TRY(cudaGetLastError());
+        note_launch();
+        if (r != rank) {
+            B200_CUDA_TRY(cudaEventRecord(ps->done[r], s));
+            ps->pending[r] = true;
+        }
+    }
+    return B200_OK;
+}
+
 int b200_rowsplit_timeout_count(int * count, b200_stream_t stream) {
     if (!count) return B200_ERR_SHAPE;
     return rowsplit_timeouts_fetch(count, (cudaStream_t) stream);

@@ -25,7 +25,7 @@ EXPORTS = [
     "b200_mul_mat", "b200_mul_mat_multi_workspace_size", "b200_mul_mat_multi", "b200_mmq_plane_size", "b200_mmq_build_plane", "b200_mul_mat_mmq_workspace_size",
     "b200_mul_mat_mmq", "b200_mul_mat_mmq_multi", "b200_mmq_min_batch", "b200_mmq_use_cached_plane", "b200_mmq_chunk", "b200_mul_mat_host_workspace_size", "b200_mul_mat_host",
     "b200_mul_mat_multi_host_workspace_size", "b200_mul_mat_multi_host", "b200_mul_mat_id_workspace_size", "b200_mul_mat_id", "b200_row_split",
-    "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait", "b200_rowsplit_timeout_count", "b200_copy_async", "b200_copy_mapped_async", "b200_mul_mat_mmq_multi_rowsplit",
+    "b200_mul_mat_rowsplit_workspace_size", "b200_mul_mat_rowsplit_fused", "b200_rowsplit_wait", "b200_rowsplit_timeout_count", "b200_copy_async", "b200_copy_mapped_async", "b200_mul_mat_mmq_multi_rowsplit", "b200_rowsplit_push", "b200_rowsplit_push_join",
     "b200_ipc_get_handle", "b200_ipc_open_handle", "b200_ipc_close_handle", "b200_reload_env", "b200_debug_gemv_trace",
     "b200_noalloc_scratch_size", "b200_mul_mat_noalloc",
     "b200_sequence_plan_size", "b200_sequence_plan_build", "b200_sequence_run", "b200_sequence_status",
@@ -105,6 +105,8 @@ def lib():
     L.b200_rowsplit_timeout_count.argtypes = [C.POINTER(C.c_int), vp]
     L.b200_copy_async.argtypes = [vp, vp, sz, vp]
     L.b200_mmq_use_cached_plane.argtypes = [i32, i64]
+    L.b200_rowsplit_push.argtypes = [i32, vp, vp, vp, i64, i32, i32, vp, vp, vp]
+    L.b200_rowsplit_push_join.argtypes = [vp]
     L.b200_mul_mat_mmq_multi_rowsplit.argtypes = [i32, vp, vp, vp, i64, vp, vp, vp, i64, i64, i32, i32, vp, vp, vp, sz, vp]
     L.b200_copy_mapped_async.argtypes = [vp, vp, sz, vp]
     L.b200_ipc_get_handle.argtypes = [vp, vp, C.POINTER(i64)]

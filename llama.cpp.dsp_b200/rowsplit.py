@@ -158,6 +158,29 @@ class MultiMatMulMMQRowSplit:
             self.world, self.rank, self.delta, ptr_sync, ws, wsz, qmm._stream_ptr(stream)))
 
 
+class RowSplitPush:
+    """Prepared arguments of b200_rowsplit_push: this rank's result slices (views [n, rows_i] of its own full dst) go to the
+    same place in every peer's dst through the copy engines, one side stream per peer, then count this rank's arrival."""
+
+    def __init__(self, dsts_local, n, world, rank, peer_delta):
+        import ctypes as C
+        d = [t for t in dsts_local if t is not None]
+        self.keep = d
+        self.nmat, self.n, self.world, self.rank = len(d), n, world, rank
+        self.src = (C.c_void_p * max(1, len(d)))(*[t.data_ptr() for t in d])
+        self.stride = (C.c_int64 * max(1, len(d)))(*[t.stride(0) for t in d])
+        self.cols = (C.c_int64 * max(1, len(d)))(*[t.shape[1] for t in d])
+        self.delta = (C.c_int64 * world)(*peer_delta)
+
+    def __call__(self, ptr_sync, stream=None):
+        qmm.check(qmm.lib().b200_rowsplit_push(self.nmat, self.src, self.stride, self.cols, self.n, self.world, self.rank,
+                                               self.delta, ptr_sync, qmm._stream_ptr(stream)))
+
+
+def row_split_push_join(stream=None):
+    qmm.check(qmm.lib().b200_rowsplit_push_join(qmm._stream_ptr(stream)))
+
+
 def row_split_wait(ptr_sync, rank, world, stream=None, calls=1):
     """stream-ordered wait until the slices of all `world` ranks (x `calls` fused calls sharing the block) have landed
     in this rank's dst; re-arms the counter"""
