@@ -346,6 +346,12 @@ __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[32]) { tm
 __device__ __forceinline__ void tmem_ldw(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld16(taddr, r); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // eight columns of this warp's 32 lanes <- one 32-bit value (EPI 3: the accumulator's conversion bias, see below)
+// Measured (profiles/r02/ncu_mmq_p_v3_tmem_bias_*): the store's source is a vector of DISTINCT registers, and under the
+// 96-register cap ptxas re-creates the constant in them before every store (8 IMAD.MOV per 8 columns), so the instruction
+// count per element stays where it was and the gain is small (+1 % on the 8B step, +3.5 % on 28672 x 4096 x 512).  Two
+// alternatives were built and dropped: holding the fill registers for the whole kernel (ptxas merges equal values and
+// copies them anyway; spills), and refilling from shared memory with tcgen05.cp from the MMA thread (correct, but 32
+// copies of 4 KB per chunk run in order with the MMAs at ~100 B/clk: 79 -> 111 us).
 __device__ __forceinline__ void tmem_st8_fill(uint32_t taddr, uint32_t v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(v) : "memory");
 }
