@@ -315,9 +315,15 @@ int b200_dequantize_f32(int type, const void * w, int64_t w_row_stride, float * 
 //  * fused   : every CTA quantizes the f32 row into its shared memory cooperatively.  One launch per matmul, but 150-300
 //              CTAs re-reading and re-quantizing the same row cost 2-5 us between the dependency release and the first
 //              dot product (k = 4096: 6.8 us vs 6.0 us per matmul; k = 14336: 18 us vs 12 us).
-// So separate is the default; B200_FUSED_QUANT_MAX_K > 0 opts single-column matmuls with k <= that into the fused path.
-static int fused_quant_max_k() { return env_knob("B200_FUSED_QUANT_MAX_K", 0); }
-static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k(); }
+// Round 2 re-measured it after the quantizer got 8 loads per lane in flight (one L2 round trip for k <= 16384), conflict-free
+// unit loads and grouped launches: on whole decode tokens the fused form now wins for k <= 8192 (8B token 660 -> 687 tok/s
+// with k = 4096 fused; 70B 122.0 -> 122.7 with k = 8192) and still loses for the long rows (k = 14336: 676; k = 28672:
+// 117.6), where 148 CTAs re-quantizing 57-115 KB each cost more than the launch they save.  Default: fused for
+// single-column matmuls with k <= 8192 (B200_FUSED_QUANT_MAX_K, 0 = never) -- except when x is pinned HOST memory read in
+// place (the _host entries): 148 CTAs reading it over PCIe is far worse than one quantizer kernel doing it once.
+static thread_local bool tl_x_in_host_memory = false;
+static int fused_quant_max_k() { return env_knob("B200_FUSED_QUANT_MAX_K", 8192); }
+static bool use_fused_quant(int64_t n, int64_t k) { return n == 1 && k <= fused_quant_max_k() && !tl_x_in_host_memory; }
 // in-lane activation quantizer inside the GEMV (no quantizer kernel): B200_INLANE_QUANT=1
 static bool use_inlane_quant() { return env_knob("B200_INLANE_QUANT", 0) != 0; }
 
@@ -329,7 +335,8 @@ static bool use_mmq(int type, int64_t n, int64_t k) { return n >= mmq_min_batch(
 size_t b200_mul_mat_workspace_size(int type, int64_t m, int64_t n, int64_t k) {
     if (!weight_type(type) || k <= 0 || n <= 0 || m <= 0) return 0;
     if (use_mmq(type, n, k)) return ws_align(mmq_plane_bytes(type, m, k)) + mmq_workspace_bytes(n, k);
-    if (use_fused_quant(n, k)) return 0;
+    // (the fused quantizer needs no scratch, but which form runs may differ between this query and the call -- a knob
+    //  re-read, a host-resident x -- so the size never depends on it)
     return (size_t) n * q8_soa_layout(k).bytes;
 }
 
@@ -517,8 +524,8 @@ int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, cons
     int i = 0;
     while (i < nmat) {
         const int type = types[i], il = type == B200_TYPE_IQ4_XS ? 1 : 0;
-        const bool inlane = use_inlane_quant();
-        if (!inlane && !have[il]) {
+        const bool inlane = use_inlane_quant(), fusedq = use_fused_quant(n, k);
+        if (!inlane && !fusedq && !have[il]) {
             int st = launch_quantize_q8_soa(x, x_row_stride, xq[il], k, n, il == 1, stream);
             if (st != B200_OK) return st;
             have[il] = true;
@@ -537,6 +544,7 @@ int b200_mul_mat_multi(int nmat, const int * types, const void * const * W, cons
             g.ncols = (int) (n - c0 < maxc ? n - c0 : maxc);
             g.xq    = xq[il] + (size_t) c0 * L.bytes;
             if (inlane) g.xq = nullptr, g.x = x + c0 * x_row_stride, g.x_col_stride = x_row_stride, g.inlane = true;
+            if (fusedq) g.xq = nullptr, g.x = x, g.x_col_stride = x_row_stride;   // every CTA quantizes x into its shared memory
             g.W = (const uint8_t *) W[i], g.dst = dst[i] + c0 * dst_row_stride[i], g.dst_col_stride = dst_row_stride[i];
             g.m = total, g.nmat = j - i;
             int64_t at = m[i];
@@ -593,8 +601,10 @@ int b200_mul_mat_host(int type, const void * W, int64_t w_row_stride, const floa
         if (k > 0) B200_CUDA_TRY(cudaMemcpyAsync(x_dev, x_host, (size_t) n * k * 4, cudaMemcpyHostToDevice, stream));
         x_in = x_dev;
     }
+    tl_x_in_host_memory = x_in != x_dev;
     const int st = b200_mul_mat(type, W, w_row_stride, x_in, k, dst_dev, m, m, n, k, ws,
                                 b200_mul_mat_workspace_size(type, m, n, k), stream_);
+    tl_x_in_host_memory = false;
     if (st != B200_OK) return st;
     return results_to_host(dst_host, dst_dev, (size_t) n * m, stream);
 }
@@ -639,8 +649,10 @@ int b200_mul_mat_multi_host(int nmat, const int * types, const void * const * W,
         dd[i] = dst_dev + off, ds[i] = m[i];
         off += (size_t) n * m[i];
     }
+    tl_x_in_host_memory = x_in != x_dev;
     const int st = b200_mul_mat_multi(nmat, types, W, x_in, k, dd, ds, m, n, k, ws,
                                       b200_mul_mat_multi_workspace_size(nmat, types, m, n, k), stream_);
+    tl_x_in_host_memory = false;
     if (st != B200_OK) return st;
     for (int i = 0; i < nmat;) {
         int    j     = i + 1;

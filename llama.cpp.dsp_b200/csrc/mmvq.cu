@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(gemv_shape<NCOLS, MINB>::THREADS, gemv_shape<N
     if (a.act_bytes) {
         // fused quantizer: all NW compute warps (spare ones included) quantize the row into shared memory once,
         // eight lanes per 32-block, with exactly the arithmetic of the standalone kernel (actquant.cuh)
-        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS, 4, false, true>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
+        quantize_row_q8_soa<TYPE == B200_TYPE_IQ4_XS, 8, false, true>(x, a.k, smem, L, warp, NW, lane, (uintptr_t) x % 16 == 0);
         asm volatile("bar.sync 1, %0;" ::"n"(NW * 32) : "memory");
     }
     const int team = warp / T, wt = warp - team * T;
@@ -566,7 +566,7 @@ static int launch_gemv_t(const gemv_args & g, cudaStream_t stream) {
     // in-lane (g.inlane: any column count, no shared memory)
     const bool fused = g.xq == nullptr && !g.inlane;
     if (fused && NCOLS != 1) return B200_ERR_UNSUPPORTED;
-    if (g.nmat > 1 && (!contiguous || fused || g.ids || g.it_hdr || g.world > 1)) return B200_ERR_UNSUPPORTED;
+    if (g.nmat > 1 && (!contiguous || g.ids || g.it_hdr || g.world > 1)) return B200_ERR_UNSUPPORTED;
     if (g.it_hdr && (fused || g.inlane || g.world > 1)) return B200_ERR_UNSUPPORTED;
     if (!make_plan(TYPE, g.k, NCOLS, contiguous, (g.m + gx0 - 1) / gx0, fused, P)) return B200_ERR_UNSUPPORTED;
     int64_t gx = (int64_t) g_sm_count * P.minb * env_int("B200_GEMV_WAVES", 1);

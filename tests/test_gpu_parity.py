@@ -433,8 +433,17 @@ def test_mul_mat_multi_launches_fewer_kernels(qmm):
     ws = [dev(qref.random_blocks(t, m, k, rng)) for t, m in spec]
     x = dev(rng.uniform(-1, 1, (1, k)).astype(np.float32))
     before = qmm.launch_count()
-    qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
-    assert qmm.launch_count() - before == 2          # one quantizer + one GEMV for three matrices
+    got = qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
+    assert qmm.launch_count() - before == 1          # ONE GEMV for three matrices; its CTAs quantize x themselves (k <= 8192)
+    qmm.setenv(B200_FUSED_QUANT_MAX_K=0)
+    try:
+        before = qmm.launch_count()
+        sep = qmm.mul_mat_multi([t for t, _ in spec], ws, x, [m for _, m in spec], k)
+        assert qmm.launch_count() - before == 2      # the separate quantizer kernel + one GEMV
+    finally:
+        qmm.setenv(B200_FUSED_QUANT_MAX_K=None)
+    for a, b in zip(got, sep):
+        assert torch.equal(a, b)                     # the same quantizer arithmetic either way
 
 
 def test_mmq_multi_planes_equal_single_calls(qmm):
