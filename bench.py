@@ -1205,18 +1205,36 @@ def main():
             torch.cuda.empty_cache()
 
     # ---- N > 1: the SAME workload on ONE GPU (rank 0 alone, the other ranks wait), so that the line carries the
-    #      row-split speed-up measured in the same run on the same box (the driver's own N=1 run uses the 8B workload)
+    #      row-split speed-up measured in the same run on the same box, with the same grouped calls as the N = 1 bench line
     single = None
     if world > 1 and not args.no_single:
         if rank == 0:
             del weights
             torch.cuda.empty_cache()
             full = [gen_weights(torch, t, m, k, gen, dev) for _, t, m, k in mms]
-            outs = {m: torch.zeros((n, m), device=dev) for _, _, m, _ in mms}
+            # the same grouped calls as the N = 1 bench line (matmuls sharing activations in one b200_mul_mat_multi)
+            def group_of1(name):
+                base = name.split(".")[0]
+                return {"attn_q": "qkv", "attn_k": "qkv", "attn_v": "qkv", "ffn_gate": "gu", "ffn_up": "gu"}.get(base, base)
+            g1groups, outs1 = [], {}
+            for (name, t, m, k), w in zip(mms, full):
+                key = (group_of1(name), name.split(".")[-1])
+                if not g1groups or g1groups[-1][0] != key:
+                    g1groups.append((key, k, []))
+                g1groups[-1][2].append((name.split(".")[0], t, m, w))
+            calls1 = []
+            for _, k, members in g1groups:
+                oo = []
+                for base, t, m, w in members:
+                    if base not in outs1:
+                        outs1[base] = torch.zeros((n, m), device=dev)
+                    oo.append(outs1[base])
+                calls1.append((qmm.MultiMatMul([t for _, t, _, _ in members], [w for _, _, _, w in members],
+                                               [m for _, _, m, _ in members], k, oo, n), xs[k]))
 
             def token_step_1gpu():
-                for (name, t, m, k), w in zip(mms, full):
-                    qmm.mul_mat(t, w, xs[k], m, k, out=outs[m])
+                for call, x in calls1:
+                    call(x)
             with torch.cuda.stream(stream):
                 token_step_1gpu()
                 stream.synchronize()
@@ -1237,8 +1255,8 @@ def main():
             single = {"value": 1e3 / ms1, "unit": "tok/s", "ms_per_step": ms1, "steps": k1, "n_gpus": 1,
                       "speedup_of_this_run": ms1 / ms_step,
                       "hbm_gbs": total_bytes_all_ranks / ms1 / 1e6,
-                      "note": "same workload, all rows on rank 0's GPU, CUDA-graph replay, measured in this run"}
-            del full, g1
+                      "note": "same workload, all rows on rank 0's GPU, grouped calls as at N = 1, CUDA-graph replay, measured in this run"}
+            del full, g1, calls1, outs1
             torch.cuda.empty_cache()
             weights = []
         dist.barrier()
