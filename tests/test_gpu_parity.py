@@ -709,3 +709,23 @@ def test_small_batches_on_a_cached_plane(qmm):
             got_g = qmm.mul_mat(t, wd, dev(x), m, k).cpu().numpy()
             assert qref.nmse(got_p, want) < 5e-4 and qref.nmse(got_g, want) < 5e-4
             assert qref.nmse(got_p, got_g) < 5e-4
+
+
+@pytest.mark.gpu
+def test_sequence_rows_with_an_odd_number_of_blocks(qmm):
+    """k % 64 == 32 (Q4_0 / Q8_0 only): the last 64-element unit of a row has one block; the sequence kernel's in-CTA
+    quantizer (rotated chunks, qs padded to whole units) must give the bits of b200_mul_mat."""
+    rng = np.random.default_rng(77)
+    groups, want = [], []
+    for k, t, m in [(96, qref.Q4_0, 40), (1056, qref.Q8_0, 300), (4128, qref.Q4_0, 520), (96, qref.Q8_0, 8)]:
+        w = dev(qref.random_blocks(t, m, k, rng))
+        x = dev(rng.uniform(-1, 1, (k,)).astype(np.float32))
+        out = torch.full((m,), float("nan"), device="cuda")
+        groups.append((x, k, [(t, w, m, out)], True))
+        want.append(qmm.mul_mat(t, w, x.view(1, k), m, k)[0])
+    seq = qmm.Sequence(groups)
+    seq()
+    torch.cuda.synchronize()
+    assert seq.status() == 0
+    for (_, _, mats, _), wv in zip(groups, want):
+        assert torch.equal(mats[0][3], wv)
