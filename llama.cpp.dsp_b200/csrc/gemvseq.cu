@@ -27,10 +27,17 @@
 //    2.6x slower (profiles/r02/seq_bench_*.log);
 //  * per-stage compute is the code of mmvq.cu (gemv_core.cuh): one 64-element unit of k per lane in registers, dp4a,
 //    butterfly over V rows, deterministic team reduction.  Results are bit-identical to b200_mul_mat.
-// Measured (8B token, 129 dependent groups, profiles/r02/seq_trace_v4_slot24k.log): steady-state streaming inside a
-// group reaches 6.7 TB/s, a group boundary costs ~3.2 us (1.0 grid-wide arrival + 1.1 quantize + 1.1 first weights), the
-// token 1.74 ms as one launch -- better than 1.85 ms of eager per-group launches, behind their CUDA-graph replay (1.54 ms):
-// the dot products issue at about the HBM rate, so compute-warp idle time at a boundary is not made up afterwards.
+//  * split-mode row (b200_sequence_plan_build_rowsplit): one such launch per rank; a computed row leaves the epilogue as
+//    8-byte {value, tag} stores into every peer's exchange buffer, each rank polls the tags of the rows it expects, copies
+//    them into its dst and publishes the group on a LOCAL counter ("flag in the data": no system-scope fence, no remote
+//    atomics); the older protocol (rows stored straight into the peers' dst, fence.acq_rel.sys + one remote add per rank)
+//    is kept behind peer_ll == NULL.
+// Measured (profiles/r02/seq_*.log, bench_n{2,4,8}_final.json): on ONE GPU a CUDA-graph replay of grouped
+// calls is still faster (8B token 1.59 ms as one launch against 1.46 ms; 70B 10.0 against 8.2 ms) -- a group boundary
+// costs 3-7 us (publish, grid-wide arrival, quantizer, first stage), every round trip of it queues behind the weight
+// prefetch, and the run-time-dispatched stage loop executes ~25 % more instructions than the templated per-call kernel
+// while both are issue-latency-bound.  Under row split the launches are what hurts, and this kernel is the fastest path:
+// 156-159 / 219-223 / 268-274 tok/s on 2 / 4 / 8 GPUs against 118 / 142 / 157 with one fused launch per matmul.
 // n = 1 only (the decode token); larger batches keep the per-group entry points.
 #include "gemv_core.cuh"
 #include "kernels.h"
