@@ -68,3 +68,26 @@ def test_status_strings_and_no_device_is_loud(qmm):
         # host tensors are rejected outright: the product has no CPU path
         with pytest.raises(qmm.B200Error):
             qmm.mul_mat(12, torch.zeros(144, dtype=torch.uint8), torch.zeros((1, 256)), 1, 256)
+
+
+def test_header_compiles_as_c_and_struct_layout_matches_binding(qmm, tmp_path):
+    """include/b200_qmm.h is plain C (no CUDA / C++ / torch types) and the one struct that crosses the boundary,
+    b200_seq_group, has the layout the ctypes binding assumes (size and field offsets from a C compiler)."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "b200_qmm.h"\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(b200_seq_group), '
+                   'offsetof(b200_seq_group, x_device), offsetof(b200_seq_group, k), offsetof(b200_seq_group, nmat), '
+                   'offsetof(b200_seq_group, type), offsetof(b200_seq_group, W_device), offsetof(b200_seq_group, dst_device), '
+                   'offsetof(b200_seq_group, m)); return 0; }\n')
+    exe = tmp_path / "layout"
+    subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE, text=True).stdout.split()]
+    S = qmm.qmm.SeqGroup
+    want = [C.sizeof(S), S.x.offset, S.k.offset, S.nmat.offset, S.type.offset, S.W.offset, S.dst.offset, S.m.offset]
+    assert got == want, (got, want)
