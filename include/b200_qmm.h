@@ -262,8 +262,9 @@ B200_API int b200_sequence_plan_build(const b200_seq_group * groups, int ngroups
  * the reference's get_row_split rule.  Every dst lies inside this rank's symmetric allocation [peer_base[rank],
  * + span_bytes); peer_base[r], peer_sync[r] (>= 2 * ngroups ints, zeroed once) and peer_ll[r] are rank r's buffers mapped
  * into this process (b200_ipc_*).  Every group is ordered after the one before it.
- *   peer_ll != NULL ("flag in the data"): every rank has an exchange buffer of 2 * span_bytes, zeroed before the plans are
- *     built and used by one plan at a time.  A computed row is stored in the peers as 8 bytes {value, tag of (launch,
+ *   peer_ll != NULL ("flag in the data"): every rank has an exchange buffer of 2 * span_bytes used by one plan at a time;
+ *     building a plan clears this rank's buffer (stream-ordered), and the ranks must meet at a barrier between building
+ *     their plans and the first run.  A computed row is stored in the peers as 8 bytes {value, tag of (launch,
  *     group)}; each rank polls the tags of the rows it expects, copies the values into its dst and publishes the group on a
  *     local counter -- one NVLink store latency per group, no system-scope fence, no remote atomics.  Consecutive groups
  *     may not write the same dst rows (B200_ERR_SHAPE).

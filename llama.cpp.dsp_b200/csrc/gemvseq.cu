@@ -697,6 +697,12 @@ int b200_sequence_plan_build_rowsplit(const b200_seq_group * groups, int ngroups
         if (peer_ll && (!peer_ll[r] || (uintptr_t) peer_ll[r] % 8 != 0)) return B200_ERR_ALIGNMENT;
     }
     seq_split_info sp = {world, rank, peer_base, span_bytes, peer_sync, world > 1 ? peer_ll : nullptr};
+    if (sp.peer_ll) {
+        // a new plan starts its tags at 1 again: slots of THIS rank's exchange buffer that an earlier plan tagged must not
+        // look valid to it.  (The peers write into this buffer as soon as they RUN their plans: the ranks need a barrier
+        // between building and the first run, which they need anyway to know that every plan exists.)
+        B200_CUDA_TRY(cudaMemsetAsync(peer_ll[rank], 0, 2 * span_bytes, (cudaStream_t) stream_));
+    }
     return seq_build(groups, ngroups, plan_device, plan_bytes, &sp, (cudaStream_t) stream_);
 }
 
