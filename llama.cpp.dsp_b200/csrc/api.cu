@@ -970,6 +970,7 @@ struct push_state {
     bool         pending[16] = {};
 };
 static push_state g_push[MAX_DEVICES];
+static std::mutex g_push_mutex;   // the side streams / events of a device are shared by all host threads that push on it
 
 static int push_state_get(push_state *& ps, int world) {
     const int dev = current_device();
@@ -983,7 +984,12 @@ static int push_state_get(push_state *& ps, int world) {
     return B200_OK;
 }
 
+static int rowsplit_push_join_locked(b200_stream_t stream_);
 int b200_rowsplit_push_join(b200_stream_t stream_) {
+    std::lock_guard<std::mutex> lock(g_push_mutex);
+    return rowsplit_push_join_locked(stream_);
+}
+static int rowsplit_push_join_locked(b200_stream_t stream_) {
     push_state * ps = nullptr;
     int st = push_state_get(ps, 0);
     if (st != B200_OK) return st;
@@ -1002,10 +1008,11 @@ int b200_rowsplit_push(int nmat, float * const * src_local, const int64_t * row_
     if (nmat > 0 && (!src_local || !row_stride || !cols)) return B200_ERR_SHAPE;
     for (int r = 0; r < world; r++)
         if (!peer_sync[r]) return B200_ERR_ALIGNMENT;
+    std::lock_guard<std::mutex> lock(g_push_mutex);
     push_state * ps = nullptr;
     int st = push_state_get(ps, world);
     if (st != B200_OK) return st;
-    st = b200_rowsplit_push_join(stream_);                      // at most one group of pushes in flight per peer
+    st = rowsplit_push_join_locked(stream_);                    // at most one group of pushes in flight per peer
     if (st != B200_OK) return st;
     B200_CUDA_TRY(cudaEventRecord(ps->fork, stream));           // the slices are complete from here on
     for (int r = 0; r < world; r++) {
