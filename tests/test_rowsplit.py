@@ -243,3 +243,50 @@ def test_fused_row_split_prefill_one_device():
         for rank in range(world):
             assert torch.equal(sym[rank, off:off + n * m].view(n, m), w_), (m, rank)
         off += n * m
+
+
+@pytest.mark.gpu
+def test_copy_engine_push_one_device():
+    """b200_rowsplit_push with ONE device playing both ranks: each "rank" multiplies its row slices locally
+    (b200_mul_mat_mmq_multi into its own copy of dst), the push copies them into the other copy through side streams and
+    counts the arrivals; both copies must hold the whole result, and the sync blocks must be re-armed by the waits."""
+    import ctypes as C
+    qmm = b200pkg.load()
+    from llama_cpp_dsp_b200.rowsplit import RowSplitPush, row_split_push_join, row_split_wait
+    rng = np.random.default_rng(22)
+    world, n, k = 2, 96, 1024
+    mats = [(qref.Q4_K, 768), (qref.IQ4_XS, 256)]
+    ws_ = [torch.from_numpy(qref.random_blocks(t, m, k, rng)).cuda() for t, m in mats]
+    x = torch.from_numpy(rng.uniform(-1, 1, (n, k)).astype(np.float32)).cuda()
+    total = sum(n * m for _, m in mats)
+    sym = torch.full((world, total), float("nan"), device="cuda")
+    syncs = torch.zeros((world, 2), dtype=torch.int32, device="cuda")
+    ptr_sync = (C.c_void_p * world)(*[syncs[r].data_ptr() for r in range(world)])
+    want = []
+    for rank in range(world):
+        delta = [(r - rank) * total * 4 for r in range(world)]
+        dl, off = [], 0
+        for (t, m), w in zip(mats, ws_):
+            lo, hi = qmm.row_split(m, world, rank)
+            full = sym[rank, off:off + n * m].view(n, m)
+            if hi > lo:
+                plane = qmm.build_plane(t, w[lo:hi].contiguous(), hi - lo, k)
+                qmm.mul_mat_mmq(t, plane, x, hi - lo, k, out=full[:, lo:hi])
+                dl.append(full[:, lo:hi])
+            off += n * m
+        RowSplitPush(dl, n, world, rank, delta)(ptr_sync)
+    for rank in range(world):
+        row_split_wait(ptr_sync, rank, world)
+    row_split_push_join()
+    torch.cuda.synchronize()
+    assert int(syncs.abs().sum()) == 0
+    off = 0
+    for (t, m), w in zip(mats, ws_):
+        a, b = sym[0, off:off + n * m].view(n, m), sym[1, off:off + n * m].view(n, m)
+        assert not torch.isnan(a).any() and torch.equal(a, b), m
+        for rank in range(world):                            # every slice equals the matmul on that rank's rows alone
+            lo, hi = qmm.row_split(m, world, rank)
+            if hi > lo:
+                ref = qmm.mul_mat_mmq(t, qmm.build_plane(t, w[lo:hi].contiguous(), hi - lo, k), x, hi - lo, k)
+                assert torch.equal(a[:, lo:hi], ref), (m, rank)
+        off += n * m
